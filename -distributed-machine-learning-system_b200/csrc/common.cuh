@@ -1,0 +1,151 @@
+// Shared declarations of the idunno_b200 CUDA library (sm_100a only).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/idunno_b200.h"
+
+namespace idn {
+
+typedef __nv_bfloat16 bf16;
+
+void set_error(const std::string& msg);
+const char* last_error_cstr();
+
+#define IDN_CUDA_TRY(expr)                                                                   \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess) {                                                                 \
+      ::idn::set_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e) + " (" +    \
+                       __FILE__ + ":" + std::to_string(__LINE__) + ")");                     \
+      return IDN_ECUDA;                                                                      \
+    }                                                                                        \
+  } while (0)
+
+#define IDN_TRY(expr)                 \
+  do {                                \
+    int _r = (expr);                  \
+    if (_r != IDN_OK) return _r;      \
+  } while (0)
+
+inline uint16_t f32_to_bf16_bits(float f) {  // round to nearest even, as torch .to(bfloat16)
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+inline float bf16_bits_to_f32(uint16_t b) {
+  uint32_t u = (uint32_t)b << 16;
+  float f;
+  std::memcpy(&f, &u, 4);
+  return f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Convolution / FC as "shifted GEMM":  out[q][n] = sum_taps sum_c A[q + off(tap)][c] * Wt[n][tap, c]
+//
+// Activations live in HBM as bf16 "flat padded NHWC": image n occupies img_rows = Hp*Wp rows of C
+// channels; pixel (h, w) is row n*img_rows + h*Wp + w; rows with h >= H or w >= W are zero and stay
+// zero (they are the convolution's zero padding: the row before pixel (h, 0) is pixel (h-1, Wp-1),
+// a pad column).  A filter tap (r, s) of a stride-1 convolution is then the constant row offset
+// (r-pad)*Wp + (s-pad), i.e. a plain 2-D TMA box over the [rows][C] matrix.  Stride-2 convolutions
+// read "parity planes" (the producing layer scatters pixel (h,w) to plane (h&1, w&1)), which makes
+// their taps constant row offsets as well.  The two stem convolutions (C=3) use a 5-D tensor map
+// with overlapping strides over a 4-channel NHWC image (see conv_tc.cu).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxTaps = 32;
+constexpr int kBlockM = 128;   // GEMM rows (pixels) per tile == TMEM lanes
+constexpr int kBlockK = 64;    // bf16 channels per k-block == one 128-byte swizzle row
+constexpr int kStemTW = 16;    // stem tile: 16 x 8 output pixels
+constexpr int kStemTH = 8;
+
+enum { MODE_FLAT = 0, MODE_STEM = 1 };
+enum { DEST_GEOM = 0, DEST_PARITY = 1 };
+
+struct ConvParams {
+  // K loop
+  int num_taps;
+  int c_blocks;               // 64-channel blocks per tap
+  int tap_off[kMaxTaps];      // flat: row offset of the tap; stem: row-group offset `a` of the tap
+  int tap_par[kMaxTaps];      // stem: row phase `b` of the tap (input row = stride*(oh+a)+b)
+  // tiles
+  int num_m_tiles, num_n_tiles;
+  // tile (source) geometry
+  int mode;
+  int nimg;                   // images valid in this pass
+  int img_rows, wp, H, W;     // flat: rows per image, row pitch, valid extents (stem: H=OH, W=OW)
+  int tiles_w, tiles_h;       // stem: tiles per image
+  // destination
+  int dest_mode;
+  int d_img_rows, d_wp, d_plane_rows;
+  int ldc;                    // elements per destination row
+  int n_total;                // padded Cout (multiple of the N tile)
+  void* out;
+  const bf16* residual;       // same geometry as the tile rows (flat only), ld = ldc
+  const float* scale;
+  const float* shift;
+  int relu;
+  int out_f32;
+  // raw operand views for the SIMT cross-check kernel
+  const bf16* a_ptr;
+  const bf16* b_ptr;
+  long long a_rows;           // flat: number of rows of A (reads outside are zero, like TMA)
+  int a_ld;                   // flat: elements per A row
+  int ktot;                   // elements per B row (= num_taps * c_blocks * 64)
+  int st_stride, st_ws, st_h, st_ow, st_nrow;   // stem image: conv stride, row pitch (px), rows,
+                                                // window starts per row, row groups per image
+};
+
+// launchers (conv_tc.cu / conv_simt.cu)
+int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int block_n,
+                   int num_sms, cudaStream_t st);
+int launch_conv_simt(const ConvParams& p, cudaStream_t st);
+int read_tc_watchdog();
+int conv_tc_configure();   // cudaFuncSetAttribute for every instantiation; once per process/device
+
+// tensor maps (conv_tc.cu)
+int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner_elems, uint64_t rows,
+                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
+int make_tmap_stem(CUtensorMap* tm, const void* base, int conv_stride, int ws_px, int img_h, int ow,
+                   int nimg_cap);
+
+// other kernels (pool_head.cu)
+struct PoolParams {
+  const bf16* in; bf16* out;
+  int nimg, C;
+  int s_img_rows, s_wp, H, W;      // source geometry (flat padded or dense)
+  int d_img_rows, d_wp, OH, OW;    // destination geometry
+  int pad;                          // 3x3 window, stride 2
+};
+int launch_maxpool(const PoolParams& p, cudaStream_t st);
+int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
+                       const float* fc_w, const float* fc_b, float* logits_or_null, int32_t* idx,
+                       float* prob, cudaStream_t st);
+int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out_or_null,
+                        int32_t* idx, float* prob, cudaStream_t st);
+
+// preprocess (preprocess.cu)
+struct PreMeta {            // one per image, device resident
+  long long offset;         // byte offset of the image in the packed buffer
+  int H, W;                 // source size
+  int htab, vtab;           // offsets (in int32 units) of the resample tables in the table pool
+};
+enum { PRE_OUT_NCHW = 0, PRE_OUT_STEM = 1 };
+int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
+                      const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
+                      int stem_ws, cudaStream_t st);
+// Builds the resample table (Pillow fixed point) of the 224 cropped outputs of one axis.
+void build_axis_table(int in_size, int out_size, int crop_off, std::string* ints /* int32 bytes */);
+void resized_size(int h, int w, int* nh, int* nw);
+int crop_offset(int resized);
+void build_norm_lut(uint16_t* lut768);
+
+}  // namespace idn

@@ -1,0 +1,558 @@
+// Implicit-GEMM convolution / FC on the 5th-generation tensor cores (sm_100a).
+//
+//   D[128 pixels x BLOCK_N channels] (fp32, TMEM) += A[128 x 64] (bf16, smem) * B[BLOCK_N x 64]^T
+//
+// * one persistent CTA per SM, 8 warps: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer,
+//   warp 2 = TMEM allocator, warps 4..7 = epilogue (one thread per TMEM lane / output pixel);
+// * operands arrive by TMA (cp.async.bulk.tensor) into a kStages-deep ring of 128B-swizzled,
+//   K-major tiles; mbarriers full[s]/empty[s] pair the producer with the MMA warp;
+// * the accumulator is double buffered in TMEM (tmem_full[a]/tmem_empty[a]) so the epilogue of
+//   tile i overlaps the k-loop of tile i+1;
+// * a filter tap is a row offset into the flat padded NHWC activation matrix (common.cuh), so the
+//   k-loop is (taps x 64-channel blocks) and the A box of every k-block is a plain 2-D TMA box;
+// * epilogue: tcgen05.ld -> per-channel fp32 scale/shift (folded BatchNorm or bias) -> optional
+//   residual add -> optional ReLU -> bf16 (or fp32 logits) with 128-bit stores, written either in
+//   the tile's own geometry or scattered to the parity planes a following stride-2 layer reads.
+//
+// Stem convolutions (C = 3; ResNet18 7x7 s2 p3, AlexNet 11x11 s4 p2) use MODE_STEM: the
+// preprocess kernel writes the normalised image as 4-channel NHWC with the convolution's left
+// padding materialised, and a 5-D tensor map with OVERLAPPING strides does the im2col: dim0 is a
+// 16-pixel (64-element, 128-byte) window, dim1 steps by `stride` pixels (16/32 bytes) per output
+// column, dim2 is the row phase, dim3 the row group (OOB rows = zero padding), dim4 the image.
+// One k-block per filter row; window positions beyond the filter width meet zero weights.
+#include "common.cuh"
+
+namespace idn {
+
+// ------------------------------------------------------------------------------------------ PTX
+namespace ptx {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok;
+}
+__device__ __forceinline__ unsigned long long globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                            int c0, int c1, int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst),
+               "n"(COLS)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS)
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; bf16 inputs, fp32 accumulate, issued by ONE thread.
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrives once every tcgen05.mma issued so far by this thread has completed.
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   bar)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+}  // namespace ptx
+
+// Diagnostics of a pipeline stall: [0] = 1 when a wait timed out, [1] = role (0 producer, 1 MMA
+// waiting for the epilogue, 2 MMA waiting for TMA, 3 epilogue), [2] = blockIdx, [3] = k-block /
+// tile.  A stalled wait makes every role of every CTA leave its loop, so a broken pipeline ends
+// the kernel with an error the host can read (read_tc_watchdog) instead of hanging the GPU.
+__device__ unsigned int g_tc_watchdog[4];
+
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, int role, int where) {
+  if (ptx::mbar_try_wait(bar, parity)) return true;
+  const unsigned long long t0 = ptx::globaltimer();
+  unsigned int spins = 0;
+  while (!ptx::mbar_try_wait(bar, parity)) {
+    if ((++spins & 0x3ffu) == 0) {
+      if (*reinterpret_cast<volatile unsigned int*>(&g_tc_watchdog[0]) != 0) return false;
+      if (ptx::globaltimer() - t0 > 2000000000ull) {  // 2 s
+        if (atomicCAS(&g_tc_watchdog[0], 0u, 1u) == 0u) {
+          g_tc_watchdog[1] = (unsigned)role; g_tc_watchdog[2] = blockIdx.x;
+          g_tc_watchdog[3] = (unsigned)where;
+        }
+        __threadfence();
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+// Shared-memory matrix descriptor of a K-major, 128B-swizzled tile (rows of 128 bytes; 8-row
+// groups 1024 bytes apart): start>>4 | LBO(unused for swizzled K-major)=1 | SBO=1024>>4 |
+// version=1 (sm_100) | layout_type=2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// Instruction descriptor, kind::f16: D=f32 (bit 4), A=B=bf16 (bits 7, 10), both K-major,
+// N>>3 at bit 17, M>>4 at bit 24.
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(m >> 4) << 24);
+}
+
+template <int BLOCK_N>
+struct TcCfg {
+  static constexpr int A_BYTES = kBlockM * kBlockK * 2;          // 16 KiB
+  static constexpr int B_BYTES = BLOCK_N * kBlockK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int kStages = BLOCK_N <= 64 ? 8 : BLOCK_N <= 128 ? 6 : BLOCK_N <= 192 ? 5 : 4;
+  static constexpr int TMEM_COLS = 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + 1024;  // + align slack
+};
+
+struct RowInfo {
+  bool valid;
+  long long dst_row;
+  long long res_row;
+};
+
+// Maps row i of M-tile m_tile to its image/pixel and to the destination row (shared with SIMT).
+__device__ __forceinline__ RowInfo decode_row(const ConvParams& p, int m_tile, int i) {
+  RowInfo r;
+  int n, h, w;
+  if (p.mode == MODE_FLAT) {
+    const long long q = (long long)m_tile * kBlockM + i;
+    n = (int)(q / p.img_rows);
+    const int rem = (int)(q - (long long)n * p.img_rows);
+    h = rem / p.wp;
+    w = rem - h * p.wp;
+    r.res_row = q;
+  } else {
+    const int per_img = p.tiles_w * p.tiles_h;
+    n = m_tile / per_img;
+    const int t = m_tile - n * per_img;
+    const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
+    h = th * kStemTH + i / kStemTW;
+    w = tw * kStemTW + i % kStemTW;
+    r.res_row = 0;
+  }
+  r.valid = (n < p.nimg) && (h < p.H) && (w < p.W);
+  if (p.dest_mode == DEST_GEOM) {
+    r.dst_row = (long long)n * p.d_img_rows + (long long)h * p.d_wp + w;
+  } else {
+    r.dst_row = (long long)((h & 1) * 2 + (w & 1)) * p.d_plane_rows + (long long)n * p.d_img_rows +
+                (long long)(h >> 1) * p.d_wp + (w >> 1);
+  }
+  return r;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int BLOCK_N, int MODE>
+__global__ void __launch_bounds__(256, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ ConvParams p) {
+  using Cfg = TcCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;   // SWIZZLE_128B tiles need 1024-byte alignment
+  const uint32_t bar_base = base + kStages * Cfg::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int k_blocks = p.num_taps * p.c_blocks;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(tfull_bar(a), 1);
+      ptx::mbar_init(tempty_bar(a), 4);   // one arrive per epilogue warp
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool alive = true;
+      for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+        const int m_tile = tile / p.num_n_tiles;
+        const int n_tile = tile - m_tile * p.num_n_tiles;
+        int st_n = 0, st_th = 0, st_tw = 0;
+        if (MODE == MODE_STEM) {
+          const int per_img = p.tiles_w * p.tiles_h;
+          st_n = m_tile / per_img;
+          const int t = m_tile - st_n * per_img;
+          st_th = t / p.tiles_w;
+          st_tw = t - st_th * p.tiles_w;
+        }
+        int tap = 0, cb = 0;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb)) { alive = false; break; }
+          const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
+          const uint32_t b_dst = a_dst + Cfg::A_BYTES;
+          ptx::mbar_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
+          if (MODE == MODE_FLAT) {
+            ptx::tma_load_2d(a_dst, &tmA, full_bar(s), cb * kBlockK,
+                             m_tile * kBlockM + p.tap_off[tap]);
+          } else {
+            ptx::tma_load_5d(a_dst, &tmA, full_bar(s), 0, st_tw * kStemTW, p.tap_par[tap],
+                             st_th * kStemTH + p.tap_off[tap], st_n);
+          }
+          ptx::tma_load_2d(b_dst, &tmB, full_bar(s), kb * kBlockK, n_tile * BLOCK_N);
+          if (++cb == p.c_blocks) { cb = 0; ++tap; }
+          if (++s == kStages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    constexpr uint32_t idesc = make_idesc(kBlockM, BLOCK_N);
+    int s = 0, as = 0;
+    uint32_t ph = 0, aph = 0;
+    bool alive = true;
+    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+      // epilogue has drained this accumulator
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile)) break;
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
+      for (int kb = 0; kb < k_blocks; ++kb) {
+        if (!mbar_wait(full_bar(s), ph, 2, kb)) { alive = false; break; }   // TMA bytes landed
+        ptx::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = base + s * Cfg::STAGE_BYTES;
+          const uint64_t da = make_sw128_desc(a_addr);
+          const uint64_t db = make_sw128_desc(a_addr + Cfg::A_BYTES);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
+            ptx::umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                           (kb | k) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(empty_bar(s));                // smem slot free once these MMAs retire
+          if (kb == k_blocks - 1) ptx::umma_commit(tfull_bar(as));   // accumulator complete
+        }
+        __syncwarp();
+        if (++s == kStages) { s = 0; ph ^= 1u; }
+      }
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue ====================================
+    const int ew = warp - 4;                 // == warp % 4: TMEM lanes [32*ew, 32*ew+32)
+    const int row_in_tile = ew * 32 + lane;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int m_tile = tile / p.num_n_tiles;
+      const int n_tile = tile - m_tile * p.num_n_tiles;
+      const RowInfo ri = decode_row(p, m_tile, row_in_tile);
+      if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, v);
+        ptx::tmem_ld_wait();
+        if (ri.valid) {
+          const int col = n_tile * BLOCK_N + c0;
+          const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
+          const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
+          float y[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 s4 = __ldg(sc + j), b4 = __ldg(sh + j);
+            y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4.x, b4.x);
+            y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4.y, b4.y);
+            y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4.z, b4.z);
+            y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4.w, b4.w);
+          }
+          if (p.residual != nullptr) {
+            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + ri.res_row * p.ldc + col);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 rr = __ldg(rp + j);
+              const uint32_t w4[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                y[8 * j + 2 * e + 0] += __uint_as_float(w4[e] << 16);
+                y[8 * j + 2 * e + 1] += __uint_as_float(w4[e] & 0xffff0000u);
+              }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], 0.0f);
+          }
+          if (p.out_f32) {
+            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
+                                                   ri.dst_row * p.ldc + col);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              op[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+          } else {
+            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) +
+                                                 ri.dst_row * p.ldc + col);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              op[j] = make_uint4(pack_bf16x2(y[8 * j + 0], y[8 * j + 1]),
+                                 pack_bf16x2(y[8 * j + 2], y[8 * j + 3]),
+                                 pack_bf16x2(y[8 * j + 4], y[8 * j + 5]),
+                                 pack_bf16x2(y[8 * j + 6], y[8 * j + 7]));
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+// --------------------------------------------------------------------------------------- host
+template <int BLOCK_N, int MODE>
+static int configure_one() {
+  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_tc_kernel<BLOCK_N, MODE>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    TcCfg<BLOCK_N>::SMEM_BYTES));
+  return IDN_OK;
+}
+
+// Returns IDN_OK when no tcgen05 pipeline wait has timed out since the last call, else IDN_ECUDA
+// with the role / CTA / position of the first stalled wait in the error text.
+int read_tc_watchdog() {
+  unsigned int w[4] = {0, 0, 0, 0};
+  IDN_CUDA_TRY(cudaMemcpyFromSymbol(w, g_tc_watchdog, sizeof(w)));
+  if (w[0] != 0) {
+    unsigned int z[4] = {0, 0, 0, 0};
+    cudaMemcpyToSymbol(g_tc_watchdog, z, sizeof(z));
+    set_error("tcgen05 pipeline stalled: role " + std::to_string(w[1]) + " cta " +
+              std::to_string(w[2]) + " at " + std::to_string(w[3]));
+    return IDN_ECUDA;
+  }
+  return IDN_OK;
+}
+
+int conv_tc_configure() {
+  IDN_TRY((configure_one<64, MODE_FLAT>()));
+  IDN_TRY((configure_one<128, MODE_FLAT>()));
+  IDN_TRY((configure_one<192, MODE_FLAT>()));
+  IDN_TRY((configure_one<256, MODE_FLAT>()));
+  IDN_TRY((configure_one<64, MODE_STEM>()));
+  return IDN_OK;
+}
+
+template <int BLOCK_N, int MODE>
+static int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
+                      int num_sms, cudaStream_t st) {
+  const int total = p.num_m_tiles * p.num_n_tiles;
+  if (total <= 0) return IDN_OK;
+  const int grid = total < num_sms ? total : num_sms;
+  conv_tc_kernel<BLOCK_N, MODE><<<grid, 256, TcCfg<BLOCK_N>::SMEM_BYTES, st>>>(tmA, tmB, p);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
+int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int block_n,
+                   int num_sms, cudaStream_t st) {
+  if (p.n_total % block_n != 0 || p.num_n_tiles * block_n != p.n_total) {
+    set_error("launch_conv_tc: n_total is not a multiple of the N tile");
+    return IDN_EINVAL;
+  }
+  if (p.mode == MODE_STEM) {
+    if (block_n != 64) { set_error("launch_conv_tc: stem uses BLOCK_N=64"); return IDN_EINVAL; }
+    return launch_one<64, MODE_STEM>(tmA, tmB, p, num_sms, st);
+  }
+  switch (block_n) {
+    case 64: return launch_one<64, MODE_FLAT>(tmA, tmB, p, num_sms, st);
+    case 128: return launch_one<128, MODE_FLAT>(tmA, tmB, p, num_sms, st);
+    case 192: return launch_one<192, MODE_FLAT>(tmA, tmB, p, num_sms, st);
+    case 256: return launch_one<256, MODE_FLAT>(tmA, tmB, p, num_sms, st);
+  }
+  set_error("launch_conv_tc: unsupported N tile");
+  return IDN_EINVAL;
+}
+
+// cuTensorMapEncodeTiled comes from the driver; resolve it through the runtime so that the
+// library links against cudart only.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || ptr == nullptr) {
+      set_error(std::string("cuTensorMapEncodeTiled is not available from the driver: ") +
+                cudaGetErrorString(e));
+      return nullptr;
+    }
+    fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+int make_tmap_2d(CUtensorMap* tm, const void* base_ptr, uint64_t inner_elems, uint64_t rows,
+                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return IDN_ECUDA;
+  cuuint64_t gdim[2] = {inner_elems, rows};
+  cuuint64_t gstr[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base_ptr), gdim, gstr,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(2d) failed with CUresult " + std::to_string((int)r) +
+              " inner=" + std::to_string(inner_elems) + " rows=" + std::to_string(rows) +
+              " stride=" + std::to_string(row_stride_bytes) + " box=" + std::to_string(box_inner) +
+              "x" + std::to_string(box_rows));
+    return IDN_ECUDA;
+  }
+  return IDN_OK;
+}
+
+int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int conv_stride, int ws_px, int img_h,
+                   int ow, int nimg_cap) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return IDN_ECUDA;
+  const uint64_t px = 8;                                   // 4 bf16 channels
+  const uint64_t row = (uint64_t)ws_px * px;
+  cuuint64_t gdim[5] = {64, (cuuint64_t)ow, (cuuint64_t)conv_stride,
+                        (cuuint64_t)(img_h / conv_stride), (cuuint64_t)nimg_cap};
+  cuuint64_t gstr[4] = {(cuuint64_t)conv_stride * px, row, (cuuint64_t)conv_stride * row,
+                        (cuuint64_t)img_h * row};
+  cuuint32_t box[5] = {64, (cuuint32_t)kStemTW, 1, (cuuint32_t)kStemTH, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base_ptr), gdim, gstr,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(stem 5d, overlapping strides) failed with CUresult " +
+              std::to_string((int)r));
+    return IDN_ECUDA;
+  }
+  return IDN_OK;
+}
+
+}  // namespace idn

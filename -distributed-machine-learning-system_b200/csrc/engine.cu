@@ -1,0 +1,925 @@
+// Model plans (AlexNet, ResNet18), weight folding / re-layout, buffers and the C ABI.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <map>
+#include <memory>
+#include <tuple>
+#include <vector>
+
+#include "common.cuh"
+
+namespace idn {
+
+// ------------------------------------------------------------------------------ error plumbing
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+const char* last_error_cstr() { return g_last_error.c_str(); }
+
+// ------------------------------------------------------------------------------------ geometry
+struct Geom {            // flat padded NHWC geometry of one activation buffer
+  int H = 0, W = 0, Hp = 0, Wp = 0;
+  int img_rows() const { return Hp * Wp; }
+};
+static Geom make_geom(int h, int w, int pad) { Geom g; g.H = h; g.W = w; g.Hp = h + pad; g.Wp = w + pad; return g; }
+
+struct Act {             // a device activation buffer
+  bf16* ptr = nullptr;
+  Geom g;
+  int C = 0;
+  int planes = 1;        // 4 = parity planes of the geometry g
+  long long plane_rows = 0;   // rows per plane (= cap * img_rows)
+  long long rows() const { return plane_rows * planes; }
+};
+
+struct ConvWeights {     // device, kernel layout
+  bf16* wt = nullptr;    // [n_total][ktot] K-major
+  float* scale = nullptr;
+  float* shift = nullptr;
+  int n_total = 0, ktot = 0, taps = 0, c_blocks = 0;
+};
+
+enum StepKind { STEP_PRE = 0, STEP_CONV, STEP_POOL, STEP_RHEAD, STEP_SOFTMAX };
+
+struct Step {
+  StepKind kind;
+  std::string name;
+  // conv
+  CUtensorMap tmA, tmB;
+  ConvParams cp;
+  int block_n = 0;
+  // pool
+  PoolParams pp;
+  // what the step wrote (for idn_read_activation)
+  const void* out_ptr = nullptr;
+  int out_kind = 0;      // 0 none, 1 bf16 geom, 2 bf16 parity planes, 3 f32 rows (FC logits)
+  Geom out_g;            // for parity: geometry of one plane
+  int out_C = 0, out_ld = 0;
+  long long out_plane_rows = 0;
+  int out_H = 0, out_W = 0;   // logical image extent (parity: 2x plane extent)
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+}  // namespace idn
+
+using namespace idn;
+
+struct idn_engine {
+  int device = 0, model = 0, cap = 0, num_sms = 148, impl = IDN_IMPL_TC;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  std::vector<void*> dev_allocs;
+  std::vector<Step> steps;
+  // preprocess
+  PreMeta* d_meta = nullptr;
+  PreMeta* h_meta = nullptr;          // pinned
+  int* d_tables = nullptr;
+  size_t tables_cap = 0, tables_used = 0;   // int32 units
+  std::map<std::tuple<int, int, int>, int> table_index;
+  uint16_t* d_lut = nullptr;
+  void* xs = nullptr;                 // stem input image
+  int stem_left = 0, stem_ws = 232;
+  // io staging
+  uint8_t* d_imgs = nullptr; size_t d_imgs_cap = 0;
+  int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
+  // head
+  const bf16* head_act = nullptr; Geom head_g; int head_C = 0;
+  float* fc_w = nullptr; float* fc_b = nullptr;        // ResNet fp32 FC
+  float* logits_pad = nullptr;                         // AlexNet [cap][1024] fp32
+  int64_t launches = 0;
+  bool stem_simt = false;   // bring-up switch IDN_STEM_SIMT=1: run the two C=3 stem layers on the
+                            // CUDA-core kernel (explicit, never automatic)
+  bool timing = false;
+  int last_n = 0;
+};
+
+namespace idn {
+
+template <class T>
+static int dev_alloc(idn_engine* e, T** p, size_t count, bool zero = true) {
+  void* q = nullptr;
+  IDN_CUDA_TRY(cudaMalloc(&q, count * sizeof(T) + 256));
+  if (zero) IDN_CUDA_TRY(cudaMemset(q, 0, count * sizeof(T) + 256));
+  if (e) e->dev_allocs.push_back(q);
+  *p = reinterpret_cast<T*>(q);
+  return IDN_OK;
+}
+
+static int alloc_act(idn_engine* e, Act* a, Geom g, int C, int cap, int planes = 1) {
+  a->g = g; a->C = C; a->planes = planes;
+  a->plane_rows = (long long)cap * g.img_rows();
+  return dev_alloc(e, &a->ptr, (size_t)a->rows() * C);
+}
+
+static int pick_block_n(int n_total, long long m_tiles, int num_sms) {
+  const int cands[4] = {256, 192, 128, 64};
+  for (int c : cands)
+    if (n_total % c == 0 && m_tiles * (n_total / c) * 10 >= (long long)num_sms * 8) return c;
+  if (n_total % 128 == 0) return 128;
+  return 64;
+}
+
+// Uploads weights [cout][cin][R][S] (fp32, host) as bf16 [n_total][taps*cpad] with the tap-major /
+// channel-minor K order of the kernels, plus fp32 scale/shift padded to n_total.
+static int upload_conv_weights(idn_engine* e, ConvWeights* cw, const float* w, int cout, int cin,
+                               int R, int S, const float* scale, const float* shift) {
+  const int cpad = (cin + 63) / 64 * 64;
+  cw->taps = R * S; cw->c_blocks = cpad / 64; cw->ktot = R * S * cpad;
+  cw->n_total = (cout + 63) / 64 * 64;
+  std::vector<uint16_t> h((size_t)cw->n_total * cw->ktot, 0);
+  for (int n = 0; n < cout; ++n)
+    for (int c = 0; c < cin; ++c)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s)
+          h[(size_t)n * cw->ktot + (size_t)(r * S + s) * cpad + c] =
+              f32_to_bf16_bits(w[(((size_t)n * cin + c) * R + r) * S + s]);
+  IDN_TRY(dev_alloc(e, &cw->wt, h.size(), false));
+  IDN_CUDA_TRY(cudaMemcpy(cw->wt, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  std::vector<float> sc(cw->n_total, 0.0f), sh(cw->n_total, 0.0f);
+  for (int n = 0; n < cout; ++n) { sc[n] = scale ? scale[n] : 1.0f; sh[n] = shift ? shift[n] : 0.0f; }
+  IDN_TRY(dev_alloc(e, &cw->scale, sc.size(), false));
+  IDN_TRY(dev_alloc(e, &cw->shift, sh.size(), false));
+  IDN_CUDA_TRY(cudaMemcpy(cw->scale, sc.data(), sc.size() * 4, cudaMemcpyHostToDevice));
+  IDN_CUDA_TRY(cudaMemcpy(cw->shift, sh.data(), sh.size() * 4, cudaMemcpyHostToDevice));
+  return IDN_OK;
+}
+
+// Stem weights [64][3][R][S] -> [64][R*64]: k = r*64 + s*4 + c (window position s, channel c of the
+// 4-channel pixel); everything else zero.
+static int upload_stem_weights(idn_engine* e, ConvWeights* cw, const float* w, int cout, int R,
+                               int S, const float* scale, const float* shift) {
+  cw->taps = R; cw->c_blocks = 1; cw->ktot = R * 64; cw->n_total = 64;
+  if (cout != 64 || S * 4 > 64) { set_error("stem: unsupported shape"); return IDN_EINVAL; }
+  std::vector<uint16_t> h((size_t)64 * cw->ktot, 0);
+  for (int n = 0; n < cout; ++n)
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s)
+          h[(size_t)n * cw->ktot + r * 64 + s * 4 + c] =
+              f32_to_bf16_bits(w[(((size_t)n * 3 + c) * R + r) * S + s]);
+  IDN_TRY(dev_alloc(e, &cw->wt, h.size(), false));
+  IDN_CUDA_TRY(cudaMemcpy(cw->wt, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  std::vector<float> sc(64), sh(64);
+  for (int n = 0; n < 64; ++n) { sc[n] = scale ? scale[n] : 1.0f; sh[n] = shift ? shift[n] : 0.0f; }
+  IDN_TRY(dev_alloc(e, &cw->scale, 64, false));
+  IDN_TRY(dev_alloc(e, &cw->shift, 64, false));
+  IDN_CUDA_TRY(cudaMemcpy(cw->scale, sc.data(), 256, cudaMemcpyHostToDevice));
+  IDN_CUDA_TRY(cudaMemcpy(cw->shift, sh.data(), 256, cudaMemcpyHostToDevice));
+  return IDN_OK;
+}
+
+struct ConvSpec {
+  int R = 1, S = 1, stride = 1, pad = 0;
+  bool relu = false, out_f32 = false;
+};
+
+static void fill_dest(Step* st, const Act& dst, bool out_f32, int ldc) {
+  ConvParams& cp = st->cp;
+  cp.ldc = ldc;
+  cp.out = dst.ptr;
+  cp.out_f32 = out_f32 ? 1 : 0;
+  cp.d_img_rows = dst.g.img_rows();
+  cp.d_wp = dst.g.Wp;
+  cp.d_plane_rows = (int)dst.plane_rows;
+  cp.dest_mode = dst.planes == 4 ? DEST_PARITY : DEST_GEOM;
+  st->out_ptr = dst.ptr;
+  st->out_kind = out_f32 ? 3 : (dst.planes == 4 ? 2 : 1);
+  st->out_g = dst.g;
+  st->out_C = dst.C;
+  st->out_ld = ldc;
+  st->out_plane_rows = dst.plane_rows;
+  st->out_H = dst.planes == 4 ? dst.g.H * 2 : dst.g.H;
+  st->out_W = dst.planes == 4 ? dst.g.W * 2 : dst.g.W;
+}
+
+// Flat convolution step: src (geometry or parity planes) -> dst.  The M tiling runs over the
+// OUTPUT pixel grid, which for stride 1 is src.g and for stride 2 the plane geometry of src.
+static int add_conv(idn_engine* e, const std::string& name, const Act& src, const ConvWeights& cw,
+                    const ConvSpec& spec, const Act& dst, const Act* residual, int cap) {
+  Step st;
+  st.kind = STEP_CONV;
+  st.name = name;
+  ConvParams& cp = st.cp;
+  std::memset(&cp, 0, sizeof(cp));
+  const Geom& tg = src.g;                    // tile geometry (== plane geometry for stride 2)
+  cp.mode = MODE_FLAT;
+  cp.num_taps = cw.taps;
+  cp.c_blocks = cw.c_blocks;
+  if (cw.taps != spec.R * spec.S || cw.taps > kMaxTaps) { set_error(name + ": tap count"); return IDN_EINVAL; }
+  if (spec.stride == 1) {
+    if (src.planes != 1 || tg.Wp - tg.W < spec.pad || tg.Hp - tg.H < spec.pad) {
+      set_error(name + ": source layout lacks the zero padding this convolution needs");
+      return IDN_EINVAL;
+    }
+    for (int r = 0; r < spec.R; ++r)
+      for (int s = 0; s < spec.S; ++s)
+        cp.tap_off[r * spec.S + s] = (r - spec.pad) * tg.Wp + (s - spec.pad);
+  } else {
+    if (src.planes != 4 || !((spec.R == 3 && spec.S == 3 && spec.pad == 1) ||
+                             (spec.R == 1 && spec.S == 1 && spec.pad == 0))) {
+      set_error(name + ": stride-2 convolutions read parity planes (3x3 p1 or 1x1 p0)");
+      return IDN_EINVAL;
+    }
+    for (int r = 0; r < spec.R; ++r)
+      for (int s = 0; s < spec.S; ++s) {
+        int ph = 0, pw = 0, di = 0, dj = 0;
+        if (spec.R == 3) {                   // input row 2*oh + r - 1
+          ph = (r == 1) ? 0 : 1; di = (r == 0) ? -1 : 0;
+          pw = (s == 1) ? 0 : 1; dj = (s == 0) ? -1 : 0;
+        }
+        cp.tap_off[r * spec.S + s] = (int)((ph * 2 + pw) * src.plane_rows) + di * tg.Wp + dj;
+      }
+  }
+  cp.img_rows = tg.img_rows(); cp.wp = tg.Wp; cp.H = tg.H; cp.W = tg.W;
+  cp.n_total = cw.n_total;
+  cp.scale = cw.scale; cp.shift = cw.shift;
+  cp.relu = spec.relu ? 1 : 0;
+  cp.residual = residual ? residual->ptr : nullptr;
+  if (residual && (residual->g.img_rows() != tg.img_rows() || residual->g.Wp != tg.Wp ||
+                   residual->C != dst.C || residual->planes != 1)) {
+    set_error(name + ": residual geometry differs from the tile geometry");
+    return IDN_EINVAL;
+  }
+  fill_dest(&st, dst, spec.out_f32, dst.C);
+  if (dst.C != cw.n_total) { set_error(name + ": dst channels != padded Cout"); return IDN_EINVAL; }
+  cp.a_ptr = src.ptr; cp.b_ptr = cw.wt;
+  cp.a_rows = src.rows(); cp.a_ld = src.C; cp.ktot = cw.ktot;
+  if (src.C != cw.c_blocks * 64) { set_error(name + ": src channels != weight channels"); return IDN_EINVAL; }
+  const long long m_tiles_cap = ((long long)cap * tg.img_rows() + kBlockM - 1) / kBlockM;
+  st.block_n = pick_block_n(cw.n_total, m_tiles_cap, e->num_sms);
+  cp.num_n_tiles = cw.n_total / st.block_n;
+  IDN_TRY(make_tmap_2d(&st.tmA, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
+                       (uint64_t)src.C * 2, kBlockK, kBlockM));
+  IDN_TRY(make_tmap_2d(&st.tmB, cw.wt, (uint64_t)cw.ktot, (uint64_t)cw.n_total,
+                       (uint64_t)cw.ktot * 2, kBlockK, (uint32_t)st.block_n));
+  e->steps.push_back(st);
+  return IDN_OK;
+}
+
+static int add_stem(idn_engine* e, const std::string& name, const void* xs, int ws, int left_pad,
+                    const ConvWeights& cw, int R, int stride, int pad, int OH, int OW,
+                    const Act& dst, int cap) {
+  (void)left_pad;
+  Step st;
+  st.kind = STEP_CONV;
+  st.name = name;
+  ConvParams& cp = st.cp;
+  std::memset(&cp, 0, sizeof(cp));
+  cp.mode = MODE_STEM;
+  cp.num_taps = R; cp.c_blocks = 1;
+  for (int r = 0; r < R; ++r) {             // input row = stride*oh + r - pad = stride*(oh+a) + b
+    const int d = r - pad;
+    const int a = (int)std::floor((double)d / stride);
+    cp.tap_off[r] = a;
+    cp.tap_par[r] = d - a * stride;
+  }
+  cp.H = OH; cp.W = OW;
+  cp.tiles_w = (OW + kStemTW - 1) / kStemTW;
+  cp.tiles_h = (OH + kStemTH - 1) / kStemTH;
+  cp.n_total = 64; cp.num_n_tiles = 1;
+  cp.scale = cw.scale; cp.shift = cw.shift; cp.relu = 1;
+  fill_dest(&st, dst, false, 64);
+  cp.a_ptr = reinterpret_cast<const bf16*>(xs); cp.b_ptr = cw.wt; cp.ktot = cw.ktot;
+  cp.st_stride = stride; cp.st_ws = ws; cp.st_h = IDN_CROP; cp.st_ow = OW;
+  cp.st_nrow = IDN_CROP / stride;
+  st.block_n = 64;
+  if (!e->stem_simt) IDN_TRY(make_tmap_stem(&st.tmA, xs, stride, ws, IDN_CROP, OW, cap));
+  IDN_TRY(make_tmap_2d(&st.tmB, cw.wt, (uint64_t)cw.ktot, 64, (uint64_t)cw.ktot * 2, kBlockK, 64));
+  e->steps.push_back(st);
+  return IDN_OK;
+}
+
+static void add_pool(idn_engine* e, const std::string& name, const Act& src, const Act& dst, int pad) {
+  Step st;
+  st.kind = STEP_POOL;
+  st.name = name;
+  std::memset(&st.cp, 0, sizeof(st.cp));
+  PoolParams& pp = st.pp;
+  pp.in = src.ptr; pp.out = dst.ptr; pp.C = src.C; pp.nimg = 0;
+  pp.s_img_rows = src.g.img_rows(); pp.s_wp = src.g.Wp; pp.H = src.g.H; pp.W = src.g.W;
+  pp.d_img_rows = dst.g.img_rows(); pp.d_wp = dst.g.Wp; pp.OH = dst.g.H; pp.OW = dst.g.W;
+  pp.pad = pad;
+  st.out_ptr = dst.ptr; st.out_kind = 1; st.out_g = dst.g; st.out_C = dst.C; st.out_ld = dst.C;
+  st.out_plane_rows = dst.plane_rows; st.out_H = dst.g.H; st.out_W = dst.g.W;
+  e->steps.push_back(st);
+}
+
+// BatchNorm (eval, eps 1e-5) folded to scale/shift: tv:models/resnet.py:197,208-213
+static void fold_bn(const float* g, const float* b, const float* rm, const float* rv, int n,
+                    std::vector<float>* scale, std::vector<float>* shift) {
+  scale->resize(n); shift->resize(n);
+  for (int i = 0; i < n; ++i) {
+    const float s = g[i] / std::sqrt(rv[i] + 1e-5f);
+    (*scale)[i] = s;
+    (*shift)[i] = b[i] - rm[i] * s;
+  }
+}
+
+struct BlobReader {
+  const float* p; size_t left;
+  const float* take(size_t n) {
+    if (n > left) return nullptr;
+    const float* r = p; p += n; left -= n; return r;
+  }
+};
+
+static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
+  const int cap = e->cap;
+  BlobReader br{blob, count};
+  auto conv_bn = [&](ConvWeights* cw, int cout, int cin, int R, bool stem) -> int {
+    const float* w = br.take((size_t)cout * cin * R * R);
+    const float* g = br.take(cout); const float* b = br.take(cout);
+    const float* rm = br.take(cout); const float* rv = br.take(cout);
+    if (!w || !g || !b || !rm || !rv) { set_error("resnet18: weight blob too short"); return IDN_EWEIGHTS; }
+    std::vector<float> sc, sh;
+    fold_bn(g, b, rm, rv, cout, &sc, &sh);
+    if (stem) return upload_stem_weights(e, cw, w, cout, R, R, sc.data(), sh.data());
+    return upload_conv_weights(e, cw, w, cout, cin, R, R, sc.data(), sh.data());
+  };
+  // stem
+  e->stem_left = 3; e->stem_ws = 232;
+  bf16* xs = nullptr;
+  IDN_TRY(dev_alloc(e, &xs, (size_t)cap * IDN_CROP * e->stem_ws * 4 + 4096));
+  e->xs = xs;
+  { Step st; st.kind = STEP_PRE; st.name = "preprocess"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
+  ConvWeights w_stem;
+  IDN_TRY(conv_bn(&w_stem, 64, 3, 7, true));
+  Act s1; IDN_TRY(alloc_act(e, &s1, make_geom(112, 112, 0), 64, cap));
+  IDN_TRY(add_stem(e, "conv1+bn1+relu", xs, e->stem_ws, e->stem_left, w_stem, 7, 2, 3, 112, 112, s1, cap));
+  const int chans[4] = {64, 128, 256, 512};
+  const int sizes[4] = {56, 28, 14, 7};
+  Act a, t, o;       // block input, mid, block output (same geometry)
+  IDN_TRY(alloc_act(e, &a, make_geom(56, 56, 1), 64, cap));
+  add_pool(e, "maxpool", s1, a, 1);
+  Act planes;        // parity planes feeding the next stage
+  for (int li = 0; li < 4; ++li) {
+    const int C = chans[li];
+    const Geom g = make_geom(sizes[li], sizes[li], 1);
+    IDN_TRY(alloc_act(e, &t, g, C, cap));
+    IDN_TRY(alloc_act(e, &o, g, C, cap));
+    Act nextp;
+    const bool last = li == 3;
+    if (!last) IDN_TRY(alloc_act(e, &nextp, make_geom(sizes[li + 1], sizes[li + 1], 1), C, cap, 4));
+    const std::string L = "layer" + std::to_string(li + 1);
+    ConvSpec c3r; c3r.R = 3; c3r.S = 3; c3r.pad = 1; c3r.relu = true;
+    // ---- block 0
+    ConvWeights w1, w2, wd;
+    if (li == 0) {
+      IDN_TRY(conv_bn(&w1, C, C, 3, false));
+      IDN_TRY(add_conv(e, L + ".0.conv1", a, w1, c3r, t, nullptr, cap));
+      IDN_TRY(conv_bn(&w2, C, C, 3, false));
+      IDN_TRY(add_conv(e, L + ".0.conv2+add", t, w2, c3r, o, &a, cap));
+    } else {
+      Act d; IDN_TRY(alloc_act(e, &d, g, C, cap));
+      if (last) IDN_TRY(alloc_act(e, &a, g, C, cap));
+      ConvSpec s2 = c3r; s2.stride = 2;
+      IDN_TRY(conv_bn(&w1, C, chans[li - 1], 3, false));
+      IDN_TRY(add_conv(e, L + ".0.conv1", planes, w1, s2, t, nullptr, cap));
+      IDN_TRY(conv_bn(&w2, C, C, 3, false));
+      ConvSpec ds; ds.R = 1; ds.S = 1; ds.stride = 2; ds.pad = 0; ds.relu = false;
+      IDN_TRY(conv_bn(&wd, C, chans[li - 1], 1, false));
+      IDN_TRY(add_conv(e, L + ".0.downsample", planes, wd, ds, d, nullptr, cap));
+      IDN_TRY(add_conv(e, L + ".0.conv2+add", t, w2, c3r, o, &d, cap));
+    }
+    // ---- block 1: input o, output -> parity planes of the next stage (or `a` for the last)
+    ConvWeights w3, w4;
+    IDN_TRY(conv_bn(&w3, C, C, 3, false));
+    IDN_TRY(add_conv(e, L + ".1.conv1", o, w3, c3r, t, nullptr, cap));
+    IDN_TRY(conv_bn(&w4, C, C, 3, false));
+    if (!last) {
+      IDN_TRY(add_conv(e, L + ".1.conv2+add", t, w4, c3r, nextp, &o, cap));
+      planes = nextp;
+    } else {
+      IDN_TRY(add_conv(e, L + ".1.conv2+add", t, w4, c3r, a, &o, cap));
+      e->head_act = a.ptr; e->head_g = g; e->head_C = C;
+    }
+  }
+  const float* fw = br.take((size_t)1000 * 512);
+  const float* fb = br.take(1000);
+  if (!fw || !fb || br.left != 0) { set_error("resnet18: weight blob has the wrong size"); return IDN_EWEIGHTS; }
+  IDN_TRY(dev_alloc(e, &e->fc_w, (size_t)1000 * 512, false));
+  IDN_TRY(dev_alloc(e, &e->fc_b, 1000, false));
+  IDN_CUDA_TRY(cudaMemcpy(e->fc_w, fw, (size_t)1000 * 512 * 4, cudaMemcpyHostToDevice));
+  IDN_CUDA_TRY(cudaMemcpy(e->fc_b, fb, 4000, cudaMemcpyHostToDevice));
+  { Step st; st.kind = STEP_RHEAD; st.name = "avgpool+fc+softmax+top1"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
+  return IDN_OK;
+}
+
+static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
+  const int cap = e->cap;
+  BlobReader br{blob, count};
+  e->stem_left = 2; e->stem_ws = 232;
+  bf16* xs = nullptr;
+  IDN_TRY(dev_alloc(e, &xs, (size_t)cap * IDN_CROP * e->stem_ws * 4 + 4096));
+  e->xs = xs;
+  { Step st; st.kind = STEP_PRE; st.name = "preprocess"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
+  auto take2 = [&](size_t nw, size_t nb, const float** w, const float** b) -> int {
+    *w = br.take(nw); *b = br.take(nb);
+    if (!*w || !*b) { set_error("alexnet: weight blob too short"); return IDN_EWEIGHTS; }
+    return IDN_OK;
+  };
+  const float *w, *b;
+  // features.0: 11x11 s4 p2 (tv:models/alexnet.py:22)
+  ConvWeights w0;
+  IDN_TRY(take2((size_t)64 * 3 * 121, 64, &w, &b));
+  IDN_TRY(upload_stem_weights(e, &w0, w, 64, 11, 11, nullptr, b));
+  Act c1; IDN_TRY(alloc_act(e, &c1, make_geom(55, 55, 0), 64, cap));
+  IDN_TRY(add_stem(e, "features.0+relu", xs, e->stem_ws, e->stem_left, w0, 11, 4, 2, 55, 55, c1, cap));
+  Act p1; IDN_TRY(alloc_act(e, &p1, make_geom(27, 27, 2), 64, cap));
+  add_pool(e, "features.2 maxpool", c1, p1, 0);
+  // features.3: 5x5 p2, 64 -> 192
+  ConvWeights w3;
+  IDN_TRY(take2((size_t)192 * 64 * 25, 192, &w, &b));
+  IDN_TRY(upload_conv_weights(e, &w3, w, 192, 64, 5, 5, nullptr, b));
+  Act c2; IDN_TRY(alloc_act(e, &c2, make_geom(27, 27, 2), 192, cap));
+  ConvSpec s5; s5.R = 5; s5.S = 5; s5.pad = 2; s5.relu = true;
+  IDN_TRY(add_conv(e, "features.3+relu", p1, w3, s5, c2, nullptr, cap));
+  Act p2; IDN_TRY(alloc_act(e, &p2, make_geom(13, 13, 1), 192, cap));
+  add_pool(e, "features.5 maxpool", c2, p2, 0);
+  ConvSpec s3; s3.R = 3; s3.S = 3; s3.pad = 1; s3.relu = true;
+  ConvWeights w6, w8, w10;
+  IDN_TRY(take2((size_t)384 * 192 * 9, 384, &w, &b));
+  IDN_TRY(upload_conv_weights(e, &w6, w, 384, 192, 3, 3, nullptr, b));
+  Act c3; IDN_TRY(alloc_act(e, &c3, make_geom(13, 13, 1), 384, cap));
+  IDN_TRY(add_conv(e, "features.6+relu", p2, w6, s3, c3, nullptr, cap));
+  IDN_TRY(take2((size_t)256 * 384 * 9, 256, &w, &b));
+  IDN_TRY(upload_conv_weights(e, &w8, w, 256, 384, 3, 3, nullptr, b));
+  Act c4; IDN_TRY(alloc_act(e, &c4, make_geom(13, 13, 1), 256, cap));
+  IDN_TRY(add_conv(e, "features.8+relu", c3, w8, s3, c4, nullptr, cap));
+  IDN_TRY(take2((size_t)256 * 256 * 9, 256, &w, &b));
+  IDN_TRY(upload_conv_weights(e, &w10, w, 256, 256, 3, 3, nullptr, b));
+  Act c5; IDN_TRY(alloc_act(e, &c5, make_geom(13, 13, 1), 256, cap));
+  IDN_TRY(add_conv(e, "features.10+relu", c4, w10, s3, c5, nullptr, cap));
+  Act p3; IDN_TRY(alloc_act(e, &p3, make_geom(6, 6, 0), 256, cap));
+  add_pool(e, "features.12 maxpool", c5, p3, 0);
+  // classifier: the flatten order of torch.flatten(x, 1) on [B,256,6,6] is (c, h, w)
+  // (tv:models/alexnet.py:50); activations here are (h, w, c), so FC6's columns are permuted once.
+  IDN_TRY(take2((size_t)4096 * 9216, 4096, &w, &b));
+  ConvWeights f6, f7, f8;
+  {
+    std::vector<float> wp((size_t)4096 * 9216);
+    for (int n = 0; n < 4096; ++n)
+      for (int c = 0; c < 256; ++c)
+        for (int hw = 0; hw < 36; ++hw)
+          wp[(size_t)n * 9216 + (size_t)hw * 256 + c] = w[(size_t)n * 9216 + (size_t)c * 36 + hw];
+    IDN_TRY(upload_conv_weights(e, &f6, wp.data(), 4096, 9216, 1, 1, nullptr, b));
+  }
+  Act x6; x6.ptr = p3.ptr; x6.g = make_geom(1, 1, 0); x6.C = 9216; x6.planes = 1; x6.plane_rows = cap;
+  Act y6; IDN_TRY(alloc_act(e, &y6, make_geom(1, 1, 0), 4096, cap));
+  ConvSpec fc; fc.relu = true;
+  IDN_TRY(add_conv(e, "classifier.1+relu", x6, f6, fc, y6, nullptr, cap));
+  IDN_TRY(take2((size_t)4096 * 4096, 4096, &w, &b));
+  IDN_TRY(upload_conv_weights(e, &f7, w, 4096, 4096, 1, 1, nullptr, b));
+  Act y7; IDN_TRY(alloc_act(e, &y7, make_geom(1, 1, 0), 4096, cap));
+  IDN_TRY(add_conv(e, "classifier.4+relu", y6, f7, fc, y7, nullptr, cap));
+  IDN_TRY(take2((size_t)1000 * 4096, 1000, &w, &b));
+  if (br.left != 0) { set_error("alexnet: weight blob has the wrong size"); return IDN_EWEIGHTS; }
+  IDN_TRY(upload_conv_weights(e, &f8, w, 1000, 4096, 1, 1, nullptr, b));   // n_total = 1024
+  IDN_TRY(dev_alloc(e, &e->logits_pad, (size_t)cap * 1024));
+  Act y8; y8.ptr = reinterpret_cast<bf16*>(e->logits_pad); y8.g = make_geom(1, 1, 0); y8.C = 1024;
+  y8.planes = 1; y8.plane_rows = cap;
+  ConvSpec fc8; fc8.relu = false; fc8.out_f32 = true;
+  IDN_TRY(add_conv(e, "classifier.6", y7, f8, fc8, y8, nullptr, cap));
+  { Step st; st.kind = STEP_SOFTMAX; st.name = "softmax+top1"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
+  return IDN_OK;
+}
+
+// ------------------------------------------------------------------------------- preprocess io
+static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int* off) {
+  auto key = std::make_tuple(in_size, out_size, crop);
+  auto it = e->table_index.find(key);
+  if (it != e->table_index.end()) { *off = it->second; return IDN_OK; }
+  std::string bytes;
+  build_axis_table(in_size, out_size, crop, &bytes);
+  const size_t n = bytes.size() / 4;
+  if (e->tables_used + n > e->tables_cap) {
+    const size_t ncap = std::max(e->tables_cap * 2, e->tables_used + n + (1u << 16));
+    int* nt = nullptr;
+    IDN_CUDA_TRY(cudaMalloc(&nt, ncap * 4));
+    if (e->d_tables) {
+      IDN_CUDA_TRY(cudaStreamSynchronize(e->stream));
+      IDN_CUDA_TRY(cudaMemcpy(nt, e->d_tables, e->tables_used * 4, cudaMemcpyDeviceToDevice));
+      cudaFree(e->d_tables);
+    }
+    e->d_tables = nt; e->tables_cap = ncap;
+  }
+  IDN_CUDA_TRY(cudaMemcpyAsync(e->d_tables + e->tables_used, bytes.data(), bytes.size(),
+                               cudaMemcpyHostToDevice, e->stream));
+  IDN_CUDA_TRY(cudaStreamSynchronize(e->stream));   // `bytes` is a temporary
+  *off = (int)e->tables_used;
+  e->table_index[key] = *off;
+  e->tables_used += n;
+  return IDN_OK;
+}
+
+static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, int n, int64_t base) {
+  for (int i = 0; i < n; ++i) {
+    const int H = hw[2 * i], W = hw[2 * i + 1];
+    if (H <= 0 || W <= 0) { set_error("image with non-positive size"); return IDN_EINVAL; }
+    int nh, nw;
+    resized_size(H, W, &nh, &nw);
+    PreMeta& m = e->h_meta[i];
+    m.offset = offsets[i] - base; m.H = H; m.W = W;
+    IDN_TRY(ensure_table(e, W, nw, crop_offset(nw), &m.htab));
+    IDN_TRY(ensure_table(e, H, nh, crop_offset(nh), &m.vtab));
+  }
+  IDN_CUDA_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, sizeof(PreMeta) * n, cudaMemcpyHostToDevice,
+                               e->stream));
+  return IDN_OK;
+}
+
+// --------------------------------------------------------------------------------- forward pass
+static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx, float* d_prob,
+                    float* d_logits) {
+  cudaStream_t st = e->stream;
+  e->last_n = n;
+  for (Step& s : e->steps) {
+    if (e->timing) {
+      if (!s.ev0) { IDN_CUDA_TRY(cudaEventCreate(&s.ev0)); IDN_CUDA_TRY(cudaEventCreate(&s.ev1)); }
+      IDN_CUDA_TRY(cudaEventRecord(s.ev0, st));
+    }
+    switch (s.kind) {
+      case STEP_PRE:
+        IDN_TRY(launch_preprocess(d_imgs, e->d_meta, e->d_tables, e->d_lut, n, PRE_OUT_STEM, e->xs,
+                                  e->stem_left, e->stem_ws, st));
+        break;
+      case STEP_CONV: {
+        ConvParams& cp = s.cp;
+        cp.nimg = n;
+        cp.num_m_tiles = cp.mode == MODE_STEM
+                             ? n * cp.tiles_w * cp.tiles_h
+                             : (int)(((long long)n * cp.img_rows + kBlockM - 1) / kBlockM);
+        if (e->impl == IDN_IMPL_TC && !(cp.mode == MODE_STEM && e->stem_simt))
+          IDN_TRY(launch_conv_tc(s.tmA, s.tmB, cp, s.block_n, e->num_sms, st));
+        else IDN_TRY(launch_conv_simt(cp, st));
+        break;
+      }
+      case STEP_POOL:
+        s.pp.nimg = n;
+        IDN_TRY(launch_maxpool(s.pp, st));
+        break;
+      case STEP_RHEAD:
+        IDN_TRY(launch_resnet_head(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,
+                                   e->head_g.W, e->head_C, e->fc_w, e->fc_b, d_logits, d_idx,
+                                   d_prob, st));
+        break;
+      case STEP_SOFTMAX:
+        IDN_TRY(launch_softmax_top1(e->logits_pad, 1024, n, d_logits, d_idx, d_prob, st));
+        break;
+    }
+    e->launches += 1;
+    if (e->timing) IDN_CUDA_TRY(cudaEventRecord(s.ev1, st));
+  }
+  return IDN_OK;
+}
+
+static int check_device(int device) {
+  int count = 0;
+  cudaError_t err = cudaGetDeviceCount(&count);
+  if (err != cudaSuccess || count <= 0) {
+    set_error(std::string("no CUDA device: ") + cudaGetErrorString(err) +
+              " -- idunno_b200 has no CPU fallback");
+    return IDN_ENODEV;
+  }
+  if (device < 0 || device >= count) { set_error("device index out of range"); return IDN_EINVAL; }
+  cudaDeviceProp prop;
+  IDN_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) {
+    set_error(std::string("device ") + prop.name + " is sm_" + std::to_string(prop.major) +
+              std::to_string(prop.minor) + "; this library is built for sm_100a only");
+    return IDN_ENODEV;
+  }
+  IDN_CUDA_TRY(cudaSetDevice(device));
+  return IDN_OK;
+}
+
+}  // namespace idn
+
+// ========================================================================================= C ABI
+extern "C" {
+
+const char* idn_last_error(void) { return idn::last_error_cstr(); }
+const char* idn_version(void) { return "idunno_b200 0.1 sm_100a"; }
+
+int64_t idn_weight_count(int model_id) {
+  if (model_id == IDN_MODEL_ALEXNET) return 61100840LL;
+  if (model_id == IDN_MODEL_RESNET18) return 11699112LL;
+  return -1;
+}
+
+int idn_destroy(idn_handle h) {
+  if (!h) return IDN_OK;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  for (void* p : h->dev_allocs) cudaFree(p);
+  if (h->d_tables) cudaFree(h->d_tables);
+  if (h->d_imgs) cudaFree(h->d_imgs);
+  if (h->h_meta) cudaFreeHost(h->h_meta);
+  for (Step& s : h->steps) { if (s.ev0) cudaEventDestroy(s.ev0); if (s.ev1) cudaEventDestroy(s.ev1); }
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+  return IDN_OK;
+}
+
+int idn_create(int device, int model_id, const void* weights_blob, size_t n_bytes, int max_batch,
+               idn_handle* out) {
+  if (!out || !weights_blob || max_batch <= 0 || max_batch > 8192 ||
+      (model_id != IDN_MODEL_ALEXNET && model_id != IDN_MODEL_RESNET18)) {
+    set_error("idn_create: bad argument");
+    return IDN_EINVAL;
+  }
+  *out = nullptr;
+  if ((int64_t)n_bytes != idn_weight_count(model_id) * 4) {
+    set_error("idn_create: weight blob is " + std::to_string(n_bytes) + " bytes, expected " +
+              std::to_string(idn_weight_count(model_id) * 4));
+    return IDN_EWEIGHTS;
+  }
+  IDN_TRY(check_device(device));
+  std::unique_ptr<idn_engine> e(new idn_engine());
+  e->device = device; e->model = model_id; e->cap = max_batch;
+  { const char* v = std::getenv("IDN_STEM_SIMT"); e->stem_simt = v && v[0] == '1'; }
+  int rc = IDN_OK;
+  auto fail = [&](int code) { idn_engine* raw = e.release(); idn_destroy(raw); return code; };
+  {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount;
+  }
+  if (cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    set_error("cudaStreamCreate failed"); return fail(IDN_ECUDA);
+  }
+  e->stream = e->own_stream;
+  if ((rc = conv_tc_configure()) != IDN_OK) return fail(rc);
+  if ((rc = dev_alloc(e.get(), &e->d_meta, (size_t)max_batch)) != IDN_OK) return fail(rc);
+  if (cudaMallocHost(&e->h_meta, sizeof(PreMeta) * max_batch) != cudaSuccess) {
+    set_error("cudaMallocHost failed"); return fail(IDN_ENOMEM);
+  }
+  uint16_t lut[768];
+  build_norm_lut(lut);
+  if ((rc = dev_alloc(e.get(), &e->d_lut, 768)) != IDN_OK) return fail(rc);
+  if (cudaMemcpy(e->d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice) != cudaSuccess) {
+    set_error("lut upload failed"); return fail(IDN_ECUDA);
+  }
+  if ((rc = dev_alloc(e.get(), &e->d_idx, (size_t)max_batch)) != IDN_OK) return fail(rc);
+  if ((rc = dev_alloc(e.get(), &e->d_prob, (size_t)max_batch)) != IDN_OK) return fail(rc);
+  if ((rc = dev_alloc(e.get(), &e->d_logits, (size_t)max_batch * IDN_NUM_CLASSES)) != IDN_OK) return fail(rc);
+  const float* blob = reinterpret_cast<const float*>(weights_blob);
+  rc = model_id == IDN_MODEL_ALEXNET ? build_alexnet(e.get(), blob, n_bytes / 4)
+                                     : build_resnet18(e.get(), blob, n_bytes / 4);
+  if (rc != IDN_OK) return fail(rc);
+  if (cudaDeviceSynchronize() != cudaSuccess) { set_error("sync after build failed"); return fail(IDN_ECUDA); }
+  *out = e.release();
+  return IDN_OK;
+}
+
+int idn_set_stream(idn_handle h, void* cuda_stream) {
+  if (!h) return IDN_EINVAL;
+  h->stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : h->own_stream;
+  return IDN_OK;
+}
+
+int idn_set_impl(idn_handle h, int impl) {
+  if (!h || (impl != IDN_IMPL_TC && impl != IDN_IMPL_SIMT)) { set_error("bad impl"); return IDN_EINVAL; }
+  h->impl = impl;
+  return IDN_OK;
+}
+
+int idn_sync(idn_handle h) {
+  if (!h) return IDN_EINVAL;
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return read_tc_watchdog();
+}
+
+int idn_infer_u8hwc_device(idn_handle h, const uint8_t* d_imgs, const int64_t* offsets,
+                           const int32_t* hw, int n, int32_t* d_idx, float* d_prob, float* d_logits) {
+  if (!h || !d_imgs || !offsets || !hw || !d_idx || !d_prob || n < 0 || n > h->cap) {
+    set_error("idn_infer_u8hwc_device: bad argument (n must be <= max_batch)");
+    return IDN_EINVAL;
+  }
+  if (n == 0) return IDN_OK;
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  IDN_TRY(fill_meta(h, offsets, hw, n, 0));
+  return run_plan(h, d_imgs, n, d_idx, d_prob, d_logits);
+}
+
+int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, const int32_t* hw,
+                    int n, int32_t* top1_idx, float* top1_prob, float* logits) {
+  if (!h || !imgs || !offsets || !hw || !top1_idx || !top1_prob || n < 0) {
+    set_error("idn_infer_u8hwc: bad argument");
+    return IDN_EINVAL;
+  }
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  for (int i0 = 0; i0 < n; i0 += h->cap) {
+    const int m = std::min(h->cap, n - i0);
+    int64_t lo = offsets[i0], hi = 0;
+    for (int i = i0; i < i0 + m; ++i) {
+      lo = std::min(lo, offsets[i]);
+      hi = std::max(hi, offsets[i] + (int64_t)hw[2 * i] * hw[2 * i + 1] * 3);
+    }
+    const size_t bytes = (size_t)(hi - lo);
+    if (bytes + 64 > h->d_imgs_cap) {
+      IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));
+      if (h->d_imgs) cudaFree(h->d_imgs);
+      h->d_imgs = nullptr; h->d_imgs_cap = 0;
+      IDN_CUDA_TRY(cudaMalloc(&h->d_imgs, bytes + 64));
+      h->d_imgs_cap = bytes + 64;
+    }
+    IDN_CUDA_TRY(cudaMemcpyAsync(h->d_imgs, imgs + lo, bytes, cudaMemcpyHostToDevice, h->stream));
+    IDN_TRY(fill_meta(h, offsets + i0, hw + 2 * i0, m, lo));
+    IDN_TRY(run_plan(h, h->d_imgs, m, h->d_idx, h->d_prob, logits ? h->d_logits : nullptr));
+    IDN_CUDA_TRY(cudaMemcpyAsync(top1_idx + i0, h->d_idx, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, h->stream));
+    IDN_CUDA_TRY(cudaMemcpyAsync(top1_prob + i0, h->d_prob, sizeof(float) * m, cudaMemcpyDeviceToHost, h->stream));
+    if (logits)
+      IDN_CUDA_TRY(cudaMemcpyAsync(logits + (size_t)i0 * IDN_NUM_CLASSES, h->d_logits,
+                                   sizeof(float) * m * IDN_NUM_CLASSES, cudaMemcpyDeviceToHost, h->stream));
+    IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));   // h_meta / staging are reused by the next chunk
+    IDN_TRY(read_tc_watchdog());
+  }
+  return IDN_OK;
+}
+
+int idn_preprocess_u8hwc(int device, const uint8_t* imgs, const int64_t* offsets, const int32_t* hw,
+                         int n, uint16_t* out) {
+  if (!imgs || !offsets || !hw || !out || n < 0) { set_error("idn_preprocess_u8hwc: bad argument"); return IDN_EINVAL; }
+  if (n == 0) return IDN_OK;
+  IDN_TRY(check_device(device));
+  idn_engine tmp;                       // borrows the table cache / meta plumbing of a handle
+  tmp.device = device; tmp.cap = n;
+  int rc = IDN_OK;
+  uint8_t* d_in = nullptr; uint16_t* d_out = nullptr;
+  auto cleanup = [&]() {
+    for (void* p : tmp.dev_allocs) cudaFree(p);
+    if (tmp.d_tables) cudaFree(tmp.d_tables);
+    if (tmp.h_meta) cudaFreeHost(tmp.h_meta);
+    if (d_in) cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+  };
+  int64_t hi = 0;
+  for (int i = 0; i < n; ++i) hi = std::max(hi, offsets[i] + (int64_t)hw[2 * i] * hw[2 * i + 1] * 3);
+  uint16_t lut[768];
+  build_norm_lut(lut);
+  const size_t out_elems = (size_t)n * 3 * IDN_CROP * IDN_CROP;
+  if (cudaMalloc(&d_in, hi + 64) != cudaSuccess || cudaMalloc(&d_out, out_elems * 2) != cudaSuccess ||
+      cudaMallocHost(&tmp.h_meta, sizeof(PreMeta) * n) != cudaSuccess) {
+    set_error("idn_preprocess_u8hwc: allocation failed"); cleanup(); return IDN_ENOMEM;
+  }
+  if ((rc = dev_alloc(&tmp, &tmp.d_meta, (size_t)n)) != IDN_OK) { cleanup(); return rc; }
+  if ((rc = dev_alloc(&tmp, &tmp.d_lut, 768)) != IDN_OK) { cleanup(); return rc; }
+  cudaMemcpy(tmp.d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice);
+  cudaMemcpy(d_in, imgs, hi, cudaMemcpyHostToDevice);
+  rc = fill_meta(&tmp, offsets, hw, n, 0);
+  if (rc == IDN_OK) rc = launch_preprocess(d_in, tmp.d_meta, tmp.d_tables, tmp.d_lut, n, PRE_OUT_NCHW, d_out, 0, 0, nullptr);
+  if (rc == IDN_OK && cudaDeviceSynchronize() != cudaSuccess) { set_error("preprocess kernel failed"); rc = IDN_ECUDA; }
+  if (rc == IDN_OK && cudaMemcpy(out, d_out, out_elems * 2, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("preprocess D2H failed"); rc = IDN_ECUDA;
+  }
+  cleanup();
+  return rc;
+}
+
+int idn_num_steps(idn_handle h) { return h ? (int)h->steps.size() : IDN_EINVAL; }
+
+int idn_step_info(idn_handle h, int step, char* name, int name_len, int32_t* chw) {
+  if (!h || step < 0 || step >= (int)h->steps.size()) { set_error("bad step"); return IDN_EINVAL; }
+  const Step& s = h->steps[step];
+  if (name && name_len > 0) { std::snprintf(name, name_len, "%s", s.name.c_str()); }
+  if (chw) {
+    if (s.out_kind == 0) { chw[0] = chw[1] = chw[2] = 0; }
+    else if (s.out_kind == 3) { chw[0] = IDN_NUM_CLASSES; chw[1] = 1; chw[2] = 1; }
+    else { chw[0] = s.out_C; chw[1] = s.out_H; chw[2] = s.out_W; }
+  }
+  return IDN_OK;
+}
+
+int idn_read_activation(idn_handle h, int step, int n, float* out) {
+  if (!h || !out || step < 0 || step >= (int)h->steps.size() || n <= 0 || n > h->cap) { set_error("bad argument"); return IDN_EINVAL; }
+  const Step& s = h->steps[step];
+  if (s.out_kind == 0) { set_error("step has no image-shaped output"); return IDN_EINVAL; }
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));
+  if (s.out_kind == 3) {
+    std::vector<float> tmp((size_t)n * s.out_ld);
+    IDN_CUDA_TRY(cudaMemcpy(tmp.data(), s.out_ptr, tmp.size() * 4, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; ++i)
+      for (int c = 0; c < IDN_NUM_CLASSES; ++c) out[(size_t)i * IDN_NUM_CLASSES + c] = tmp[(size_t)i * s.out_ld + c];
+    return IDN_OK;
+  }
+  const int planes = s.out_kind == 2 ? 4 : 1;
+  const size_t rows = (size_t)s.out_plane_rows * planes;
+  std::vector<uint16_t> tmp(rows * s.out_ld);
+  IDN_CUDA_TRY(cudaMemcpy(tmp.data(), s.out_ptr, tmp.size() * 2, cudaMemcpyDeviceToHost));
+  const int C = s.out_C, H = s.out_H, W = s.out_W;
+  for (int i = 0; i < n; ++i)
+    for (int y = 0; y < H; ++y)
+      for (int x = 0; x < W; ++x) {
+        size_t row;
+        if (planes == 1) row = (size_t)i * s.out_g.img_rows() + (size_t)y * s.out_g.Wp + x;
+        else row = (size_t)((y & 1) * 2 + (x & 1)) * s.out_plane_rows + (size_t)i * s.out_g.img_rows() +
+                   (size_t)(y >> 1) * s.out_g.Wp + (x >> 1);
+        const uint16_t* src = tmp.data() + row * s.out_ld;
+        for (int c = 0; c < C; ++c)
+          out[(((size_t)i * C + c) * H + y) * W + x] = bf16_bits_to_f32(src[c]);
+      }
+  return IDN_OK;
+}
+
+int64_t idn_kernel_launches(idn_handle h) { return h ? h->launches : -1; }
+
+int idn_set_timing(idn_handle h, int on) { if (!h) return IDN_EINVAL; h->timing = on != 0; return IDN_OK; }
+
+int idn_step_time_ms(idn_handle h, int step, float* ms) {
+  if (!h || !ms || step < 0 || step >= (int)h->steps.size()) { set_error("bad step"); return IDN_EINVAL; }
+  const Step& s = h->steps[step];
+  if (!s.ev0 || !s.ev1) { set_error("timing was not enabled for the last pass"); return IDN_EINVAL; }
+  IDN_CUDA_TRY(cudaEventSynchronize(s.ev1));
+  IDN_CUDA_TRY(cudaEventElapsedTime(ms, s.ev0, s.ev1));
+  return IDN_OK;
+}
+
+// ---------------------------------------------------------------- stand-alone layer (tests only)
+int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h, int w,
+                    const float* wgt, int cout, int r, int s, int stride, int pad,
+                    const float* scale, const float* shift, const float* residual, int relu,
+                    float* y) {
+  if (!x || !wgt || !y || n <= 0 || r != s) { set_error("idn_conv2d_nchw: bad argument"); return IDN_EINVAL; }
+  IDN_TRY(check_device(device));
+  std::unique_ptr<idn_engine> e(new idn_engine());
+  e->device = device; e->cap = n; e->impl = impl;
+  { cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) e->num_sms = prop.multiProcessorCount; }
+  int rc = IDN_OK;
+  auto done = [&](int code) { idn_engine* raw = e.release(); idn_destroy(raw); return code; };
+  if (cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("stream"); return done(IDN_ECUDA); }
+  e->stream = e->own_stream;
+  if ((rc = conv_tc_configure()) != IDN_OK) return done(rc);
+  const int oh = (h + 2 * pad - r) / stride + 1, ow = (w + 2 * pad - s) / stride + 1;
+  Act dst;
+  std::vector<uint16_t> hbuf;
+  if (cin == 3) {
+    // stem path: x must be [n][3][224][224]
+    if (h != IDN_CROP || w != IDN_CROP || cout != 64 || !((r == 7 && stride == 2 && pad == 3) || (r == 11 && stride == 4 && pad == 2))) {
+      set_error("idn_conv2d_nchw: cin=3 supports the two stem shapes only"); return done(IDN_EINVAL);
+    }
+    const int ws = 232, left = pad;
+    bf16* xs = nullptr;
+    if ((rc = dev_alloc(e.get(), &xs, (size_t)n * IDN_CROP * ws * 4 + 4096)) != IDN_OK) return done(rc);
+    hbuf.assign((size_t)n * IDN_CROP * ws * 4, 0);
+    for (int i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) for (int yy = 0; yy < h; ++yy) for (int xx = 0; xx < w; ++xx)
+      hbuf[(((size_t)i * IDN_CROP + yy) * ws + left + xx) * 4 + c] = f32_to_bf16_bits(x[(((size_t)i * 3 + c) * h + yy) * w + xx]);
+    cudaMemcpy(xs, hbuf.data(), hbuf.size() * 2, cudaMemcpyHostToDevice);
+    ConvWeights cw;
+    if ((rc = upload_stem_weights(e.get(), &cw, wgt, cout, r, s, scale, shift)) != IDN_OK) return done(rc);
+    if ((rc = alloc_act(e.get(), &dst, make_geom(oh, ow, 0), 64, n)) != IDN_OK) return done(rc);
+    if ((rc = add_stem(e.get(), "stem", xs, ws, left, cw, r, stride, pad, oh, ow, dst, n)) != IDN_OK) return done(rc);
+    e->steps.back().cp.relu = relu;
+  } else {
+    if (cin % 64 != 0 || cout % 64 != 0) { set_error("idn_conv2d_nchw: cin/cout must be multiples of 64"); return done(IDN_EINVAL); }
+    Act src;
+    if (stride == 1) {
+      if (2 * pad != r - 1) { set_error("idn_conv2d_nchw: stride 1 needs 'same' padding"); return done(IDN_EINVAL); }
+      if ((rc = alloc_act(e.get(), &src, make_geom(h, w, pad), cin, n)) != IDN_OK) return done(rc);
+      hbuf.assign((size_t)src.rows() * cin, 0);
+      for (int i = 0; i < n; ++i) for (int c = 0; c < cin; ++c) for (int yy = 0; yy < h; ++yy) for (int xx = 0; xx < w; ++xx)
+        hbuf[((size_t)i * src.g.img_rows() + (size_t)yy * src.g.Wp + xx) * cin + c] = f32_to_bf16_bits(x[(((size_t)i * cin + c) * h + yy) * w + xx]);
+      if ((rc = alloc_act(e.get(), &dst, src.g, cout, n)) != IDN_OK) return done(rc);
+    } else {
+      if (stride != 2 || (h & 1) || (w & 1)) { set_error("idn_conv2d_nchw: stride 2 needs even H, W"); return done(IDN_EINVAL); }
+      if ((rc = alloc_act(e.get(), &src, make_geom(h / 2, w / 2, 1), cin, n, 4)) != IDN_OK) return done(rc);
+      hbuf.assign((size_t)src.rows() * cin, 0);
+      for (int i = 0; i < n; ++i) for (int c = 0; c < cin; ++c) for (int yy = 0; yy < h; ++yy) for (int xx = 0; xx < w; ++xx) {
+        const size_t row = (size_t)((yy & 1) * 2 + (xx & 1)) * src.plane_rows + (size_t)i * src.g.img_rows() + (size_t)(yy >> 1) * src.g.Wp + (xx >> 1);
+        hbuf[row * cin + c] = f32_to_bf16_bits(x[(((size_t)i * cin + c) * h + yy) * w + xx]);
+      }
+      if ((rc = alloc_act(e.get(), &dst, make_geom(oh, ow, 1), cout, n)) != IDN_OK) return done(rc);
+      if (oh != h / 2 || ow != w / 2) { set_error("idn_conv2d_nchw: unsupported stride-2 shape"); return done(IDN_EINVAL); }
+    }
+    cudaMemcpy(src.ptr, hbuf.data(), hbuf.size() * 2, cudaMemcpyHostToDevice);
+    ConvWeights cw;
+    if ((rc = upload_conv_weights(e.get(), &cw, wgt, cout, cin, r, s, scale, shift)) != IDN_OK) return done(rc);
+    Act res; Act* resp = nullptr;
+    if (residual) {
+      if ((rc = alloc_act(e.get(), &res, dst.g, cout, n)) != IDN_OK) return done(rc);
+      std::vector<uint16_t> rb((size_t)res.rows() * cout, 0);
+      for (int i = 0; i < n; ++i) for (int c = 0; c < cout; ++c) for (int yy = 0; yy < oh; ++yy) for (int xx = 0; xx < ow; ++xx)
+        rb[((size_t)i * res.g.img_rows() + (size_t)yy * res.g.Wp + xx) * cout + c] = f32_to_bf16_bits(residual[(((size_t)i * cout + c) * oh + yy) * ow + xx]);
+      cudaMemcpy(res.ptr, rb.data(), rb.size() * 2, cudaMemcpyHostToDevice);
+      resp = &res;
+    }
+    ConvSpec spec; spec.R = r; spec.S = s; spec.stride = stride; spec.pad = pad; spec.relu = relu != 0;
+    if ((rc = add_conv(e.get(), "conv", src, cw, spec, dst, resp, n)) != IDN_OK) return done(rc);
+  }
+  Step& st = e->steps.back();
+  st.cp.nimg = n;
+  st.cp.num_m_tiles = st.cp.mode == MODE_STEM ? n * st.cp.tiles_w * st.cp.tiles_h
+                                              : (int)(((long long)n * st.cp.img_rows + kBlockM - 1) / kBlockM);
+  rc = impl == IDN_IMPL_TC ? launch_conv_tc(st.tmA, st.tmB, st.cp, st.block_n, e->num_sms, e->stream)
+                           : launch_conv_simt(st.cp, e->stream);
+  if (rc != IDN_OK) return done(rc);
+  if (cudaStreamSynchronize(e->stream) != cudaSuccess) {
+    set_error(std::string("conv kernel failed: ") + cudaGetErrorString(cudaGetLastError()));
+    return done(IDN_ECUDA);
+  }
+  if ((rc = read_tc_watchdog()) != IDN_OK) return done(rc);
+  rc = idn_read_activation(e.get(), (int)e->steps.size() - 1, n, y);
+  return done(rc);
+}
+
+}  // extern "C"

@@ -1,0 +1,190 @@
+// HBM-bound tail kernels: 3x3/stride-2 max-pool between layouts, ResNet18 head
+// (global average pool + FC + softmax/top-1 in one kernel) and softmax/top-1 over fp32 logits.
+#include "common.cuh"
+
+namespace idn {
+
+// ------------------------------------------------------------------------------------- max-pool
+// One thread = one output pixel x 8 channels (one 128-bit load per window tap, one 128-bit store).
+// Replaces nn.MaxPool2d(3, 2[, 1]) of tv:models/alexnet.py:24,27,34 and tv:models/resnet.py:201.
+// Window taps outside the valid H x W extent are skipped (PyTorch pads with -inf).
+__global__ void __launch_bounds__(256) maxpool3x3s2_kernel(const PoolParams p) {
+  const int cvec = p.C >> 3;
+  const long long total = (long long)p.nimg * p.OH * p.OW * cvec;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(t % cvec);
+    long long r = t / cvec;
+    const int ow = (int)(r % p.OW); r /= p.OW;
+    const int oh = (int)(r % p.OH);
+    const int n = (int)(r / p.OH);
+    float m[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) m[e] = -INFINITY;
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy) {
+      const int h = oh * 2 - p.pad + dy;
+      if (h < 0 || h >= p.H) continue;
+#pragma unroll
+      for (int dx = 0; dx < 3; ++dx) {
+        const int w = ow * 2 - p.pad + dx;
+        if (w < 0 || w >= p.W) continue;
+        const long long row = (long long)n * p.s_img_rows + (long long)h * p.s_wp + w;
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.in + row * p.C) + cv);
+        const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          m[2 * e] = fmaxf(m[2 * e], __uint_as_float(u[e] << 16));
+          m[2 * e + 1] = fmaxf(m[2 * e + 1], __uint_as_float(u[e] & 0xffff0000u));
+        }
+      }
+    }
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e)   // inputs are bf16, so the max is exactly representable
+      o[e] = (__float_as_uint(m[2 * e]) >> 16) | (__float_as_uint(m[2 * e + 1]) & 0xffff0000u);
+    const long long drow = (long long)n * p.d_img_rows + (long long)oh * p.d_wp + ow;
+    reinterpret_cast<uint4*>(p.out + drow * p.C)[cv] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+int launch_maxpool(const PoolParams& p, cudaStream_t st) {
+  if (p.C % 8 != 0) { set_error("maxpool: C % 8 != 0"); return IDN_EINVAL; }
+  const long long total = (long long)p.nimg * p.OH * p.OW * (p.C / 8);
+  if (total <= 0) return IDN_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > 148LL * 32) blocks = 148LL * 32;
+  maxpool3x3s2_kernel<<<(int)blocks, 256, 0, st>>>(p);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
+// ------------------------------------------------------------------------- softmax / top-1 tail
+// Warp-level: max + first argmax, then sum of exp(l - max); top-1 probability = 1 / sum.
+// Replaces softmax + topk(.,1) of alexnet_resnet.py:80-84; exact ties -> lowest class index.
+__device__ __forceinline__ void warp_softmax_top1(const float* logits, int lane, int32_t* idx_out,
+                                                  float* prob_out) {
+  float best = -INFINITY;
+  int best_i = 0x7fffffff;
+  for (int j = lane; j < IDN_NUM_CLASSES; j += 32) {
+    const float v = logits[j];
+    if (v > best) { best = v; best_i = j; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+    if (ob > best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
+  }
+  float sum = 0.0f;
+  for (int j = lane; j < IDN_NUM_CLASSES; j += 32) sum += expf(logits[j] - best);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) {
+    *idx_out = best_i;
+    *prob_out = 1.0f / sum;
+  }
+}
+
+__global__ void __launch_bounds__(256) softmax_top1_kernel(const float* __restrict__ logits, int ld,
+                                                           int nimg, float* __restrict__ logits_out,
+                                                           int32_t* __restrict__ idx,
+                                                           float* __restrict__ prob) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= nimg) return;
+  const float* l = logits + (long long)warp * ld;
+  if (logits_out != nullptr)
+    for (int j = lane; j < IDN_NUM_CLASSES; j += 32)
+      logits_out[(long long)warp * IDN_NUM_CLASSES + j] = l[j];
+  warp_softmax_top1(l, lane, idx + warp, prob + warp);
+}
+
+int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out, int32_t* idx,
+                        float* prob, cudaStream_t st) {
+  if (nimg <= 0) return IDN_OK;
+  softmax_top1_kernel<<<(nimg + 7) / 8, 256, 0, st>>>(logits, ld, nimg, logits_out, idx, prob);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
+// ---------------------------------------------------------------------------------- ResNet head
+// avgpool (tv:models/resnet.py:278) + fc (:280) + softmax/top-1 (alexnet_resnet.py:80-84) for
+// kHeadImgs images per CTA.  The FC runs in fp32 on fp32 weights (1 MFLOP/image): the last-layer
+// rounding is what decides near-tie top-1s.
+constexpr int kHeadImgs = 8;
+
+__global__ void __launch_bounds__(256)
+resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W, int C,
+                   const float* __restrict__ fc_w, const float* __restrict__ fc_b,
+                   float* __restrict__ logits_out, int32_t* __restrict__ idx,
+                   float* __restrict__ prob) {
+  extern __shared__ float sm[];
+  float* feat = sm;                           // [kHeadImgs][C]
+  float* logit = sm + kHeadImgs * C;          // [kHeadImgs][1000]
+  const int n0 = blockIdx.x * kHeadImgs;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float inv = 1.0f / (float)(H * W);
+  for (int e = threadIdx.x; e < kHeadImgs * C; e += blockDim.x) {
+    const int g = e / C, c = e - g * C;
+    float s = 0.0f;
+    if (n0 + g < nimg) {
+      const bf16* base = act + ((long long)(n0 + g) * img_rows) * C + c;
+      for (int h = 0; h < H; ++h)
+        for (int w = 0; w < W; ++w) s += __bfloat162float(base[(long long)(h * wp + w) * C]);
+    }
+    feat[e] = s * inv;
+  }
+  __syncthreads();
+  for (int j = warp; j < IDN_NUM_CLASSES; j += 8) {
+    float acc[kHeadImgs];
+#pragma unroll
+    for (int g = 0; g < kHeadImgs; ++g) acc[g] = 0.0f;
+    const float* wr = fc_w + (long long)j * C;
+    for (int c = lane * 4; c < C; c += 128) {
+      const float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + c));
+#pragma unroll
+      for (int g = 0; g < kHeadImgs; ++g) {
+        const float4 f4 = *reinterpret_cast<const float4*>(feat + g * C + c);
+        acc[g] = fmaf(w4.x, f4.x, acc[g]);
+        acc[g] = fmaf(w4.y, f4.y, acc[g]);
+        acc[g] = fmaf(w4.z, f4.z, acc[g]);
+        acc[g] = fmaf(w4.w, f4.w, acc[g]);
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < kHeadImgs; ++g) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], o);
+    }
+    if (lane == 0) {
+      const float b = fc_b[j];
+#pragma unroll
+      for (int g = 0; g < kHeadImgs; ++g) logit[g * IDN_NUM_CLASSES + j] = acc[g] + b;
+    }
+  }
+  __syncthreads();
+  if (warp < kHeadImgs && n0 + warp < nimg) {
+    const float* l = logit + warp * IDN_NUM_CLASSES;
+    if (logits_out != nullptr)
+      for (int j = lane; j < IDN_NUM_CLASSES; j += 32)
+        logits_out[(long long)(n0 + warp) * IDN_NUM_CLASSES + j] = l[j];
+    warp_softmax_top1(l, lane, idx + n0 + warp, prob + n0 + warp);
+  }
+}
+
+int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
+                       const float* fc_w, const float* fc_b, float* logits, int32_t* idx,
+                       float* prob, cudaStream_t st) {
+  if (nimg <= 0) return IDN_OK;
+  if (C % 128 != 0) { set_error("resnet_head: C % 128 != 0"); return IDN_EINVAL; }
+  const size_t smem = (size_t)kHeadImgs * (C + IDN_NUM_CLASSES) * sizeof(float);
+  IDN_CUDA_TRY(cudaFuncSetAttribute(resnet_head_kernel,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+  resnet_head_kernel<<<(nimg + kHeadImgs - 1) / kHeadImgs, 256, smem, st>>>(
+      act, nimg, img_rows, wp, H, W, C, fc_w, fc_b, logits, idx, prob);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
+}  // namespace idn

@@ -1,0 +1,133 @@
+/*
+ * idunno_b200.h -- C ABI of the B200-native inference hot path of the IDunno cluster.
+ *
+ * The reference (kentchen831213/-Distributed-Machine-Learning-System) has no FFI: its worker calls
+ * the plain Python function  alexnet_resnet.deeplearning(filename, modelname, start, end)
+ * (alexnet_resnet.py:12-92; call sites mp4_machinelearning.py:596 and :765).  The drop-in module
+ * of the same name shipped in this repo keeps that signature and binds the entry points below
+ * through ctypes.  Every function:
+ *   - has C linkage, plain pointers and sizes, no C++/torch types;
+ *   - returns 0 on success and a negative IDN_E* code otherwise; the message of the last error on
+ *     the calling thread is available from idn_last_error();
+ *   - never throws across the boundary;
+ *   - never falls back to a CPU implementation: without a usable sm_100 device it fails.
+ *
+ * Threading: calls on one handle must be serialised by the caller (the reference calls
+ * deeplearning() from one receiver thread, mp4_machinelearning.py:552-616).  No entry point holds
+ * the Python GIL (ctypes releases it around foreign calls).
+ */
+#ifndef IDUNNO_B200_H
+#define IDUNNO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IDN_OK            0
+#define IDN_EINVAL       -1   /* bad argument                                   */
+#define IDN_ECUDA        -2   /* CUDA runtime / driver error                    */
+#define IDN_ENODEV       -3   /* no sm_100 device / extension cannot run here   */
+#define IDN_EWEIGHTS     -4   /* weight blob has the wrong size for the model   */
+#define IDN_ENOMEM       -5
+
+#define IDN_MODEL_ALEXNET  0  /* modelname == "alexnet"  (alexnet_resnet.py:17-19) */
+#define IDN_MODEL_RESNET18 1  /* any other modelname     (alexnet_resnet.py:20-22) */
+
+#define IDN_NUM_CLASSES 1000
+#define IDN_CROP        224   /* transforms.CenterCrop(224), alexnet_resnet.py:59 */
+
+/* Convolution back-ends.  TC is the product path (tcgen05 / TMEM / TMA implicit GEMM).  SIMT is a
+ * slow CUDA-core kernel over the same operand layouts kept as an on-device cross-check for tests
+ * and bring-up; it is never selected implicitly. */
+#define IDN_IMPL_TC   0
+#define IDN_IMPL_SIMT 1
+
+typedef struct idn_engine* idn_handle;
+
+/* Replaces: model construction/load + .eval() at alexnet_resnet.py:17-22, done once per process
+ * instead of once per call.  weights_blob = the model's state_dict as fp32 values concatenated in
+ * torchvision state_dict order, skipping the integer num_batches_tracked entries (layout in
+ * INTEGRATION.md; idunno_b200.weights.pack_state_dict builds it).  BatchNorm is folded to a
+ * per-channel fp32 scale/shift, weights are converted to bf16 and re-laid-out for the kernels.
+ * max_batch = largest tensor batch one pass processes (activation buffers are sized for it; longer
+ * inputs are processed in chunks of max_batch). */
+int idn_create(int device, int model_id, const void* weights_blob, size_t n_bytes, int max_batch,
+               idn_handle* out);
+
+/* Frees all device memory owned by the handle. */
+int idn_destroy(idn_handle h);
+
+/* Number of fp32 values idn_create expects for model_id (61 100 840 for AlexNet,
+ * 11 699 112 for ResNet18 = parameters + BatchNorm running statistics). */
+int64_t idn_weight_count(int model_id);
+
+/* Work is enqueued on this CUDA stream (a cudaStream_t); default: a stream owned by the handle. */
+int idn_set_stream(idn_handle h, void* cuda_stream);
+
+/* Selects IDN_IMPL_TC (default) or IDN_IMPL_SIMT for the convolution / FC layers. */
+int idn_set_impl(idn_handle h, int impl);
+
+/* Replaces the per-image body of the reference loop, alexnet_resnet.py:57-87:
+ * Resize(256)/CenterCrop(224)/ToTensor/Normalize, model forward, softmax, top-1 -- for n images at
+ * once (eval-mode results are independent per image, so batching is exact).
+ *   imgs_packed : uint8 RGB, HWC, images back to back (HOST memory; pinned is faster)
+ *   offsets[n]  : byte offset of image i in imgs_packed
+ *   hw[2n]      : (H_i, W_i)
+ *   top1_idx[n] : argmax class index (lowest index on exact ties)
+ *   top1_prob[n]: softmax probability of that class, fp32
+ *   logits      : optional [n][1000] fp32 (NULL to skip)
+ * Host buffers in and out: the call copies inputs to the device, runs, copies results back and
+ * returns after they have arrived. */
+int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* offsets,
+                    const int32_t* hw, int n, int32_t* top1_idx, float* top1_prob, float* logits);
+
+/* Same computation with the image bytes and the results resident in DEVICE memory (offsets/hw stay
+ * host arrays: a few bytes of metadata).  Asynchronous on the handle's stream; n <= max_batch. */
+int idn_infer_u8hwc_device(idn_handle h, const uint8_t* d_imgs_packed, const int64_t* offsets,
+                           const int32_t* hw, int n, int32_t* d_top1_idx, float* d_top1_prob,
+                           float* d_logits);
+
+/* Blocks until everything enqueued on the handle's stream has finished. */
+int idn_sync(idn_handle h);
+
+/* Replaces the preprocess Compose at alexnet_resnet.py:57-66 alone (parity tests, staging):
+ * host uint8 HWC images -> host bf16 (raw uint16 bit patterns) NCHW [n][3][224][224]. */
+int idn_preprocess_u8hwc(int device, const uint8_t* imgs_packed, const int64_t* offsets,
+                         const int32_t* hw, int n, uint16_t* out_nchw_bf16);
+
+/* Test/diagnostic taps (no reference counterpart).  After idn_infer_*, copy the activation written
+ * by plan step `step` of the last pass to host as fp32 NCHW [n][C][H][W]; idn_num_steps /
+ * idn_step_info describe the plan.  Returns IDN_EINVAL for steps without an image-shaped output. */
+int idn_num_steps(idn_handle h);
+int idn_step_info(idn_handle h, int step, char* name, int name_len, int32_t* chw /* [3] */);
+int idn_read_activation(idn_handle h, int step, int n, float* out_nchw);
+
+/* Counters for bench.py: kernels launched by this handle since creation, and the duration in
+ * milliseconds of plan step `step` in the last pass when timing was switched on
+ * (idn_set_timing(h, 1) records CUDA events around every step). */
+int64_t idn_kernel_launches(idn_handle h);
+int idn_set_timing(idn_handle h, int on);
+int idn_step_time_ms(idn_handle h, int step, float* ms);
+
+/* Stand-alone layer entry (tests): y = act(conv(x, w) * scale + shift (+ residual)) with NCHW fp32
+ * host tensors, computed through the same operand layouts and kernels as the model plans.
+ * x [n][cin][h][w], w [cout][cin][r][s] fp32 (rounded to bf16 inside), scale/shift [cout],
+ * residual NULL or [n][cout][oh][ow], y [n][cout][oh][ow].  cin must be a multiple of 64 and cout
+ * a multiple of 64; stride 1 or 2 (stride 2 supports r=s=3,pad=1 and r=s=1,pad=0). */
+int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h, int w,
+                    const float* wgt, int cout, int r, int s, int stride, int pad,
+                    const float* scale, const float* shift, const float* residual, int relu,
+                    float* y);
+
+const char* idn_last_error(void);
+
+/* Library build identification ("idunno_b200 <version> sm_100a"). */
+const char* idn_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IDUNNO_B200_H */

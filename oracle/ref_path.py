@@ -79,13 +79,26 @@ def forward(modelname: str, sd: dict, x: torch.Tensor) -> torch.Tensor:
         return alexnet_forward(sd, x) if modelname == "alexnet" else resnet18_forward(sd, x)
 
 
-def infer_arrays(modelname: str, sd: dict, images: list[np.ndarray]):
+def preprocess_library(img: np.ndarray) -> np.ndarray:
+    """The reference's own preprocess call chain (alexnet_resnet.py:57-66): PIL image through
+    torchvision's Compose.  Bit-identical to ``pil_resize.preprocess`` (tests/test_oracle.py) and
+    much faster (Pillow's C resample); used where the CPU path is TIMED."""
+    from PIL import Image
+    from torchvision import transforms
+    tf = transforms.Compose([                                               # :57-62, rebuilt per image
+        transforms.Resize(256), transforms.CenterCrop(224), transforms.ToTensor(),
+        transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])
+    return tf(Image.fromarray(img)).numpy()
+
+
+def infer_arrays(modelname: str, sd: dict, images: list[np.ndarray], library_preprocess: bool = False):
     """Hot path on in-memory uint8 HWC images, one image per forward as the reference does
     (``alexnet_resnet.py:66-84``).  Returns dict(pre[n,3,224,224] f32, logits[n,1000] f32,
     idx[n] int64, prob[n] f32)."""
     pre, logits, idx, prob = [], [], [], []
+    prep = preprocess_library if library_preprocess else pil_resize.preprocess
     for img in images:
-        t = torch.from_numpy(pil_resize.preprocess(img)).unsqueeze(0)       # :66-67
+        t = torch.from_numpy(prep(img)).unsqueeze(0)                         # :66-67
         out = forward(modelname, sd, t)                                      # :74-75
         p = F.softmax(out[0], dim=0)                                         # :80
         top_prob, top_catid = torch.topk(p, 1)                               # :84
@@ -139,3 +152,46 @@ def imagenet_categories() -> list[str]:
     by the reference; offline the same names come from torchvision's metadata."""
     from torchvision.models._meta import _IMAGENET_CATEGORIES
     return list(_IMAGENET_CATEGORIES)
+
+
+def forward_taps(modelname: str, sd: dict, x: torch.Tensor) -> dict:
+    """Intermediate activations of the restated forward, keyed by the plan-step names of the CUDA
+    engine (csrc/engine.cu), for layer-by-layer parity tests.  fp32 NCHW."""
+    taps = {}
+    with torch.no_grad():
+        if modelname == "alexnet":
+            x = F.relu(F.conv2d(x, sd["features.0.weight"], sd["features.0.bias"], stride=4, padding=2))
+            taps["features.0+relu"] = x
+            x = F.max_pool2d(x, 3, 2); taps["features.2 maxpool"] = x
+            x = F.relu(F.conv2d(x, sd["features.3.weight"], sd["features.3.bias"], padding=2))
+            taps["features.3+relu"] = x
+            x = F.max_pool2d(x, 3, 2); taps["features.5 maxpool"] = x
+            for k in ("6", "8", "10"):
+                x = F.relu(F.conv2d(x, sd[f"features.{k}.weight"], sd[f"features.{k}.bias"], padding=1))
+                taps[f"features.{k}+relu"] = x
+            x = F.max_pool2d(x, 3, 2); taps["features.12 maxpool"] = x
+            x = torch.flatten(F.adaptive_avg_pool2d(x, (6, 6)), 1)
+            x = F.relu(F.linear(x, sd["classifier.1.weight"], sd["classifier.1.bias"]))
+            taps["classifier.1+relu"] = x[:, :, None, None]
+            x = F.relu(F.linear(x, sd["classifier.4.weight"], sd["classifier.4.bias"]))
+            taps["classifier.4+relu"] = x[:, :, None, None]
+            x = F.linear(x, sd["classifier.6.weight"], sd["classifier.6.bias"])
+            taps["classifier.6"] = x[:, :, None, None]
+            return taps
+        x = F.relu(_bn(sd, "bn1", F.conv2d(x, sd["conv1.weight"], None, stride=2, padding=3)))
+        taps["conv1+bn1+relu"] = x
+        x = F.max_pool2d(x, 3, 2, 1); taps["maxpool"] = x
+        for li, stride in ((1, 1), (2, 2), (3, 2), (4, 2)):
+            for bi, st in ((0, stride), (1, 1)):
+                p = f"layer{li}.{bi}"
+                out = F.relu(_bn(sd, p + ".bn1", F.conv2d(x, sd[p + ".conv1.weight"], None, stride=st, padding=1)))
+                taps[p + ".conv1"] = out
+                out = _bn(sd, p + ".bn2", F.conv2d(out, sd[p + ".conv2.weight"], None, padding=1))
+                if (p + ".downsample.0.weight") in sd:
+                    idn = _bn(sd, p + ".downsample.1", F.conv2d(x, sd[p + ".downsample.0.weight"], None, stride=st))
+                    taps[p + ".downsample"] = idn
+                else:
+                    idn = x
+                x = F.relu(out + idn)
+                taps[p + ".conv2+add"] = x
+    return taps

@@ -1,0 +1,110 @@
+"""CPU: host-side logic (sharding, packing, weights blob) and the C-ABI library surface."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from idunno_b200 import _lib, pack_images, sharding, weights
+from idunno_b200.synth import make_state_dict, synth_image
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_split_range_matches_reference_examples():
+    # SURVEY.md 3.1 step 5 / mp4_machinelearning.py:523-536
+    assert [(s, e) for _, s, e in sharding.split_range(0, 399, list(range(5)))] == \
+        [(0, 79), (80, 159), (160, 239), (240, 319), (320, 399)]
+    assert [(s, e) for _, s, e in sharding.split_range(0, 399, list(range(8)))] == \
+        [(50 * i, 50 * i + 49) for i in range(8)]
+    assert [(s, e) for _, s, e in sharding.split_range(0, 399, list(range(3)))] == \
+        [(0, 132), (133, 266), (267, 399)]
+    assert [(s, e) for _, s, e in sharding.split_range(0, 79999, list(range(8)))] == \
+        [(10000 * i, 10000 * i + 9999) for i in range(8)]
+
+
+@pytest.mark.parametrize("start,end,k", [(0, 0, 1), (5, 11, 3), (0, 2, 5), (7, 406, 8), (0, 1000, 7)])
+def test_split_range_covers_range_exactly_once(start, end, k):
+    shards = sharding.split_range(start, end, list(range(k)))
+    seen = []
+    for _, s, e in shards:
+        seen.extend(range(s, e + 1))
+    assert seen == list(range(start, end + 1))
+
+
+def test_split_queries_and_fair_share():
+    assert sharding.split_queries(0, 399) == [(0, 399)]
+    assert sharding.split_queries(0, 3999)[:2] == [(0, 399), (400, 799)]
+    assert len(sharding.split_queries(0, 3999)) == 10
+    # the reference's constant 100/100 average times give 5 workers per query
+    assert sharding.fair_share("alexnet", {"alexnet": 100, "resnet18": 100}, 10) == 5
+    assert sharding.fair_share("resnet18", {"alexnet": 100, "resnet18": 100}, 10) == 5
+    # AlexNet queries twice as fast -> ResNet18 gets the larger share, clamped to the box
+    assert sharding.fair_share("alexnet", {"alexnet": 1.0, "resnet18": 2.0}, 8) == 3
+    assert sharding.fair_share("resnet18", {"alexnet": 1.0, "resnet18": 2.0}, 8) == 7
+    assert sharding.fair_share("resnet18", {"alexnet": 1.0, "resnet18": 0}, 8) == 5
+
+
+def test_reassign_moves_whole_subrange_to_ring_successor():
+    shards = sharding.split_range(0, 399, list(range(4)))
+    out = sharding.reassign(shards, dead=2, alive={0, 1, 3}, world=4)
+    assert out == [(0, 0, 99), (1, 100, 199), (3, 200, 299), (3, 300, 399)]
+    # successor of the last rank is the coordinator (0), which is skipped (:720) -> rank 1
+    out = sharding.reassign(shards, dead=3, alive={0, 1, 2}, world=4)
+    assert out[3] == (1, 300, 399)
+    # only the coordinator left
+    out = sharding.reassign([(1, 0, 9)], dead=1, alive={0}, world=2)
+    assert out == [(0, 0, 9)]
+
+
+def test_pack_images_ragged_and_aligned():
+    imgs = [synth_image(i, mixed=True) for i in range(5)]
+    packed, offsets, hw = pack_images(imgs)
+    assert all(int(o) % 16 == 0 for o in offsets)
+    for im, o, (h, w) in zip(imgs, offsets, hw):
+        assert (h, w) == im.shape[:2]
+        assert np.array_equal(packed[int(o):int(o) + im.size].reshape(im.shape), im)
+    p0, o0, hw0 = pack_images([])
+    assert o0.shape == (0,) and hw0.shape == (0, 2)
+    with pytest.raises(ValueError):
+        pack_images([np.zeros((4, 4), dtype=np.uint8)])
+
+
+def test_weight_blob_sizes_match_library():
+    lib = _lib.load_library()
+    for model, mid in (("alexnet", 0), ("resnet18", 1)):
+        blob = weights.pack_state_dict(make_state_dict(model, 0))
+        assert blob.dtype == np.float32 and blob.size == lib.idn_weight_count(mid)
+    assert lib.idn_weight_count(7) == -1
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "idunno_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(idn_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert b"sm_100a" in _lib.load_library().idn_version()
+
+
+def test_no_cpu_fallback_without_a_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    lib = _lib.load_library()
+    blob = np.zeros(lib.idn_weight_count(1), dtype=np.float32)
+    h = ctypes.c_void_p()
+    rc = lib.idn_create(0, 1, blob.ctypes.data, blob.nbytes, 8, ctypes.byref(h))
+    assert rc != 0 and not h.value
+    assert b"no CUDA device" in lib.idn_last_error() or b"failed" in lib.idn_last_error()
+    out = np.zeros((1, 3, 224, 224), dtype=np.uint16)
+    packed, offsets, hw = pack_images([synth_image(0)])
+    assert lib.idn_preprocess_u8hwc(0, packed.ctypes.data, offsets.ctypes.data, hw.ctypes.data, 1,
+                                    out.ctypes.data) != 0
+    # bad arguments are rejected before any device work
+    assert lib.idn_create(0, 5, blob.ctypes.data, blob.nbytes, 8, ctypes.byref(h)) == -1
+    assert lib.idn_create(0, 1, blob.ctypes.data, 16, 8, ctypes.byref(h)) == -4

@@ -1,0 +1,40 @@
+#!/bin/bash
+# One GPU-box session: parity tests (one pytest process per file), diagnostics, bench, profiles.
+# Usage (from the repo root, under gpurun):  bash tools/gpu_round.sh [tests|bench|ncu ...]
+set -u
+mkdir -p gpurun_out
+WHAT="${*:-tests bench}"
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.limit --format=csv > gpurun_out/gpu.csv 2>&1
+for w in $WHAT; do
+case $w in
+diag)
+  timeout 600 python tools/gpu_diag.py > gpurun_out/diag.log 2>&1; echo "diag rc=$?" ;;
+tests)
+  for f in tests/test_gpu_preprocess.py tests/test_gpu_conv.py tests/test_gpu_model.py; do
+    b=$(basename $f .py)
+    timeout 1500 python -m pytest $f -m gpu -q -rA -s -p no:cacheprovider > gpurun_out/$b.log 2>&1
+    echo "$b rc=$? $(tail -1 gpurun_out/$b.log)"
+  done ;;
+bench)
+  timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err
+  echo "bench rc=$?"; cat gpurun_out/bench.json | cut -c1-1500 ;;
+benchref)
+  timeout 900 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
+  echo "benchref rc=$?"; cut -c1-600 gpurun_out/bench_ref.json ;;
+ncu)
+  for m in alexnet resnet18; do
+    timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_$m.log 2>&1 &&
+    timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s 120 -c 200 --csv \
+        --log-file gpurun_out/launches_$m.csv python bench.py --steps 2 --warmup 3 --models $m \
+        > gpurun_out/ncu_launch_$m.log 2>&1
+    echo "ncu launches $m rc=$?"
+  done ;;
+ncufull)
+  m=${NCU_MODEL:-resnet18}
+  timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_full.log 2>&1 &&
+  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:conv_tc_kernel \
+      -s ${NCU_SKIP:-100} -c ${NCU_COUNT:-6} -o gpurun_out/prof_$m -f python bench.py --steps 2 --warmup 3 --models $m \
+      > gpurun_out/ncu_full_$m.log 2>&1
+  echo "ncu full $m rc=$?" ;;
+esac
+done

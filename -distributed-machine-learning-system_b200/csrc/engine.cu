@@ -89,6 +89,7 @@ struct idn_engine {
   bool stem_simt = false;   // bring-up switch IDN_STEM_SIMT=1: run the two C=3 stem layers on the
                             // CUDA-core kernel (explicit, never automatic)
   bool timing = false;
+  int stop_after = -1;      // diagnostic: run the plan up to and including this step
   int last_n = 0;
 };
 
@@ -112,6 +113,10 @@ static int alloc_act(idn_engine* e, Act* a, Geom g, int C, int cap, int planes =
 
 static int pick_block_n(int n_total, long long m_tiles, int num_sms) {
   const int cands[4] = {256, 192, 128, 64};
+  if (const char* v = std::getenv("IDN_BLOCK_N")) {     // test hook: force an N tile that divides Cout
+    const int f = std::atoi(v);
+    for (int c : cands) if (c == f && n_total % c == 0) return c;
+  }
   for (int c : cands)
     if (n_total % c == 0 && m_tiles * (n_total / c) * 10 >= (long long)num_sms * 8) return c;
   if (n_total % 128 == 0) return 128;
@@ -532,7 +537,10 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
                     float* d_logits) {
   cudaStream_t st = e->stream;
   e->last_n = n;
+  int step_no = 0;
   for (Step& s : e->steps) {
+    if (e->stop_after >= 0 && step_no > e->stop_after) break;
+    ++step_no;
     if (e->timing) {
       if (!s.ev0) { IDN_CUDA_TRY(cudaEventCreate(&s.ev0)); IDN_CUDA_TRY(cudaEventCreate(&s.ev1)); }
       IDN_CUDA_TRY(cudaEventRecord(s.ev0, st));
@@ -559,8 +567,9 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
         break;
       case STEP_RHEAD:
         IDN_TRY(launch_resnet_head(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,
-                                   e->head_g.W, e->head_C, e->fc_w, e->fc_b, d_logits, d_idx,
-                                   d_prob, st));
+                                   e->head_g.W, e->head_C, e->fc_w, e->fc_b,
+                                   d_logits ? d_logits : e->d_logits, d_idx, d_prob, st));
+        e->launches += 1;                       // avgpool+fc kernel, then softmax/top-1
         break;
       case STEP_SOFTMAX:
         IDN_TRY(launch_softmax_top1(e->logits_pad, 1024, n, d_logits, d_idx, d_prob, st));
@@ -819,6 +828,12 @@ int idn_read_activation(idn_handle h, int step, int n, float* out) {
         for (int c = 0; c < C; ++c)
           out[(((size_t)i * C + c) * H + y) * W + x] = bf16_bits_to_f32(src[c]);
       }
+  return IDN_OK;
+}
+
+int idn_debug_stop_after(idn_handle h, int step) {
+  if (!h) return IDN_EINVAL;
+  h->stop_after = step;
   return IDN_OK;
 }
 

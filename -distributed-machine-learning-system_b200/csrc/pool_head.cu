@@ -109,34 +109,44 @@ int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out
 }
 
 // ---------------------------------------------------------------------------------- ResNet head
-// avgpool (tv:models/resnet.py:278) + fc (:280) + softmax/top-1 (alexnet_resnet.py:80-84) for
-// kHeadImgs images per CTA.  The FC runs in fp32 on fp32 weights (1 MFLOP/image): the last-layer
-// rounding is what decides near-tie top-1s.
-constexpr int kHeadImgs = 8;
+// avgpool (tv:models/resnet.py:278) + fc (:280) in one kernel, softmax/top-1 (alexnet_resnet.py:80-84)
+// in the warp-shuffle kernel above.  The FC runs in fp32 on fp32 weights (1 MFLOP/image): the
+// last-layer rounding is what decides near-tie top-1s.
+// grid = (ceil(n / 16), 8): a CTA pools 16 images into shared memory (fp32) and computes 125 of the
+// 1000 classes for them; a warp owns a class at a time, lanes split K = 512 with 128-bit loads.
+constexpr int kHeadImgs = 16;
+constexpr int kHeadChunks = 8;
+constexpr int kHeadClassesPerChunk = IDN_NUM_CLASSES / kHeadChunks;   // 125
 
 __global__ void __launch_bounds__(256)
 resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W, int C,
                    const float* __restrict__ fc_w, const float* __restrict__ fc_b,
-                   float* __restrict__ logits_out, int32_t* __restrict__ idx,
-                   float* __restrict__ prob) {
-  extern __shared__ float sm[];
-  float* feat = sm;                           // [kHeadImgs][C]
-  float* logit = sm + kHeadImgs * C;          // [kHeadImgs][1000]
+                   float* __restrict__ logits) {
+  extern __shared__ float feat[];             // [kHeadImgs][C]
   const int n0 = blockIdx.x * kHeadImgs;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float inv = 1.0f / (float)(H * W);
-  for (int e = threadIdx.x; e < kHeadImgs * C; e += blockDim.x) {
-    const int g = e / C, c = e - g * C;
-    float s = 0.0f;
+  const int cpairs = C >> 1;
+  for (int e = threadIdx.x; e < kHeadImgs * cpairs; e += blockDim.x) {
+    const int g = e / cpairs, cp = e - g * cpairs;
+    float s0 = 0.0f, s1 = 0.0f;
     if (n0 + g < nimg) {
-      const bf16* base = act + ((long long)(n0 + g) * img_rows) * C + c;
+      const uint32_t* base =
+          reinterpret_cast<const uint32_t*>(act + ((long long)(n0 + g) * img_rows) * C) + cp;
       for (int h = 0; h < H; ++h)
-        for (int w = 0; w < W; ++w) s += __bfloat162float(base[(long long)(h * wp + w) * C]);
+        for (int w = 0; w < W; ++w) {
+          const uint32_t u = __ldg(base + (long long)(h * wp + w) * cpairs);
+          s0 += __uint_as_float(u << 16);
+          s1 += __uint_as_float(u & 0xffff0000u);
+        }
     }
-    feat[e] = s * inv;
+    feat[g * C + 2 * cp] = s0 * inv;
+    feat[g * C + 2 * cp + 1] = s1 * inv;
   }
   __syncthreads();
-  for (int j = warp; j < IDN_NUM_CLASSES; j += 8) {
+  const int j0 = blockIdx.y * kHeadClassesPerChunk;
+  for (int jj = warp; jj < kHeadClassesPerChunk; jj += 8) {
+    const int j = j0 + jj;
     float acc[kHeadImgs];
 #pragma unroll
     for (int g = 0; g < kHeadImgs; ++g) acc[g] = 0.0f;
@@ -157,19 +167,10 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], o);
     }
-    if (lane == 0) {
-      const float b = fc_b[j];
+    const float b = __ldg(fc_b + j);
 #pragma unroll
-      for (int g = 0; g < kHeadImgs; ++g) logit[g * IDN_NUM_CLASSES + j] = acc[g] + b;
-    }
-  }
-  __syncthreads();
-  if (warp < kHeadImgs && n0 + warp < nimg) {
-    const float* l = logit + warp * IDN_NUM_CLASSES;
-    if (logits_out != nullptr)
-      for (int j = lane; j < IDN_NUM_CLASSES; j += 32)
-        logits_out[(long long)(n0 + warp) * IDN_NUM_CLASSES + j] = l[j];
-    warp_softmax_top1(l, lane, idx + n0 + warp, prob + n0 + warp);
+    for (int g = 0; g < kHeadImgs; ++g)
+      if (lane == g && n0 + g < nimg) logits[(long long)(n0 + g) * IDN_NUM_CLASSES + j] = acc[g] + b;
   }
 }
 
@@ -177,14 +178,12 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
                        const float* fc_w, const float* fc_b, float* logits, int32_t* idx,
                        float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  if (C % 128 != 0) { set_error("resnet_head: C % 128 != 0"); return IDN_EINVAL; }
-  const size_t smem = (size_t)kHeadImgs * (C + IDN_NUM_CLASSES) * sizeof(float);
-  IDN_CUDA_TRY(cudaFuncSetAttribute(resnet_head_kernel,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-  resnet_head_kernel<<<(nimg + kHeadImgs - 1) / kHeadImgs, 256, smem, st>>>(
-      act, nimg, img_rows, wp, H, W, C, fc_w, fc_b, logits, idx, prob);
+  if (C % 128 != 0 || logits == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
+  const size_t smem = (size_t)kHeadImgs * C * sizeof(float);
+  dim3 grid((nimg + kHeadImgs - 1) / kHeadImgs, kHeadChunks);
+  resnet_head_kernel<<<grid, 256, smem, st>>>(act, nimg, img_rows, wp, H, W, C, fc_w, fc_b, logits);
   IDN_CUDA_TRY(cudaGetLastError());
-  return IDN_OK;
+  return launch_softmax_top1(logits, IDN_NUM_CLASSES, nimg, nullptr, idx, prob, st);
 }
 
 }  // namespace idn

@@ -32,6 +32,7 @@ SIGNATURES = {
     "idn_num_steps": (C.c_int, [C.c_void_p]),
     "idn_step_info": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.c_void_p]),
     "idn_read_activation": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "idn_debug_stop_after": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_kernel_launches": (C.c_int64, [C.c_void_p]),
     "idn_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_step_time_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),

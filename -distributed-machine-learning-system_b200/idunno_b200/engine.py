@@ -128,6 +128,9 @@ class Engine:
         _lib.check(self._lib.idn_read_activation(self._h, step, n, out.ctypes.data), "idn_read_activation")
         return out
 
+    def stop_after(self, step: int):
+        _lib.check(self._lib.idn_debug_stop_after(self._h, int(step)), "idn_debug_stop_after")
+
     def step_times_ms(self):
         out = []
         for i, (name, _) in enumerate(self.steps()):

@@ -130,7 +130,8 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
 
     sd = make_state_dict(model, 0, "default")
     eng = Engine(model, sd, device=device, max_batch=BATCH)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=device)      # a real (non-NULL) stream: NULL selects the handle's own
+    torch.cuda.set_stream(stream)
     eng.set_stream(stream.cuda_stream)
 
     n_pool = 4                                     # 4 x 60.2 MB of distinct uint8 input > 126 MB L2

@@ -99,11 +99,15 @@ int idn_preprocess_u8hwc(int device, const uint8_t* imgs_packed, const int64_t* 
                          const int32_t* hw, int n, uint16_t* out_nchw_bf16);
 
 /* Test/diagnostic taps (no reference counterpart).  After idn_infer_*, copy the activation written
- * by plan step `step` of the last pass to host as fp32 NCHW [n][C][H][W]; idn_num_steps /
+ * by plan step `step` of the last pass to host as fp32 NCHW [n][C][H][W] (buffers are reused: the
+ * value is the LAST writer's unless idn_debug_stop_after stopped the pass there); idn_num_steps /
  * idn_step_info describe the plan.  Returns IDN_EINVAL for steps without an image-shaped output. */
 int idn_num_steps(idn_handle h);
 int idn_step_info(idn_handle h, int step, char* name, int name_len, int32_t* chw /* [3] */);
 int idn_read_activation(idn_handle h, int step, int n, float* out_nchw);
+/* Later passes run the plan only up to and including `step` (-1: whole plan), so that an
+ * activation buffer that a later step reuses can be read back right after its producer. */
+int idn_debug_stop_after(idn_handle h, int step);
 
 /* Counters for bench.py: kernels launched by this handle since creation, and the duration in
  * milliseconds of plan step `step` in the last pass when timing was switched on

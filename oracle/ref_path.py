@@ -195,3 +195,51 @@ def forward_taps(modelname: str, sd: dict, x: torch.Tensor) -> dict:
                 x = F.relu(out + idn)
                 taps[p + ".conv2+add"] = x
     return taps
+
+
+# ---------------------------------------------------------------------------------------------
+# Precision contract of the CUDA path, restated on the CPU: bf16 operands (weights and every
+# stored activation rounded to bf16, round-to-nearest-even), fp32 accumulation, BatchNorm / bias
+# applied in fp32 as a per-channel scale/shift after the convolution, residual added in fp32,
+# ResNet18's last FC in fp32, AlexNet's last FC with bf16 weights and fp32 output.  Used by the
+# tests to state the bf16-vs-fp32 tolerance: |this - fp32 oracle| is what bf16 arithmetic costs on
+# a given weight set, independently of any kernel.
+# ---------------------------------------------------------------------------------------------
+def _q(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def _fold(sd, p):
+    s = sd[p + ".weight"] / torch.sqrt(sd[p + ".running_var"] + 1e-5)
+    return s, sd[p + ".bias"] - sd[p + ".running_mean"] * s
+
+
+def forward_bf16_contract(modelname: str, sd: dict, x: torch.Tensor) -> torch.Tensor:
+    with torch.no_grad():
+        x = _q(x)
+        if modelname == "alexnet":
+            def cv(x, k, **kw):
+                return _q(F.relu(F.conv2d(x, _q(sd[f"features.{k}.weight"]), None, **kw)
+                                 + sd[f"features.{k}.bias"].view(1, -1, 1, 1)))
+            x = F.max_pool2d(cv(x, 0, stride=4, padding=2), 3, 2)
+            x = F.max_pool2d(cv(x, 3, padding=2), 3, 2)
+            x = cv(cv(cv(x, 6, padding=1), 8, padding=1), 10, padding=1)
+            x = torch.flatten(F.max_pool2d(x, 3, 2), 1)
+            x = _q(F.relu(F.linear(x, _q(sd["classifier.1.weight"])) + sd["classifier.1.bias"]))
+            x = _q(F.relu(F.linear(x, _q(sd["classifier.4.weight"])) + sd["classifier.4.bias"]))
+            return F.linear(x, _q(sd["classifier.6.weight"])) + sd["classifier.6.bias"]
+
+        def cbn(x, conv, bn, stride=1, padding=0):
+            s, b = _fold(sd, bn)
+            return F.conv2d(x, _q(sd[conv + ".weight"]), None, stride=stride, padding=padding) \
+                * s.view(1, -1, 1, 1) + b.view(1, -1, 1, 1)
+        x = F.max_pool2d(_q(F.relu(cbn(x, "conv1", "bn1", 2, 3))), 3, 2, 1)
+        for li, stride in ((1, 1), (2, 2), (3, 2), (4, 2)):
+            for bi, st in ((0, stride), (1, 1)):
+                p = f"layer{li}.{bi}"
+                out = _q(F.relu(cbn(x, p + ".conv1", p + ".bn1", st, 1)))
+                idn = _q(cbn(x, p + ".downsample.0", p + ".downsample.1", st, 0)) \
+                    if (p + ".downsample.0.weight") in sd else x
+                x = _q(F.relu(cbn(out, p + ".conv2", p + ".bn2", 1, 1) + idn))
+        x = torch.flatten(F.adaptive_avg_pool2d(x, (1, 1)), 1)
+        return F.linear(x, sd["fc.weight"], sd["fc.bias"])

@@ -48,8 +48,13 @@ SHAPES = [
 
 
 def _err(got, want):
-    scale = float(np.sqrt((want.astype(np.float64) ** 2).mean())) + 1e-6
-    return float(np.abs(got - want).max()) / scale
+    """max over elements of |got - want| / (|want| + rms(want)).  The output is stored as bf16
+    (half an ulp = 2^-9 = 0.2 % of the value); fp32 accumulation-order noise is far below that."""
+    rms = float(np.sqrt((want.astype(np.float64) ** 2).mean())) + 1e-6
+    return float((np.abs(got - want) / (np.abs(want) + rms)).max())
+
+
+TOL = 6e-3
 
 
 @pytest.mark.parametrize("impl", ["simt", "tc"])
@@ -60,8 +65,7 @@ def test_conv_layer_matches_torch(built_library, shape, impl):
     got = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl=impl)
     assert got.shape == want.shape
     e = _err(got, want)
-    # bf16 output rounding is 2^-9 relative; 2e-2 of the output RMS leaves room for large values
-    assert e < 2e-2, f"{impl} {shape}: max err / rms = {e:.4f}"
+    assert e < TOL, f"{impl} {shape}: max err = {e:.4f}"
 
 
 def test_fc_shaped_gemm(built_library):
@@ -74,4 +78,30 @@ def test_fc_shaped_gemm(built_library):
     want = F.relu(F.conv2d(x, wt, b)).numpy()
     for impl in ("simt", "tc"):
         got = conv2d_nchw(x.numpy(), wt.numpy(), None, b.numpy(), None, relu=True, impl=impl)
-        assert _err(got, want) < 2e-2, impl
+        assert _err(got, want) < TOL, impl
+
+
+@pytest.mark.parametrize("block_n,shape", [
+    (256, (9, 256, 14, 14, 256, 3, 1, 1, True, True)),
+    (256, (20, 512, 7, 7, 512, 3, 1, 1, True, True)),
+    (192, (4, 64, 27, 27, 192, 5, 1, 2, False, True)),
+    (192, (6, 192, 13, 13, 384, 3, 1, 1, False, True)),
+    (64, (5, 128, 28, 28, 128, 3, 1, 1, True, True)),
+], ids=lambda v: str(v).replace(" ", ""))
+def test_every_n_tile_width(built_library, monkeypatch, block_n, shape):
+    """Small problems pick narrow N tiles by themselves; force the wide instantiations
+    (BLOCK_N = 192 / 256: 5- and 4-stage rings, 512 TMEM columns) that batch-400 plans use."""
+    monkeypatch.setenv("IDN_BLOCK_N", str(block_n))
+    n, cin, h, w, cout, r, stride, pad, residual, relu = shape
+    x, wt, sc, sh, res, want = _case(*shape, seed=block_n + n)
+    got = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl="tc")
+    assert _err(got, want) < TOL
+
+
+def test_many_tiles_per_cta(built_library):
+    """More M tiles than SMs: every CTA loops over several tiles, so both TMEM accumulator stages
+    and several wraps of the smem ring are exercised (persistent scheduling)."""
+    shape = (40, 64, 56, 56, 64, 3, 1, 1, True, True)     # 40*57*57/128 = 1016 tiles
+    x, wt, sc, sh, res, want = _case(*shape, seed=77)
+    got = conv2d_nchw(x, wt, sc, sh, res, stride=1, pad=1, relu=True, impl="tc")
+    assert _err(got, want) < TOL

@@ -23,8 +23,10 @@ benchref)
   echo "benchref rc=$?"; cut -c1-600 gpurun_out/bench_ref.json ;;
 ncu)
   for m in alexnet resnet18; do
+    # one pass = 13 launches (alexnet) / 24 (resnet18); skip the 3 warm-up passes, list 2 passes
+    if [ $m = alexnet ]; then SK=39; CN=26; else SK=72; CN=48; fi
     timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_$m.log 2>&1 &&
-    timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s 120 -c 200 --csv \
+    timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s $SK -c $CN --csv \
         --log-file gpurun_out/launches_$m.csv python bench.py --steps 2 --warmup 3 --models $m \
         > gpurun_out/ncu_launch_$m.log 2>&1
     echo "ncu launches $m rc=$?"
@@ -33,7 +35,7 @@ ncufull)
   m=${NCU_MODEL:-resnet18}
   timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_full.log 2>&1 &&
   timeout 1500 ncu --set full --clock-control none --import-source on -k regex:conv_tc_kernel \
-      -s ${NCU_SKIP:-100} -c ${NCU_COUNT:-6} -o gpurun_out/prof_$m -f python bench.py --steps 2 --warmup 3 --models $m \
+      -s ${NCU_SKIP:-60} -c ${NCU_COUNT:-20} -o gpurun_out/prof_$m -f python bench.py --steps 2 --warmup 3 --models $m \
       > gpurun_out/ncu_full_$m.log 2>&1
   echo "ncu full $m rc=$?" ;;
 esac

@@ -127,8 +127,8 @@ struct PoolParams {
 };
 int launch_maxpool(const PoolParams& p, cudaStream_t st);
 int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
-                       const float* fc_w, const float* fc_b, float* logits_or_null, int32_t* idx,
-                       float* prob, cudaStream_t st);
+                       const float* fc_w, const float* fc_b, float* feats, float* logits,
+                       int32_t* idx, float* prob, cudaStream_t st);
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out_or_null,
                         int32_t* idx, float* prob, cudaStream_t st);
 
@@ -138,7 +138,7 @@ struct PreMeta {            // one per image, device resident
   int H, W;                 // source size
   int htab, vtab;           // offsets (in int32 units) of the resample tables in the table pool
 };
-enum { PRE_OUT_NCHW = 0, PRE_OUT_STEM = 1 };
+enum { PRE_OUT_NCHW = 0, PRE_OUT_STEM = 1, PRE_OUT_S2D4 = 2 };
 int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
                       int stem_ws, cudaStream_t st);

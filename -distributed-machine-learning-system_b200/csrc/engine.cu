@@ -84,6 +84,8 @@ struct idn_engine {
   // head
   const bf16* head_act = nullptr; Geom head_g; int head_C = 0;
   float* fc_w = nullptr; float* fc_b = nullptr;        // ResNet fp32 FC
+  float* feats = nullptr;                              // ResNet pooled features [cap][512] fp32
+  int pre_mode = PRE_OUT_STEM;
   float* logits_pad = nullptr;                         // AlexNet [cap][1024] fp32
   int64_t launches = 0;
   bool stem_simt = false;   // bring-up switch IDN_STEM_SIMT=1: run the two C=3 stem layers on the
@@ -403,6 +405,7 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
   if (!fw || !fb || br.left != 0) { set_error("resnet18: weight blob has the wrong size"); return IDN_EWEIGHTS; }
   IDN_TRY(dev_alloc(e, &e->fc_w, (size_t)1000 * 512, false));
   IDN_TRY(dev_alloc(e, &e->fc_b, 1000, false));
+  IDN_TRY(dev_alloc(e, &e->feats, (size_t)cap * 512));
   IDN_CUDA_TRY(cudaMemcpy(e->fc_w, fw, (size_t)1000 * 512 * 4, cudaMemcpyHostToDevice));
   IDN_CUDA_TRY(cudaMemcpy(e->fc_b, fb, 4000, cudaMemcpyHostToDevice));
   { Step st; st.kind = STEP_RHEAD; st.name = "avgpool+fc+softmax+top1"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
@@ -412,10 +415,14 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
 static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
   const int cap = e->cap;
   BlobReader br{blob, count};
-  e->stem_left = 2; e->stem_ws = 232;
-  bf16* xs = nullptr;
-  IDN_TRY(dev_alloc(e, &xs, (size_t)cap * IDN_CROP * e->stem_ws * 4 + 4096));
-  e->xs = xs;
+  // The 11x11 / stride-4 / pad-2 stem (tv:models/alexnet.py:22) runs as a 3x3 stride-1 convolution
+  // over the 4x4 space-to-depth image the preprocess kernel writes (57 x 57 pixels of 48+16
+  // channels, block origin at crop pixel (-2, -2) so the stem's padding is part of the layout):
+  // input row 4*oh - 2 + r with r = 4a + dy is s2d row oh + a, channel (dy*4+dx)*3 + c.
+  e->pre_mode = PRE_OUT_S2D4;
+  Act xs;
+  { Geom g; g.H = 55; g.W = 55; g.Hp = 57; g.Wp = 57; IDN_TRY(alloc_act(e, &xs, g, 64, cap)); }
+  e->xs = xs.ptr;
   { Step st; st.kind = STEP_PRE; st.name = "preprocess"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
   auto take2 = [&](size_t nw, size_t nb, const float** w, const float** b) -> int {
     *w = br.take(nw); *b = br.take(nb);
@@ -423,12 +430,22 @@ static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
     return IDN_OK;
   };
   const float *w, *b;
-  // features.0: 11x11 s4 p2 (tv:models/alexnet.py:22)
   ConvWeights w0;
   IDN_TRY(take2((size_t)64 * 3 * 121, 64, &w, &b));
-  IDN_TRY(upload_stem_weights(e, &w0, w, 64, 11, 11, nullptr, b));
+  {
+    std::vector<float> w2((size_t)64 * 64 * 9, 0.0f);
+    for (int n = 0; n < 64; ++n)
+      for (int c = 0; c < 3; ++c)
+        for (int r = 0; r < 11; ++r)
+          for (int s = 0; s < 11; ++s) {
+            const int a = r / 4, dy = r % 4, bb = s / 4, dx = s % 4, ch = (dy * 4 + dx) * 3 + c;
+            w2[(((size_t)n * 64 + ch) * 3 + a) * 3 + bb] = w[(((size_t)n * 3 + c) * 11 + r) * 11 + s];
+          }
+    IDN_TRY(upload_conv_weights(e, &w0, w2.data(), 64, 64, 3, 3, nullptr, b));
+  }
   Act c1; IDN_TRY(alloc_act(e, &c1, make_geom(55, 55, 0), 64, cap));
-  IDN_TRY(add_stem(e, "features.0+relu", xs, e->stem_ws, e->stem_left, w0, 11, 4, 2, 55, 55, c1, cap));
+  { ConvSpec s0; s0.R = 3; s0.S = 3; s0.pad = 0; s0.relu = true;
+    IDN_TRY(add_conv(e, "features.0+relu", xs, w0, s0, c1, nullptr, cap)); }
   Act p1; IDN_TRY(alloc_act(e, &p1, make_geom(27, 27, 2), 64, cap));
   add_pool(e, "features.2 maxpool", c1, p1, 0);
   // features.3: 5x5 p2, 64 -> 192
@@ -547,7 +564,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     }
     switch (s.kind) {
       case STEP_PRE:
-        IDN_TRY(launch_preprocess(d_imgs, e->d_meta, e->d_tables, e->d_lut, n, PRE_OUT_STEM, e->xs,
+        IDN_TRY(launch_preprocess(d_imgs, e->d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
                                   e->stem_left, e->stem_ws, st));
         break;
       case STEP_CONV: {
@@ -567,9 +584,9 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
         break;
       case STEP_RHEAD:
         IDN_TRY(launch_resnet_head(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,
-                                   e->head_g.W, e->head_C, e->fc_w, e->fc_b,
+                                   e->head_g.W, e->head_C, e->fc_w, e->fc_b, e->feats,
                                    d_logits ? d_logits : e->d_logits, d_idx, d_prob, st));
-        e->launches += 1;                       // avgpool+fc kernel, then softmax/top-1
+        e->launches += 2;                       // avgpool, fc, softmax/top-1
         break;
       case STEP_SOFTMAX:
         IDN_TRY(launch_softmax_top1(e->logits_pad, 1024, n, d_logits, d_idx, d_prob, st));

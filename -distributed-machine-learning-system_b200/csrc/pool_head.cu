@@ -109,39 +109,48 @@ int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out
 }
 
 // ---------------------------------------------------------------------------------- ResNet head
-// avgpool (tv:models/resnet.py:278) + fc (:280) in one kernel, softmax/top-1 (alexnet_resnet.py:80-84)
-// in the warp-shuffle kernel above.  The FC runs in fp32 on fp32 weights (1 MFLOP/image): the
-// last-layer rounding is what decides near-tie top-1s.
-// grid = (ceil(n / 16), 8): a CTA pools 16 images into shared memory (fp32) and computes 125 of the
-// 1000 classes for them; a warp owns a class at a time, lanes split K = 512 with 128-bit loads.
+// avgpool (tv:models/resnet.py:278) -> fp32 features, fc (:280) in fp32 on fp32 weights, then the
+// warp-shuffle softmax/top-1 kernel above (alexnet_resnet.py:80-84).  The FC stays fp32
+// (1 MFLOP/image): the last-layer rounding is what decides near-tie top-1s.
+__global__ void __launch_bounds__(256)
+avgpool_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W, int C,
+               float* __restrict__ feats) {
+  const int cpairs = C >> 1;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nimg * cpairs) return;
+  const int n = t / cpairs, cp = t - n * cpairs;
+  const uint32_t* base = reinterpret_cast<const uint32_t*>(act + ((long long)n * img_rows) * C) + cp;
+  float s0 = 0.0f, s1 = 0.0f;
+  for (int h = 0; h < H; ++h) {
+#pragma unroll 7
+    for (int w = 0; w < W; ++w) {
+      const uint32_t u = __ldg(base + (long long)(h * wp + w) * cpairs);
+      s0 += __uint_as_float(u << 16);
+      s1 += __uint_as_float(u & 0xffff0000u);
+    }
+  }
+  const float inv = 1.0f / (float)(H * W);
+  reinterpret_cast<float2*>(feats)[t] = make_float2(s0 * inv, s1 * inv);
+}
+
+// grid = (ceil(n / 16), 8): a CTA stages the features of 16 images in shared memory and computes
+// 125 of the 1000 classes for them; a warp owns two classes at a time, lanes split K with 128-bit loads.
 constexpr int kHeadImgs = 16;
 constexpr int kHeadChunks = 8;
 constexpr int kHeadClassesPerChunk = IDN_NUM_CLASSES / kHeadChunks;   // 125
 
 __global__ void __launch_bounds__(256)
-resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W, int C,
-                   const float* __restrict__ fc_w, const float* __restrict__ fc_b,
-                   float* __restrict__ logits) {
+fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __restrict__ fc_w,
+               const float* __restrict__ fc_b, float* __restrict__ logits) {
   extern __shared__ float feat[];             // [kHeadImgs][C]
   const int n0 = blockIdx.x * kHeadImgs;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const float inv = 1.0f / (float)(H * W);
-  const int cpairs = C >> 1;
-  for (int e = threadIdx.x; e < kHeadImgs * cpairs; e += blockDim.x) {
-    const int g = e / cpairs, cp = e - g * cpairs;
-    float s0 = 0.0f, s1 = 0.0f;
-    if (n0 + g < nimg) {
-      const uint32_t* base =
-          reinterpret_cast<const uint32_t*>(act + ((long long)(n0 + g) * img_rows) * C) + cp;
-      for (int h = 0; h < H; ++h)
-        for (int w = 0; w < W; ++w) {
-          const uint32_t u = __ldg(base + (long long)(h * wp + w) * cpairs);
-          s0 += __uint_as_float(u << 16);
-          s1 += __uint_as_float(u & 0xffff0000u);
-        }
-    }
-    feat[g * C + 2 * cp] = s0 * inv;
-    feat[g * C + 2 * cp + 1] = s1 * inv;
+  const int valid = min(kHeadImgs, nimg - n0);
+  for (int e = threadIdx.x; e < kHeadImgs * C / 4; e += blockDim.x) {
+    const int g = (e * 4) / C;
+    reinterpret_cast<float4*>(feat)[e] =
+        g < valid ? __ldg(reinterpret_cast<const float4*>(feats + (long long)n0 * C) + e)
+                  : make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncthreads();
   const int j0 = blockIdx.y * kHeadClassesPerChunk;
@@ -151,6 +160,7 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
 #pragma unroll
     for (int g = 0; g < kHeadImgs; ++g) acc[g] = 0.0f;
     const float* wr = fc_w + (long long)j * C;
+#pragma unroll 4
     for (int c = lane * 4; c < C; c += 128) {
       const float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + c));
 #pragma unroll
@@ -170,18 +180,21 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
     const float b = __ldg(fc_b + j);
 #pragma unroll
     for (int g = 0; g < kHeadImgs; ++g)
-      if (lane == g && n0 + g < nimg) logits[(long long)(n0 + g) * IDN_NUM_CLASSES + j] = acc[g] + b;
+      if (lane == g && g < valid) logits[(long long)(n0 + g) * IDN_NUM_CLASSES + j] = acc[g] + b;
   }
 }
 
 int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
-                       const float* fc_w, const float* fc_b, float* logits, int32_t* idx,
-                       float* prob, cudaStream_t st) {
+                       const float* fc_w, const float* fc_b, float* feats, float* logits,
+                       int32_t* idx, float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  if (C % 128 != 0 || logits == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
+  if (C % 128 != 0 || logits == nullptr || feats == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
+  const int items = nimg * (C / 2);
+  avgpool_kernel<<<(items + 255) / 256, 256, 0, st>>>(act, nimg, img_rows, wp, H, W, C, feats);
+  IDN_CUDA_TRY(cudaGetLastError());
   const size_t smem = (size_t)kHeadImgs * C * sizeof(float);
   dim3 grid((nimg + kHeadImgs - 1) / kHeadImgs, kHeadChunks);
-  resnet_head_kernel<<<grid, 256, smem, st>>>(act, nimg, img_rows, wp, H, W, C, fc_w, fc_b, logits);
+  fc_fp32_kernel<<<grid, 256, smem, st>>>(feats, nimg, C, fc_w, fc_b, logits);
   IDN_CUDA_TRY(cudaGetLastError());
   return launch_softmax_top1(logits, IDN_NUM_CLASSES, nimg, nullptr, idx, prob, st);
 }

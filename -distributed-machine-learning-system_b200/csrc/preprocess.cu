@@ -93,61 +93,210 @@ void build_axis_table(int in_size, int out_size, int crop_off, std::string* out)
 
 __device__ __forceinline__ int clip8(int v) { return v < 0 ? 0 : (v > 255 ? 255 : v); }
 
-// One CTA = one output row y of one image; thread x < 224 = one output pixel (3 channels).
-// grid = (224, n).  Threads 224..231 write the stem layout's horizontal zero padding.
+// ---------------------------------------------------------------------------------------------
+// One CTA = kPreRows consecutive output rows of one image.
+//   1. stage the source rows those outputs touch into shared memory (coalesced 32-bit loads);
+//   2. horizontal pass: thread x owns output column x, keeps its <= 4 coefficients in registers,
+//      reads its 3*xn source bytes as aligned words + funnel shifts -> uint8 RGBx in smem;
+//   3. vertical pass over the uint8 intermediate (Pillow's order) -> uint8 RGBx tile in smem;
+//   4. writer: normalise through the 768-entry bf16 table and store 128 bits at a time in one of
+//      three layouts: planar NCHW (public entry point), 4-channel NHWC with the stem's left pad
+//      (ResNet18 stem image), or the 4x4 space-to-depth image AlexNet's stem reads (57x57x64).
+// Source tiles that do not fit (huge downscales) take the direct per-pixel path of step 2+3; the
+// arithmetic is the same integer arithmetic either way.
+// ---------------------------------------------------------------------------------------------
+constexpr int kPreRows = 8;
+constexpr int kPreMaxSrcRows = 26;
+constexpr int kPreRawWords = 9 * 1024;                  // 36 KiB of staged source bytes
+constexpr int kPreSmemBytes = (kPreRawWords + kPreMaxSrcRows * IDN_CROP + kPreRows * IDN_CROP) * 4 + 768 * 2;
+
+__device__ __forceinline__ void pre_direct_pixel(const uint8_t* __restrict__ src, int W,
+                                                 const int* __restrict__ ht, const int* __restrict__ vt,
+                                                 int x, int y, int out3[3]) {
+  const int hks = ht[0], vks = vt[0];
+  const int x0 = ht[1 + x], xn = ht[1 + IDN_CROP + x];
+  const int* hk = ht + 1 + 2 * IDN_CROP + x * hks;
+  const int y0 = vt[1 + y], yn = vt[1 + IDN_CROP + y];
+  const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
+  int acc[3] = {1 << 21, 1 << 21, 1 << 21};
+  for (int j = 0; j < yn; ++j) {
+    const uint8_t* rowp = src + ((long long)(y0 + j) * W + x0) * 3;
+    int h0 = 1 << 21, h1 = 1 << 21, h2 = 1 << 21;
+    for (int i = 0; i < xn; ++i) {
+      const int k = __ldg(hk + i);
+      h0 += (int)__ldg(rowp + 3 * i + 0) * k;
+      h1 += (int)__ldg(rowp + 3 * i + 1) * k;
+      h2 += (int)__ldg(rowp + 3 * i + 2) * k;
+    }
+    const int kv = __ldg(vk + j);
+    acc[0] += clip8(h0 >> 22) * kv;
+    acc[1] += clip8(h1 >> 22) * kv;
+    acc[2] += clip8(h2 >> 22) * kv;
+  }
+  out3[0] = clip8(acc[0] >> 22); out3[1] = clip8(acc[1] >> 22); out3[2] = clip8(acc[2] >> 22);
+}
+
 template <int OUT_MODE>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ meta,
                   const int* __restrict__ tables, const uint16_t* __restrict__ lut, void* out,
                   int left_pad, int ws) {
-  __shared__ uint16_t s_lut[768];
-  for (int i = threadIdx.x; i < 768; i += blockDim.x) s_lut[i] = lut[i];
-  __syncthreads();
-  const int y = blockIdx.x, n = blockIdx.y, x = threadIdx.x;
+  extern __shared__ uint32_t sm[];
+  uint32_t* s_raw = sm;                                        // staged source bytes
+  uint32_t* s_h = sm + kPreRawWords;                           // [src rows][224] RGBx after pass 1
+  uint32_t* s_out = s_h + kPreMaxSrcRows * IDN_CROP;           // [kPreRows][224] RGBx resized tile
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_out + kPreRows * IDN_CROP);
+  const int tid = threadIdx.x, n = blockIdx.y;
+  for (int i = tid; i < 768; i += blockDim.x) s_lut[i] = lut[i];
   const PreMeta m = meta[n];
-  if (x < IDN_CROP) {
-    const int* ht = tables + m.htab;
-    const int* vt = tables + m.vtab;
+  const int* ht = tables + m.htab;
+  const int* vt = tables + m.vtab;
+  const uint8_t* src = imgs + m.offset;
+  // rows of the 224x224 crop this CTA produces; S2D4 tiles are shifted by the stem's padding (2)
+  const int ybase = OUT_MODE == PRE_OUT_S2D4 ? kPreRows * (int)blockIdx.x - 2 : kPreRows * (int)blockIdx.x;
+  const int ylo = ybase < 0 ? 0 : ybase;
+  const int yhi = ybase + kPreRows > IDN_CROP ? IDN_CROP : ybase + kPreRows;   // exclusive
+
+  if (ylo < yhi) {
     const int hks = ht[0], vks = vt[0];
-    const int x0 = ht[1 + x], xn = ht[1 + IDN_CROP + x];
-    const int* hk = ht + 1 + 2 * IDN_CROP + x * hks;
-    const int y0 = vt[1 + y], yn = vt[1 + IDN_CROP + y];
-    const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
-    const uint8_t* src = imgs + m.offset;
-    int acc[3] = {1 << 21, 1 << 21, 1 << 21};
-    for (int j = 0; j < yn; ++j) {
-      const uint8_t* rowp = src + ((long long)(y0 + j) * m.W + x0) * 3;
-      int h0 = 1 << 21, h1 = 1 << 21, h2 = 1 << 21;
-      for (int i = 0; i < xn; ++i) {
-        const int k = __ldg(hk + i);
-        h0 += (int)__ldg(rowp + 3 * i + 0) * k;
-        h1 += (int)__ldg(rowp + 3 * i + 1) * k;
-        h2 += (int)__ldg(rowp + 3 * i + 2) * k;
+    const int ys0 = vt[1 + ylo];
+    const int ys1 = vt[1 + yhi - 1] + vt[1 + IDN_CROP + yhi - 1];              // exclusive
+    const int nrows = ys1 - ys0;
+    const int c0 = ht[1], c1 = ht[1 + IDN_CROP - 1] + ht[1 + 2 * IDN_CROP - 1];
+    const int rowbytes = (c1 - c0) * 3;
+    const int pitchw = (rowbytes + 3) / 4 + 4;                                  // words per staged row
+    const bool tiled = hks <= 4 && nrows <= kPreMaxSrcRows && nrows * pitchw <= kPreRawWords;
+    if (tiled) {
+      // ---- 1. stage source rows (word r*pitchw + w holds bytes of the 4-aligned word that
+      //         contains the row's first needed byte, onwards)
+      for (int r = 0; r < nrows; ++r) {
+        const uint8_t* g = src + ((long long)(ys0 + r) * m.W + c0) * 3;
+        const int shift = (int)(reinterpret_cast<uintptr_t>(g) & 3);
+        const uint8_t* g0 = g - shift;
+        const int nw = (shift + rowbytes + 3) >> 2;
+        for (int w = tid; w < nw; w += blockDim.x) {
+          uint32_t v;
+          if (w == 0 || w == nw - 1) {          // edge words: only touch bytes inside the row
+            v = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+              const int off = 4 * w + b - shift;
+              if (off >= 0 && off < rowbytes) v |= (uint32_t)__ldg(g + off) << (8 * b);
+            }
+          } else {
+            v = __ldg(reinterpret_cast<const uint32_t*>(g0) + w);
+          }
+          s_raw[r * pitchw + w] = v;
+        }
       }
-      const int kv = __ldg(vk + j);
-      acc[0] += clip8(h0 >> 22) * kv;
-      acc[1] += clip8(h1 >> 22) * kv;
-      acc[2] += clip8(h2 >> 22) * kv;
+      __syncthreads();
+      // ---- 2. horizontal pass
+      if (tid < IDN_CROP) {
+        const int x = tid;
+        const int x0 = ht[1 + x], xn = ht[1 + IDN_CROP + x];
+        const int* hk = ht + 1 + 2 * IDN_CROP + x * hks;
+        int k[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) k[i] = (i < xn) ? __ldg(hk + i) : 0;
+        for (int r = 0; r < nrows; ++r) {
+          const uint8_t* g = src + ((long long)(ys0 + r) * m.W + c0) * 3;
+          const int bstart = (int)(reinterpret_cast<uintptr_t>(g) & 3) + (x0 - c0) * 3;
+          const uint32_t* wp = s_raw + r * pitchw + (bstart >> 2);
+          const int sh = (bstart & 3) * 8;
+          const uint32_t a = wp[0], b = wp[1], c = wp[2], d = wp[3];
+          const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
+                         p2 = __funnelshift_r(c, d, sh);           // 12 bytes = 4 RGB pixels
+          int h0 = 1 << 21, h1 = 1 << 21, h2 = 1 << 21;
+          h0 += (int)(p0 & 255) * k[0];         h1 += (int)((p0 >> 8) & 255) * k[0];  h2 += (int)((p0 >> 16) & 255) * k[0];
+          h0 += (int)(p0 >> 24) * k[1];         h1 += (int)(p1 & 255) * k[1];         h2 += (int)((p1 >> 8) & 255) * k[1];
+          h0 += (int)((p1 >> 16) & 255) * k[2]; h1 += (int)(p1 >> 24) * k[2];         h2 += (int)(p2 & 255) * k[2];
+          h0 += (int)((p2 >> 8) & 255) * k[3];  h1 += (int)((p2 >> 16) & 255) * k[3]; h2 += (int)(p2 >> 24) * k[3];
+          s_h[r * IDN_CROP + x] = (uint32_t)clip8(h0 >> 22) | ((uint32_t)clip8(h1 >> 22) << 8) |
+                                  ((uint32_t)clip8(h2 >> 22) << 16);
+        }
+      }
+      __syncthreads();
+      // ---- 3. vertical pass
+      if (tid < IDN_CROP) {
+        const int x = tid;
+        for (int y = ylo; y < yhi; ++y) {
+          const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
+          const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
+          int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+          for (int j = 0; j < yn; ++j) {
+            const uint32_t p = s_h[(y0 + j) * IDN_CROP + x];
+            const int kv = __ldg(vk + j);
+            a0 += (int)(p & 255) * kv; a1 += (int)((p >> 8) & 255) * kv; a2 += (int)((p >> 16) & 255) * kv;
+          }
+          s_out[(y - ybase) * IDN_CROP + x] = (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) |
+                                              ((uint32_t)clip8(a2 >> 22) << 16);
+        }
+      }
+    } else if (tid < IDN_CROP) {
+      for (int y = ylo; y < yhi; ++y) {
+        int o[3];
+        pre_direct_pixel(src, m.W, ht, vt, tid, y, o);
+        s_out[(y - ybase) * IDN_CROP + tid] = (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16);
+      }
     }
-    const uint16_t r = s_lut[clip8(acc[0] >> 22)];
-    const uint16_t g = s_lut[256 + clip8(acc[1] >> 22)];
-    const uint16_t b = s_lut[512 + clip8(acc[2] >> 22)];
-    if (OUT_MODE == PRE_OUT_NCHW) {
-      uint16_t* o = reinterpret_cast<uint16_t*>(out) + (long long)n * 3 * IDN_CROP * IDN_CROP +
-                    (long long)y * IDN_CROP + x;
-      o[0] = r;
-      o[IDN_CROP * IDN_CROP] = g;
-      o[2 * IDN_CROP * IDN_CROP] = b;
-    } else {
-      uint2* o = reinterpret_cast<uint2*>(out) + ((long long)n * IDN_CROP + y) * ws + left_pad + x;
-      *o = make_uint2((uint32_t)r | ((uint32_t)g << 16), (uint32_t)b);
+  }
+  __syncthreads();
+
+  // ---- 4. writers (128-bit stores)
+  auto norm = [&](int yy, int x, int c) -> uint32_t {     // bf16 bits of channel c at tile row yy
+    return (uint32_t)s_lut[c * 256 + ((s_out[yy * IDN_CROP + x] >> (8 * c)) & 255)];
+  };
+  if (OUT_MODE == PRE_OUT_NCHW) {
+    uint16_t* o = reinterpret_cast<uint16_t*>(out) + (long long)n * 3 * IDN_CROP * IDN_CROP;
+    const int nrow = yhi - ylo;
+    for (int it = tid; it < 3 * nrow * (IDN_CROP / 8); it += blockDim.x) {
+      const int xq = it % (IDN_CROP / 8);
+      const int yy = (it / (IDN_CROP / 8)) % nrow;
+      const int c = it / ((IDN_CROP / 8) * nrow);
+      uint32_t w[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        w[e] = norm(yy, xq * 8 + 2 * e, c) | (norm(yy, xq * 8 + 2 * e + 1, c) << 16);
+      *reinterpret_cast<uint4*>(o + ((long long)c * IDN_CROP + ylo + yy) * IDN_CROP + xq * 8) =
+          make_uint4(w[0], w[1], w[2], w[3]);
     }
   } else if (OUT_MODE == PRE_OUT_STEM) {
-    const int padpx = x - IDN_CROP;               // 0 .. ws-224-1
-    if (padpx < ws - IDN_CROP) {
-      const int px = padpx < left_pad ? padpx : IDN_CROP + padpx;
-      uint2* o = reinterpret_cast<uint2*>(out) + ((long long)n * IDN_CROP + y) * ws + px;
-      *o = make_uint2(0u, 0u);
+    uint4* o = reinterpret_cast<uint4*>(out);
+    const int pairs = ws >> 1, nrow = yhi - ylo;
+    for (int it = tid; it < nrow * pairs; it += blockDim.x) {
+      const int pr = it % pairs, yy = it / pairs;
+      uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int x = 2 * pr + e - left_pad;
+        if (x >= 0 && x < IDN_CROP) {
+          w[2 * e] = norm(yy, x, 0) | (norm(yy, x, 1) << 16);
+          w[2 * e + 1] = norm(yy, x, 2);
+        }
+      }
+      o[((long long)n * IDN_CROP + ylo + yy) * pairs + pr] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  } else {   // PRE_OUT_S2D4: pixel (by, bx) = 4x4 block of crop pixels starting at (4by-2, 4bx-2),
+             // channel (dy*4+dx)*3+c, 48..63 zero; image = 57 x 57 pixels of 64 channels
+    uint4* o = reinterpret_cast<uint4*>(out);
+    const int by0 = 2 * (int)blockIdx.x;
+    for (int it = tid; it < 2 * 57 * 8; it += blockDim.x) {
+      const int j = it & 7, bx = (it >> 3) % 57, byl = it / (8 * 57);
+      if (by0 + byl >= 57) continue;
+      uint32_t w[4] = {0u, 0u, 0u, 0u};
+      if (j < 6) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int e = 8 * j + i;
+          const int dy = e / 12, rem = e - 12 * dy, dx = rem / 3, c = rem - 3 * dx;
+          const int yy = 4 * byl + dy;                 // tile row (ybase + yy is the crop row)
+          const int x = 4 * bx - 2 + dx;
+          uint32_t v = 0;
+          if (ybase + yy >= 0 && ybase + yy < IDN_CROP && x >= 0 && x < IDN_CROP) v = norm(yy, x, c);
+          w[i >> 1] |= v << (16 * (i & 1));
+        }
+      }
+      o[(((long long)n * 57 + by0 + byl) * 57 + bx) * 8 + j] = make_uint4(w[0], w[1], w[2], w[3]);
     }
   }
 }
@@ -156,16 +305,23 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
                       int stem_ws, cudaStream_t st) {
   if (n <= 0) return IDN_OK;
-  if (out_mode == PRE_OUT_STEM && stem_ws - IDN_CROP > 32) {
-    set_error("preprocess: stem row pitch too wide");
+  if (out_mode == PRE_OUT_STEM && (stem_ws & 1)) {
+    set_error("preprocess: stem row pitch must be even");
     return IDN_EINVAL;
   }
-  dim3 grid(IDN_CROP, n);
-  if (out_mode == PRE_OUT_NCHW)
-    preprocess_kernel<PRE_OUT_NCHW><<<grid, 256, 0, st>>>(d_imgs, d_meta, d_tables, d_lut, out, 0, 0);
-  else
-    preprocess_kernel<PRE_OUT_STEM><<<grid, 256, 0, st>>>(d_imgs, d_meta, d_tables, d_lut, out,
-                                                         stem_left_pad, stem_ws);
+  if (out_mode == PRE_OUT_NCHW) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_NCHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPreSmemBytes));
+    preprocess_kernel<PRE_OUT_NCHW><<<dim3(IDN_CROP / kPreRows, n), 256, kPreSmemBytes, st>>>(
+        d_imgs, d_meta, d_tables, d_lut, out, 0, 0);
+  } else if (out_mode == PRE_OUT_STEM) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_STEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPreSmemBytes));
+    preprocess_kernel<PRE_OUT_STEM><<<dim3(IDN_CROP / kPreRows, n), 256, kPreSmemBytes, st>>>(
+        d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws);
+  } else {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPreSmemBytes));
+    preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, kPreSmemBytes, st>>>(
+        d_imgs, d_meta, d_tables, d_lut, out, 0, 0);
+  }
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }

@@ -102,12 +102,24 @@ struct ConvParams {
   int ktot;                   // elements per B row (= num_taps * c_blocks * 64)
   int st_stride, st_ws, st_h, st_ow, st_nrow;   // stem image: conv stride, row pitch (px), rows,
                                                 // window starts per row, row groups per image
+  // halo kernel (conv_halo_kernel): one staged A tile per 64-channel block serves every tap
+  int halo_lo;                // smallest tap offset (rows)
+  int halo_r1, halo_r2;       // rows of the two TMA boxes that make up the staged tile (r2 may be 0)
+  int a_stage_bytes;          // (r1 + r2) * 128 rounded up to 1024
+  int a_stages, b_stages;     // ring depths chosen by the host from the shared-memory budget
+  int msub;                   // 128-row sub-tiles per work item (1 or 2)
 };
 
 // launchers (conv_tc.cu / conv_simt.cu)
 int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int block_n,
                    int num_sms, cudaStream_t st);
 int launch_conv_simt(const ConvParams& p, cudaStream_t st);
+// Chooses the halo-kernel configuration for a stride-1 multi-tap convolution; returns false when
+// the layer should stay on conv_tc_kernel.  Fills p.halo_* / stages / msub, *block_n, *b_resident.
+bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sms, int* block_n,
+                    bool* b_resident);
+int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                     const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st);
 int read_tc_watchdog();
 int conv_tc_configure();   // cudaFuncSetAttribute for every instantiation; once per process/device
 
@@ -141,7 +153,8 @@ struct PreMeta {            // one per image, device resident
 enum { PRE_OUT_NCHW = 0, PRE_OUT_STEM = 1, PRE_OUT_S2D4 = 2 };
 int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
-                      int stem_ws, cudaStream_t st);
+                      int stem_ws, int raw_words, int src_rows, cudaStream_t st);
+void preprocess_tile_need(const int* htab, const int* vtab, int* raw_words, int* src_rows);
 // Builds the resample table (Pillow fixed point) of the 224 cropped outputs of one axis.
 void build_axis_table(int in_size, int out_size, int crop_off, std::string* ints /* int32 bytes */);
 void resized_size(int h, int w, int* nh, int* nw);

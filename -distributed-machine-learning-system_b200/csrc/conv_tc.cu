@@ -20,6 +20,9 @@
 // 16-pixel (64-element, 128-byte) window, dim1 steps by `stride` pixels (16/32 bytes) per output
 // column, dim2 is the row phase, dim3 the row group (OOB rows = zero padding), dim4 the image.
 // One k-block per filter row; window positions beyond the filter width meet zero weights.
+#include <algorithm>
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace idn {
@@ -229,6 +232,66 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// TMEM accumulator rows -> scale/shift (+residual) (+ReLU) -> bf16 / fp32, 32 columns at a time.
+// Every lane of the warp must call it (tcgen05.ld is warp-collective); stores are predicated.
+template <int BLOCK_N>
+__device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
+                                          int col0) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+    uint32_t v[32];
+    ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, v);
+    ptx::tmem_ld_wait();
+    if (ri.valid) {
+      const int col = col0 + c0;
+      const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
+      const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
+      float y[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 s4 = __ldg(sc + j), b4 = __ldg(sh + j);
+        y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4.x, b4.x);
+        y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4.y, b4.y);
+        y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4.z, b4.z);
+        y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4.w, b4.w);
+      }
+      if (p.residual != nullptr) {
+        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + ri.res_row * p.ldc + col);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint4 rr = __ldg(rp + j);
+          const uint32_t w4[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            y[8 * j + 2 * e + 0] += __uint_as_float(w4[e] << 16);
+            y[8 * j + 2 * e + 1] += __uint_as_float(w4[e] & 0xffff0000u);
+          }
+        }
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], 0.0f);
+      }
+      if (p.out_f32) {
+        float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
+                                               ri.dst_row * p.ldc + col);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          op[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+      } else {
+        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) +
+                                             ri.dst_row * p.ldc + col);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          op[j] = make_uint4(pack_bf16x2(y[8 * j + 0], y[8 * j + 1]),
+                             pack_bf16x2(y[8 * j + 2], y[8 * j + 3]),
+                             pack_bf16x2(y[8 * j + 4], y[8 * j + 5]),
+                             pack_bf16x2(y[8 * j + 6], y[8 * j + 7]));
+      }
+    }
+  }
+}
+
 template <int BLOCK_N, int MODE>
 __global__ void __launch_bounds__(256, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -356,59 +419,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-#pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, v);
-        ptx::tmem_ld_wait();
-        if (ri.valid) {
-          const int col = n_tile * BLOCK_N + c0;
-          const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
-          const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
-          float y[32];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 s4 = __ldg(sc + j), b4 = __ldg(sh + j);
-            y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4.x, b4.x);
-            y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4.y, b4.y);
-            y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4.z, b4.z);
-            y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4.w, b4.w);
-          }
-          if (p.residual != nullptr) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + ri.res_row * p.ldc + col);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint4 rr = __ldg(rp + j);
-              const uint32_t w4[4] = {rr.x, rr.y, rr.z, rr.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                y[8 * j + 2 * e + 0] += __uint_as_float(w4[e] << 16);
-                y[8 * j + 2 * e + 1] += __uint_as_float(w4[e] & 0xffff0000u);
-              }
-            }
-          }
-          if (p.relu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], 0.0f);
-          }
-          if (p.out_f32) {
-            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
-                                                   ri.dst_row * p.ldc + col);
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              op[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
-          } else {
-            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) +
-                                                 ri.dst_row * p.ldc + col);
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              op[j] = make_uint4(pack_bf16x2(y[8 * j + 0], y[8 * j + 1]),
-                                 pack_bf16x2(y[8 * j + 2], y[8 * j + 3]),
-                                 pack_bf16x2(y[8 * j + 4], y[8 * j + 5]),
-                                 pack_bf16x2(y[8 * j + 6], y[8 * j + 7]));
-          }
-        }
-      }
+      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
@@ -421,6 +432,203 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 2) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+// =============================================================================================
+// conv_halo_kernel: stride-1 multi-tap convolutions with operand reuse.
+//
+// conv_tc_kernel re-fetches a 128 x 64 A box for every filter tap and streams the whole weight
+// matrix once per 128 output rows: measured on B200 it saturates the L2 -> SM fabric (about 42
+// bytes/clk/SM) at 20-40 % tensor-pipe utilisation.  This kernel loads, per 64-channel block, ONE
+// staged A tile that covers the 128*MSUB output rows of the work item plus the halo of every tap
+// (rows [q0 + min_off, q0 + 128*MSUB + max_off]) and issues every tap's MMAs from it by moving the
+// descriptor's start address (a tap is a row offset; the 128B swizzle is a function of the shared
+// memory address, so a start address at any 128-byte row works -- verified on hardware with
+// tools/exp_base_offset.cu).  Weights are either resident in shared memory for the whole kernel
+// (Cin = Cout = 64 layers: 72 KiB) or streamed through their own ring and reused by MSUB
+// sub-tiles, which halves the weight traffic per output row.
+//   warp 0 = A producer, warp 3 = B producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
+//   warps 4..7 = epilogue; accumulators: 2 stages x MSUB sub-tiles x BLOCK_N TMEM columns.
+// =============================================================================================
+constexpr int kMaxAStages = 4;
+constexpr int kMaxBStages = 16;
+
+template <int BLOCK_N, int MSUB, bool BRES>
+__global__ void __launch_bounds__(256, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
+  constexpr int B_BYTES = BLOCK_N * kBlockK * 2;
+  constexpr int ACC_COLS = MSUB * BLOCK_N;
+  constexpr int TMEM_COLS = 2 * ACC_COLS <= 128 ? 128 : 2 * ACC_COLS <= 256 ? 256 : 512;
+  static_assert(2 * ACC_COLS <= 512, "accumulators exceed TMEM");
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+  const int k_total = p.num_taps * p.c_blocks;
+  const uint32_t a_base = base;
+  const uint32_t b_base = a_base + (uint32_t)(p.a_stages * p.a_stage_bytes);
+  const uint32_t bar_base = b_base + (uint32_t)((BRES ? k_total : p.b_stages) * B_BYTES);
+  auto a_full = [&](int s) { return bar_base + 8u * s; };
+  auto a_empty = [&](int s) { return bar_base + 8u * (kMaxAStages + s); };
+  auto b_full = [&](int s) { return bar_base + 8u * (2 * kMaxAStages + s); };
+  auto b_empty = [&](int s) { return bar_base + 8u * (2 * kMaxAStages + kMaxBStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 2 + a); };
+  const uint32_t bres_bar = bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 4);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 5);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_items = p.num_m_tiles * p.num_n_tiles;     // num_m_tiles counts 128*MSUB-row items
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA1);
+    ptx::prefetch_tmap(&tmA2);
+    ptx::prefetch_tmap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kMaxAStages; ++s) { ptx::mbar_init(a_full(s), 1); ptx::mbar_init(a_empty(s), 1); }
+    for (int s = 0; s < kMaxBStages; ++s) { ptx::mbar_init(b_full(s), 1); ptx::mbar_init(b_empty(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 4); }
+    ptx::mbar_init(bres_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ================================ A producer =================================
+    if (lane == 0) {
+      int sa = 0;
+      uint32_t pha = 0;
+      bool alive = true;
+      const uint32_t a_bytes = (uint32_t)(p.halo_r1 + p.halo_r2) * 128u;
+      for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
+        const int m_item = item / p.num_n_tiles;
+        const int row0 = m_item * (kBlockM * MSUB) + p.halo_lo;
+        for (int cb = 0; cb < p.c_blocks; ++cb) {
+          if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb)) { alive = false; break; }
+          const uint32_t dst = a_base + (uint32_t)(sa * p.a_stage_bytes);
+          ptx::mbar_expect_tx(a_full(sa), a_bytes);
+          ptx::tma_load_2d(dst, &tmA1, a_full(sa), cb * kBlockK, row0);
+          if (p.halo_r2 > 0)
+            ptx::tma_load_2d(dst + (uint32_t)p.halo_r1 * 128u, &tmA2, a_full(sa), cb * kBlockK,
+                             row0 + p.halo_r1);
+          if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 3) {
+    // ================================ B producer =================================
+    if (lane == 0) {
+      if (BRES) {
+        ptx::mbar_expect_tx(bres_bar, (uint32_t)(k_total * B_BYTES));
+        for (int kb = 0; kb < k_total; ++kb)
+          ptx::tma_load_2d(b_base + (uint32_t)(kb * B_BYTES), &tmB, bres_bar, kb * kBlockK, 0);
+      } else {
+        int sb = 0;
+        uint32_t phb = 0;
+        bool alive = true;
+        for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
+          const int n_tile = item % p.num_n_tiles;
+          for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
+            for (int tap = 0; tap < p.num_taps; ++tap) {
+              if (!mbar_wait(b_empty(sb), phb ^ 1u, 4, tap)) { alive = false; break; }
+              ptx::mbar_expect_tx(b_full(sb), B_BYTES);
+              ptx::tma_load_2d(b_base + (uint32_t)(sb * B_BYTES), &tmB, b_full(sb),
+                               (tap * p.c_blocks + cb) * kBlockK, n_tile * BLOCK_N);
+              if (++sb == p.b_stages) { sb = 0; phb ^= 1u; }
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    constexpr uint32_t idesc = make_idesc(kBlockM, BLOCK_N);
+    int sa = 0, sb = 0, as = 0;
+    uint32_t pha = 0, phb = 0, aph = 0;
+    bool alive = true;
+    if (BRES) alive = mbar_wait(bres_bar, 0u, 5, 0);
+    for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, item)) break;
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * ACC_COLS);
+      for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
+        if (!mbar_wait(a_full(sa), pha, 2, cb)) { alive = false; break; }
+        ptx::tc_fence_after();
+        const uint32_t a_tile = a_base + (uint32_t)(sa * p.a_stage_bytes);
+        for (int tap = 0; tap < p.num_taps; ++tap) {
+          uint32_t b_tile;
+          if (BRES) {
+            b_tile = b_base + (uint32_t)((tap * p.c_blocks + cb) * B_BYTES);
+          } else {
+            if (!mbar_wait(b_full(sb), phb, 6, tap)) { alive = false; break; }
+            ptx::tc_fence_after();
+            b_tile = b_base + (uint32_t)(sb * B_BYTES);
+          }
+          if (lane == 0) {
+            const uint64_t db = make_sw128_desc(b_tile);
+            const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
+#pragma unroll
+            for (int sub = 0; sub < MSUB; ++sub) {
+              const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k)
+                ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
+                               db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+            }
+            if (!BRES) ptx::umma_commit(b_empty(sb));
+          }
+          __syncwarp();
+          if (!BRES) { if (++sb == p.b_stages) { sb = 0; phb ^= 1u; } }
+        }
+        if (lane == 0 && alive) {
+          ptx::umma_commit(a_empty(sa));
+          if (cb == p.c_blocks - 1) ptx::umma_commit(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
+      }
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue ====================================
+    const int ew = warp - 4;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+      const int m_item = item / p.num_n_tiles;
+      const int n_tile = item - m_item * p.num_n_tiles;
+      if (!mbar_wait(tfull_bar(as), aph, 3, item)) break;
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int sub = 0; sub < MSUB; ++sub) {
+        const RowInfo ri = decode_row(p, m_item * MSUB + sub, ew * 32 + lane);
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) +
+                               (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
+        epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
   }
 }
 
@@ -553,6 +761,76 @@ int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int conv_stride, int w
     return IDN_ECUDA;
   }
   return IDN_OK;
+}
+
+// ----------------------------------------------------------------------------- halo kernel host
+constexpr int kSmemBudget = 232448 - 1024 - 1024;     // max dynamic smem minus alignment and barriers
+
+bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sms, int* block_n,
+                    bool* b_resident) {
+  if (p->mode != MODE_FLAT || p->num_taps < 2) return false;
+  if (const char* v = std::getenv("IDN_NO_HALO")) { if (v[0] == '1') return false; }
+  int lo = p->tap_off[0], hi = p->tap_off[0];
+  for (int t = 1; t < p->num_taps; ++t) { lo = std::min(lo, p->tap_off[t]); hi = std::max(hi, p->tap_off[t]); }
+  const int span = (hi - lo + 7) / 8 * 8;
+  if (span > 128) return false;                       // parity-plane (stride-2) taps and the like
+  int bn = 0;
+  bool res = false;
+  const int k_total = p->num_taps * p->c_blocks;
+  if (n_total == 64) { bn = 64; res = (k_total * 64 * 128) <= 80 * 1024; }
+  else if (n_total % 128 == 0) bn = 128;
+  else if (n_total % 96 == 0) bn = 96;
+  else return false;
+  if (bn == 64 && !res) return false;
+  const int msub = 2;
+  const int total_rows = kBlockM * msub + span;
+  p->msub = msub;
+  p->halo_lo = lo;
+  p->halo_r1 = total_rows <= 256 ? total_rows : 256;
+  p->halo_r2 = total_rows - p->halo_r1;
+  p->a_stage_bytes = (total_rows * 128 + 1023) / 1024 * 1024;
+  const int b_bytes = bn * 128;
+  if (res) {
+    const int left = kSmemBudget - k_total * b_bytes;
+    p->a_stages = std::min(kMaxAStages, left / p->a_stage_bytes);
+    p->b_stages = 0;
+    if (p->a_stages < 2) return false;
+  } else {
+    p->a_stages = 3;
+    int left = kSmemBudget - p->a_stages * p->a_stage_bytes;
+    if (left / b_bytes < 4) { p->a_stages = 2; left = kSmemBudget - 2 * p->a_stage_bytes; }
+    p->b_stages = std::min(kMaxBStages, left / b_bytes);
+    if (p->b_stages < 3) return false;
+  }
+  (void)m_rows_cap; (void)num_sms;
+  *block_n = bn;
+  *b_resident = res;
+  return true;
+}
+
+template <int BLOCK_N, int MSUB, bool BRES>
+static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                           const ConvParams& p, int num_sms, cudaStream_t st) {
+  const int total = p.num_m_tiles * p.num_n_tiles;
+  if (total <= 0) return IDN_OK;
+  const int k_total = p.num_taps * p.c_blocks;
+  const int smem = p.a_stages * p.a_stage_bytes + (BRES ? k_total : p.b_stages) * BLOCK_N * 128 + 1024 + 1024;
+  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, MSUB, BRES>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int grid = total < num_sms ? total : num_sms;
+  conv_halo_kernel<BLOCK_N, MSUB, BRES><<<grid, 256, smem, st>>>(tmA1, tmA2, tmB, p);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
+int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                     const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st) {
+  if (p.msub != 2) { set_error("launch_conv_halo: msub"); return IDN_EINVAL; }
+  if (block_n == 64 && b_resident) return launch_halo_one<64, 2, true>(tmA1, tmA2, tmB, p, num_sms, st);
+  if (block_n == 128 && !b_resident) return launch_halo_one<128, 2, false>(tmA1, tmA2, tmB, p, num_sms, st);
+  if (block_n == 96 && !b_resident) return launch_halo_one<96, 2, false>(tmA1, tmA2, tmB, p, num_sms, st);
+  set_error("launch_conv_halo: unsupported configuration");
+  return IDN_EINVAL;
 }
 
 }  // namespace idn

@@ -45,9 +45,10 @@ struct Step {
   StepKind kind;
   std::string name;
   // conv
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmA2, tmB;
   ConvParams cp;
   int block_n = 0;
+  bool use_halo = false, b_resident = false;   // conv_halo_kernel instead of conv_tc_kernel
   // pool
   PoolParams pp;
   // what the step wrote (for idn_read_activation)
@@ -75,6 +76,8 @@ struct idn_engine {
   int* d_tables = nullptr;
   size_t tables_cap = 0, tables_used = 0;   // int32 units
   std::map<std::tuple<int, int, int>, int> table_index;
+  std::map<int, std::vector<int>> table_host;   // offset -> host copy (tile sizing)
+  int pre_raw_words = 0, pre_src_rows = 0;     // staged-tile need of the current batch
   uint16_t* d_lut = nullptr;
   void* xs = nullptr;                 // stem input image
   int stem_left = 0, stem_ws = 232;
@@ -252,6 +255,19 @@ static int add_conv(idn_engine* e, const std::string& name, const Act& src, cons
   cp.a_rows = src.rows(); cp.a_ld = src.C; cp.ktot = cw.ktot;
   if (src.C != cw.c_blocks * 64) { set_error(name + ": src channels != weight channels"); return IDN_EINVAL; }
   const long long m_tiles_cap = ((long long)cap * tg.img_rows() + kBlockM - 1) / kBlockM;
+  st.use_halo = plan_conv_halo(&cp, cw.n_total, (long long)cap * tg.img_rows(), e->num_sms,
+                               &st.block_n, &st.b_resident);
+  if (st.use_halo) {
+    cp.num_n_tiles = cw.n_total / st.block_n;
+    IDN_TRY(make_tmap_2d(&st.tmA, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
+                         (uint64_t)src.C * 2, kBlockK, (uint32_t)cp.halo_r1));
+    IDN_TRY(make_tmap_2d(&st.tmA2, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
+                         (uint64_t)src.C * 2, kBlockK, (uint32_t)(cp.halo_r2 > 0 ? cp.halo_r2 : 8)));
+    IDN_TRY(make_tmap_2d(&st.tmB, cw.wt, (uint64_t)cw.ktot, (uint64_t)cw.n_total,
+                         (uint64_t)cw.ktot * 2, kBlockK, (uint32_t)st.block_n));
+    e->steps.push_back(st);
+    return IDN_OK;
+  }
   st.block_n = pick_block_n(cw.n_total, m_tiles_cap, e->num_sms);
   cp.num_n_tiles = cw.n_total / st.block_n;
   IDN_TRY(make_tmap_2d(&st.tmA, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
@@ -529,11 +545,15 @@ static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int*
   IDN_CUDA_TRY(cudaStreamSynchronize(e->stream));   // `bytes` is a temporary
   *off = (int)e->tables_used;
   e->table_index[key] = *off;
+  e->table_host[*off].assign(reinterpret_cast<const int*>(bytes.data()),
+                             reinterpret_cast<const int*>(bytes.data()) + n);
   e->tables_used += n;
   return IDN_OK;
 }
 
 static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, int n, int64_t base) {
+  e->pre_raw_words = 0; e->pre_src_rows = 0;
+  int last_h = -1, last_v = -1;
   for (int i = 0; i < n; ++i) {
     const int H = hw[2 * i], W = hw[2 * i + 1];
     if (H <= 0 || W <= 0) { set_error("image with non-positive size"); return IDN_EINVAL; }
@@ -543,6 +563,13 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
     m.offset = offsets[i] - base; m.H = H; m.W = W;
     IDN_TRY(ensure_table(e, W, nw, crop_offset(nw), &m.htab));
     IDN_TRY(ensure_table(e, H, nh, crop_offset(nh), &m.vtab));
+    if (m.htab != last_h || m.vtab != last_v) {
+      int rw = 0, sr = 0;
+      preprocess_tile_need(e->table_host[m.htab].data(), e->table_host[m.vtab].data(), &rw, &sr);
+      e->pre_raw_words = std::max(e->pre_raw_words, rw);
+      e->pre_src_rows = std::max(e->pre_src_rows, sr);
+      last_h = m.htab; last_v = m.vtab;
+    }
   }
   IDN_CUDA_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, sizeof(PreMeta) * n, cudaMemcpyHostToDevice,
                                e->stream));
@@ -550,6 +577,22 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
 }
 
 // --------------------------------------------------------------------------------- forward pass
+static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_t st) {
+  ConvParams& cp = s.cp;
+  cp.nimg = n;
+  const long long rows = (long long)n * cp.img_rows;
+  if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
+  else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
+  if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
+  if (cp.mode == MODE_STEM && e->stem_simt) return launch_conv_simt(cp, st);
+  if (s.use_halo) {
+    const int item_rows = kBlockM * cp.msub;
+    cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
+    return launch_conv_halo(s.tmA, s.tmA2, s.tmB, cp, s.block_n, s.b_resident, e->num_sms, st);
+  }
+  return launch_conv_tc(s.tmA, s.tmB, cp, s.block_n, e->num_sms, st);
+}
+
 static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx, float* d_prob,
                     float* d_logits) {
   cudaStream_t st = e->stream;
@@ -565,19 +608,11 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     switch (s.kind) {
       case STEP_PRE:
         IDN_TRY(launch_preprocess(d_imgs, e->d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
-                                  e->stem_left, e->stem_ws, st));
+                                  e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st));
         break;
-      case STEP_CONV: {
-        ConvParams& cp = s.cp;
-        cp.nimg = n;
-        cp.num_m_tiles = cp.mode == MODE_STEM
-                             ? n * cp.tiles_w * cp.tiles_h
-                             : (int)(((long long)n * cp.img_rows + kBlockM - 1) / kBlockM);
-        if (e->impl == IDN_IMPL_TC && !(cp.mode == MODE_STEM && e->stem_simt))
-          IDN_TRY(launch_conv_tc(s.tmA, s.tmB, cp, s.block_n, e->num_sms, st));
-        else IDN_TRY(launch_conv_simt(cp, st));
+      case STEP_CONV:
+        IDN_TRY(launch_conv_step(e, s, n, e->impl, st));
         break;
-      }
       case STEP_POOL:
         s.pp.nimg = n;
         IDN_TRY(launch_maxpool(s.pp, st));
@@ -793,7 +828,8 @@ int idn_preprocess_u8hwc(int device, const uint8_t* imgs, const int64_t* offsets
   cudaMemcpy(tmp.d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice);
   cudaMemcpy(d_in, imgs, hi, cudaMemcpyHostToDevice);
   rc = fill_meta(&tmp, offsets, hw, n, 0);
-  if (rc == IDN_OK) rc = launch_preprocess(d_in, tmp.d_meta, tmp.d_tables, tmp.d_lut, n, PRE_OUT_NCHW, d_out, 0, 0, nullptr);
+  if (rc == IDN_OK) rc = launch_preprocess(d_in, tmp.d_meta, tmp.d_tables, tmp.d_lut, n, PRE_OUT_NCHW, d_out, 0, 0,
+                                        tmp.pre_raw_words, tmp.pre_src_rows, nullptr);
   if (rc == IDN_OK && cudaDeviceSynchronize() != cudaSuccess) { set_error("preprocess kernel failed"); rc = IDN_ECUDA; }
   if (rc == IDN_OK && cudaMemcpy(out, d_out, out_elems * 2, cudaMemcpyDeviceToHost) != cudaSuccess) {
     set_error("preprocess D2H failed"); rc = IDN_ECUDA;
@@ -938,12 +974,7 @@ int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h,
     ConvSpec spec; spec.R = r; spec.S = s; spec.stride = stride; spec.pad = pad; spec.relu = relu != 0;
     if ((rc = add_conv(e.get(), "conv", src, cw, spec, dst, resp, n)) != IDN_OK) return done(rc);
   }
-  Step& st = e->steps.back();
-  st.cp.nimg = n;
-  st.cp.num_m_tiles = st.cp.mode == MODE_STEM ? n * st.cp.tiles_w * st.cp.tiles_h
-                                              : (int)(((long long)n * st.cp.img_rows + kBlockM - 1) / kBlockM);
-  rc = impl == IDN_IMPL_TC ? launch_conv_tc(st.tmA, st.tmB, st.cp, st.block_n, e->num_sms, e->stream)
-                           : launch_conv_simt(st.cp, e->stream);
+  rc = launch_conv_step(e.get(), e->steps.back(), n, impl, e->stream);
   if (rc != IDN_OK) return done(rc);
   if (cudaStreamSynchronize(e->stream) != cudaSuccess) {
     set_error(std::string("conv kernel failed: ") + cudaGetErrorString(cudaGetLastError()));

@@ -106,9 +106,8 @@ __device__ __forceinline__ int clip8(int v) { return v < 0 ? 0 : (v > 255 ? 255 
 // arithmetic is the same integer arithmetic either way.
 // ---------------------------------------------------------------------------------------------
 constexpr int kPreRows = 8;
-constexpr int kPreMaxSrcRows = 26;
-constexpr int kPreRawWords = 9 * 1024;                  // 36 KiB of staged source bytes
-constexpr int kPreSmemBytes = (kPreRawWords + kPreMaxSrcRows * IDN_CROP + kPreRows * IDN_CROP) * 4 + 768 * 2;
+constexpr int kPreMaxSrcRows = 26;                      // upper limits of the staged tile; the launch
+constexpr int kPreMaxRawWords = 9 * 1024;               // sizes shared memory for the batch at hand
 
 __device__ __forceinline__ void pre_direct_pixel(const uint8_t* __restrict__ src, int W,
                                                  const int* __restrict__ ht, const int* __restrict__ vt,
@@ -140,11 +139,11 @@ template <int OUT_MODE>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ meta,
                   const int* __restrict__ tables, const uint16_t* __restrict__ lut, void* out,
-                  int left_pad, int ws) {
+                  int left_pad, int ws, int raw_cap_words, int src_rows_cap) {
   extern __shared__ uint32_t sm[];
   uint32_t* s_raw = sm;                                        // staged source bytes
-  uint32_t* s_h = sm + kPreRawWords;                           // [src rows][224] RGBx after pass 1
-  uint32_t* s_out = s_h + kPreMaxSrcRows * IDN_CROP;           // [kPreRows][224] RGBx resized tile
+  uint32_t* s_h = sm + raw_cap_words;                          // [src rows][224] RGBx after pass 1
+  uint32_t* s_out = s_h + src_rows_cap * IDN_CROP;             // [kPreRows][224] RGBx resized tile
   uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_out + kPreRows * IDN_CROP);
   const int tid = threadIdx.x, n = blockIdx.y;
   for (int i = tid; i < 768; i += blockDim.x) s_lut[i] = lut[i];
@@ -165,29 +164,30 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
     const int c0 = ht[1], c1 = ht[1 + IDN_CROP - 1] + ht[1 + 2 * IDN_CROP - 1];
     const int rowbytes = (c1 - c0) * 3;
     const int pitchw = (rowbytes + 3) / 4 + 4;                                  // words per staged row
-    const bool tiled = hks <= 4 && nrows <= kPreMaxSrcRows && nrows * pitchw <= kPreRawWords;
+    const bool tiled = hks <= 4 && nrows <= src_rows_cap && nrows * pitchw <= raw_cap_words;
     if (tiled) {
       // ---- 1. stage source rows (word r*pitchw + w holds bytes of the 4-aligned word that
       //         contains the row's first needed byte, onwards)
-      for (int r = 0; r < nrows; ++r) {
+      const int nwmax = (rowbytes + 6) >> 2;                  // words per row incl. both edge words
+#pragma unroll 4
+      for (int it = tid; it < nrows * nwmax; it += blockDim.x) {
+        const int r = it / nwmax, w = it - r * nwmax;
         const uint8_t* g = src + ((long long)(ys0 + r) * m.W + c0) * 3;
         const int shift = (int)(reinterpret_cast<uintptr_t>(g) & 3);
-        const uint8_t* g0 = g - shift;
         const int nw = (shift + rowbytes + 3) >> 2;
-        for (int w = tid; w < nw; w += blockDim.x) {
-          uint32_t v;
-          if (w == 0 || w == nw - 1) {          // edge words: only touch bytes inside the row
-            v = 0;
+        if (w >= nw) continue;
+        uint32_t v;
+        if (w == 0 || w == nw - 1) {            // edge words: only touch bytes inside the row
+          v = 0;
 #pragma unroll
-            for (int b = 0; b < 4; ++b) {
-              const int off = 4 * w + b - shift;
-              if (off >= 0 && off < rowbytes) v |= (uint32_t)__ldg(g + off) << (8 * b);
-            }
-          } else {
-            v = __ldg(reinterpret_cast<const uint32_t*>(g0) + w);
+          for (int b = 0; b < 4; ++b) {
+            const int off = 4 * w + b - shift;
+            if (off >= 0 && off < rowbytes) v |= (uint32_t)__ldg(g + off) << (8 * b);
           }
-          s_raw[r * pitchw + w] = v;
+        } else {
+          v = __ldg(reinterpret_cast<const uint32_t*>(g - shift) + w);
         }
+        s_raw[r * pitchw + w] = v;
       }
       __syncthreads();
       // ---- 2. horizontal pass
@@ -198,6 +198,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
         int k[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) k[i] = (i < xn) ? __ldg(hk + i) : 0;
+#pragma unroll 2
         for (int r = 0; r < nrows; ++r) {
           const uint8_t* g = src + ((long long)(ys0 + r) * m.W + c0) * 3;
           const int bstart = (int)(reinterpret_cast<uintptr_t>(g) & 3) + (x0 - c0) * 3;
@@ -303,27 +304,47 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
 
 int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
-                      int stem_ws, cudaStream_t st) {
+                      int stem_ws, int raw_words, int src_rows, cudaStream_t st) {
   if (n <= 0) return IDN_OK;
   if (out_mode == PRE_OUT_STEM && (stem_ws & 1)) {
     set_error("preprocess: stem row pitch must be even");
     return IDN_EINVAL;
   }
+  // shared memory for the largest staged tile of this batch (images beyond the caps take the
+  // direct path inside the kernel)
+  const int raw_cap = raw_words < 64 ? 64 : (raw_words > kPreMaxRawWords ? kPreMaxRawWords : raw_words);
+  const int rows_cap = src_rows < 1 ? 1 : (src_rows > kPreMaxSrcRows ? kPreMaxSrcRows : src_rows);
+  const int smem = (raw_cap + rows_cap * IDN_CROP + kPreRows * IDN_CROP) * 4 + 768 * 2;
   if (out_mode == PRE_OUT_NCHW) {
-    IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_NCHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPreSmemBytes));
-    preprocess_kernel<PRE_OUT_NCHW><<<dim3(IDN_CROP / kPreRows, n), 256, kPreSmemBytes, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, 0, 0);
+    if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_NCHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    preprocess_kernel<PRE_OUT_NCHW><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
+        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap);
   } else if (out_mode == PRE_OUT_STEM) {
-    IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_STEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPreSmemBytes));
-    preprocess_kernel<PRE_OUT_STEM><<<dim3(IDN_CROP / kPreRows, n), 256, kPreSmemBytes, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws);
+    if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_STEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    preprocess_kernel<PRE_OUT_STEM><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
+        d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap);
   } else {
-    IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPreSmemBytes));
-    preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, kPreSmemBytes, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, 0, 0);
+    if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, smem, st>>>(
+        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap);
   }
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
+}
+
+// Shared-memory need of the staged tile for one image: (staged words, source rows) for the worst
+// window of kPreRows consecutive crop rows (any alignment: the S2D4 tiles are shifted by 2).
+void preprocess_tile_need(const int* htab, const int* vtab, int* raw_words, int* src_rows) {
+  const int c0 = htab[1], c1 = htab[1 + IDN_CROP - 1] + htab[1 + 2 * IDN_CROP - 1];
+  const int pitchw = ((c1 - c0) * 3 + 3) / 4 + 4;
+  int span = 1;
+  for (int y = 0; y < IDN_CROP; ++y) {
+    const int last = y + kPreRows - 1 < IDN_CROP ? y + kPreRows - 1 : IDN_CROP - 1;
+    const int s = vtab[1 + last] + vtab[1 + IDN_CROP + last] - vtab[1 + y];
+    if (s > span) span = s;
+  }
+  *src_rows = span;
+  *raw_words = span * pitchw;
 }
 
 }  // namespace idn

@@ -92,10 +92,25 @@ def test_every_n_tile_width(built_library, monkeypatch, block_n, shape):
     """Small problems pick narrow N tiles by themselves; force the wide instantiations
     (BLOCK_N = 192 / 256: 5- and 4-stage rings, 512 TMEM columns) that batch-400 plans use."""
     monkeypatch.setenv("IDN_BLOCK_N", str(block_n))
+    monkeypatch.setenv("IDN_NO_HALO", "1")       # keep the layer on conv_tc_kernel
     n, cin, h, w, cout, r, stride, pad, residual, relu = shape
     x, wt, sc, sh, res, want = _case(*shape, seed=block_n + n)
     got = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl="tc")
     assert _err(got, want) < TOL
+
+
+@pytest.mark.parametrize("shape", [SHAPES[1], SHAPES[4], SHAPES[5], SHAPES[7], SHAPES[8]],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_halo_and_per_tap_kernels_agree(built_library, monkeypatch, shape):
+    """conv_halo_kernel (one staged A tile for all taps, resident / reused weights) and
+    conv_tc_kernel (one TMA box per tap) differ only in accumulation order."""
+    n, cin, h, w, cout, r, stride, pad, residual, relu = shape
+    x, wt, sc, sh, res, want = _case(*shape, seed=11)
+    a = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl="tc")
+    monkeypatch.setenv("IDN_NO_HALO", "1")
+    b = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl="tc")
+    assert _err(a, want) < TOL and _err(b, want) < TOL
+    assert _err(a, b) < TOL
 
 
 def test_many_tiles_per_cta(built_library):

@@ -777,9 +777,15 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   int bn = 0;
   bool res = false;
   const int k_total = p->num_taps * p->c_blocks;
+  // Measured on B200 (profiles/): the halo kernel wins for the 64-channel layers (weights resident,
+  // 1.7x over one-box-per-tap) and loses for wider layers, where 128 x 128 SS-mode MMAs read
+  // 128 B/clk of operands from shared memory and 128 x 256 tiles of conv_tc_kernel do better.
+  // The streamed-weights instantiations stay available behind IDN_HALO_WIDE=1 for experiments.
+  bool wide = false;
+  if (const char* v = std::getenv("IDN_HALO_WIDE")) wide = v[0] == '1';
   if (n_total == 64) { bn = 64; res = (k_total * 64 * 128) <= 80 * 1024; }
-  else if (n_total % 128 == 0) bn = 128;
-  else if (n_total % 96 == 0) bn = 96;
+  else if (wide && n_total % 128 == 0) bn = 128;
+  else if (wide && n_total % 96 == 0) bn = 96;
   else return false;
   if (bn == 64 && !res) return false;
   const int msub = 2;

@@ -105,6 +105,7 @@ def test_halo_and_per_tap_kernels_agree(built_library, monkeypatch, shape):
     """conv_halo_kernel (one staged A tile for all taps, resident / reused weights) and
     conv_tc_kernel (one TMA box per tap) differ only in accumulation order."""
     n, cin, h, w, cout, r, stride, pad, residual, relu = shape
+    monkeypatch.setenv("IDN_HALO_WIDE", "1")     # also the streamed-weights instantiations
     x, wt, sc, sh, res, want = _case(*shape, seed=11)
     a = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl="tc")
     monkeypatch.setenv("IDN_NO_HALO", "1")

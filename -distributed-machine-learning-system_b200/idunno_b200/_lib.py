@@ -29,6 +29,8 @@ SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "idn_sync": (C.c_int, [C.c_void_p]),
     "idn_preprocess_u8hwc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "idn_preprocess_u8hwc_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                               C.c_void_p, C.c_void_p]),
     "idn_num_steps": (C.c_int, [C.c_void_p]),
     "idn_step_info": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.c_void_p]),
     "idn_read_activation": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),

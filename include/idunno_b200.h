@@ -126,6 +126,30 @@ int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h,
                     const float* scale, const float* shift, const float* residual, int relu,
                     float* y);
 
+/* Has no counterpart in the reference: an entry point for callers that cannot allocate device
+ * memory (all of it already belongs to another framework's pool, an allocator call would stall a
+ * latency-critical loop, or the caller is a plug-in that only receives buffers and a stream).
+ * Same computation and same NCHW bf16 output as idn_preprocess_u8hwc, but the image bytes and the
+ * output are DEVICE buffers the caller owns, and the kernel's working data (normalisation table,
+ * per-image records, resample tables) lives in a static device array inside the library instead of
+ * cudaMalloc'ed buffers: IDN_NOALLOC_SCRATCH_BYTES per GPU that loads the library, held until the
+ * process exits.  Limits: n <= IDN_NOALLOC_MAX_IMAGES per call and resample tables that fit the
+ * array (always true for a batch of equally sized images); anything larger returns IDN_EINVAL with
+ * the reason in idn_last_error().  The call makes no cudaMalloc/cudaFree/cudaMallocHost and no
+ * host heap allocation on its success path.  It is asynchronous: work is enqueued on cuda_stream
+ * (NULL = the legacy default stream) and d_out_nchw_bf16 is complete once that stream has been
+ * synchronised.  offsets/hw are host arrays as elsewhere.
+ * The first call on a device looks up the array's device address and uploads the normalisation
+ * table (a blocking copy); make that first call before starting any stream capture.
+ * Every call on a device shares the one array: it is rewritten by each call (nothing from an
+ * earlier call is read), so two calls whose GPU work overlaps -- different streams, or different
+ * threads -- race on it.  Serialise calls per device, or order them on one stream. */
+#define IDN_NOALLOC_MAX_IMAGES    64
+#define IDN_NOALLOC_SCRATCH_BYTES (512 * 1024)
+int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_packed, const int64_t* offsets,
+                                 const int32_t* hw, int n, uint16_t* d_out_nchw_bf16,
+                                 void* cuda_stream);
+
 const char* idn_last_error(void);
 
 /* Library build identification ("idunno_b200 <version> sm_100a"). */

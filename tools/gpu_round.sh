@@ -10,11 +10,14 @@ case $w in
 diag)
   timeout 600 python tools/gpu_diag.py > gpurun_out/diag.log 2>&1; echo "diag rc=$?" ;;
 tests)
-  for f in tests/test_gpu_preprocess.py tests/test_gpu_conv.py tests/test_gpu_model.py; do
+  for f in tests/test_gpu_preprocess.py tests/test_gpu_conv.py tests/test_gpu_model.py tests/test_zz_no_alloc.py; do
     b=$(basename $f .py)
     timeout 1500 python -m pytest $f -m gpu -q -rA -s -p no:cacheprovider > gpurun_out/$b.log 2>&1
     echo "$b rc=$? $(tail -1 gpurun_out/$b.log)"
   done ;;
+suite)
+  timeout 1500 python -m pytest tests/ -x -q -m gpu -p no:cacheprovider > gpurun_out/suite.log 2>&1
+  echo "suite rc=$? $(tail -1 gpurun_out/suite.log)" ;;
 bench)
   timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err
   echo "bench rc=$?"; cat gpurun_out/bench.json | cut -c1-1500 ;;

@@ -974,6 +974,9 @@ int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h,
     ConvSpec spec; spec.R = r; spec.S = s; spec.stride = stride; spec.pad = pad; spec.relu = relu != 0;
     if ((rc = add_conv(e.get(), "conv", src, cw, spec, dst, resp, n)) != IDN_OK) return done(rc);
   }
+  // uploads above went through the legacy default stream (a pageable cudaMemcpy may return before its
+  // DMA has landed); the kernel runs on a non-blocking stream, so drain the device first
+  if (cudaDeviceSynchronize() != cudaSuccess) { set_error("sync before conv failed"); return done(IDN_ECUDA); }
   rc = launch_conv_step(e.get(), e->steps.back(), n, impl, e->stream);
   if (rc != IDN_OK) return done(rc);
   if (cudaStreamSynchronize(e->stream) != cudaSuccess) {

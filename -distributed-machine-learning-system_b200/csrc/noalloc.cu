@@ -141,7 +141,8 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
     }
     uint16_t lut[768];
     build_norm_lut(lut);
-    IDN_CUDA_TRY(cudaMemcpy(ptr + kLutOff, lut, sizeof(lut), cudaMemcpyHostToDevice));
+    // on the caller's stream, so that the kernel below is ordered after it whatever kind of stream it is
+    IDN_CUDA_TRY(cudaMemcpyAsync(ptr + kLutOff, lut, sizeof(lut), cudaMemcpyHostToDevice, st));
     ds.scratch = ptr;
     ds.ready = true;
   }

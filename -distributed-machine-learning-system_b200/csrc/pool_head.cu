@@ -8,53 +8,47 @@ namespace idn {
 // One thread = one output pixel x 8 channels (one 128-bit load per window tap, one 128-bit store).
 // Replaces nn.MaxPool2d(3, 2[, 1]) of tv:models/alexnet.py:24,27,34 and tv:models/resnet.py:201.
 // Window taps outside the valid H x W extent are skipped (PyTorch pads with -inf).
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a), y = *reinterpret_cast<__nv_bfloat162*>(&b);
+  __nv_bfloat162 m = __hmax2(x, y);
+  return *reinterpret_cast<uint32_t*>(&m);
+}
+
+// grid = (ceil(OH*OW*C/8 / 256), n); 32-bit index math, packed bf16x2 max (inputs are finite)
 __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(const PoolParams p) {
   const int cvec = p.C >> 3;
-  const long long total = (long long)p.nimg * p.OH * p.OW * cvec;
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-       t += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(t % cvec);
-    long long r = t / cvec;
-    const int ow = (int)(r % p.OW); r /= p.OW;
-    const int oh = (int)(r % p.OH);
-    const int n = (int)(r / p.OH);
-    float m[8];
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= p.OH * p.OW * cvec) return;
+  const int n = blockIdx.y;
+  const int cv = t % cvec;
+  const int pix = t / cvec;
+  const int oh = pix / p.OW, ow = pix - oh * p.OW;
+  const int h0 = oh * 2 - p.pad, w0 = ow * 2 - p.pad;
+  const uint4* base = reinterpret_cast<const uint4*>(p.in + (long long)n * p.s_img_rows * p.C) + cv;
+  const uint32_t ninf = 0xff80ff80u;                       // (-inf, -inf) in bf16
+  uint4 m = make_uint4(ninf, ninf, ninf, ninf);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) m[e] = -INFINITY;
+  for (int dy = 0; dy < 3; ++dy) {
+    const int h = h0 + dy;
+    if (h < 0 || h >= p.H) continue;
 #pragma unroll
-    for (int dy = 0; dy < 3; ++dy) {
-      const int h = oh * 2 - p.pad + dy;
-      if (h < 0 || h >= p.H) continue;
-#pragma unroll
-      for (int dx = 0; dx < 3; ++dx) {
-        const int w = ow * 2 - p.pad + dx;
-        if (w < 0 || w >= p.W) continue;
-        const long long row = (long long)n * p.s_img_rows + (long long)h * p.s_wp + w;
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.in + row * p.C) + cv);
-        const uint32_t u[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          m[2 * e] = fmaxf(m[2 * e], __uint_as_float(u[e] << 16));
-          m[2 * e + 1] = fmaxf(m[2 * e + 1], __uint_as_float(u[e] & 0xffff0000u));
-        }
-      }
+    for (int dx = 0; dx < 3; ++dx) {
+      const int w = w0 + dx;
+      if (w < 0 || w >= p.W) continue;
+      const uint4 v = __ldg(base + (h * p.s_wp + w) * cvec);
+      m.x = bf16x2_max(m.x, v.x); m.y = bf16x2_max(m.y, v.y);
+      m.z = bf16x2_max(m.z, v.z); m.w = bf16x2_max(m.w, v.w);
     }
-    uint32_t o[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e)   // inputs are bf16, so the max is exactly representable
-      o[e] = (__float_as_uint(m[2 * e]) >> 16) | (__float_as_uint(m[2 * e + 1]) & 0xffff0000u);
-    const long long drow = (long long)n * p.d_img_rows + (long long)oh * p.d_wp + ow;
-    reinterpret_cast<uint4*>(p.out + drow * p.C)[cv] = make_uint4(o[0], o[1], o[2], o[3]);
   }
+  reinterpret_cast<uint4*>(p.out + ((long long)n * p.d_img_rows + oh * p.d_wp + ow) * p.C)[cv] = m;
 }
 
 int launch_maxpool(const PoolParams& p, cudaStream_t st) {
   if (p.C % 8 != 0) { set_error("maxpool: C % 8 != 0"); return IDN_EINVAL; }
-  const long long total = (long long)p.nimg * p.OH * p.OW * (p.C / 8);
-  if (total <= 0) return IDN_OK;
-  long long blocks = (total + 255) / 256;
-  if (blocks > 148LL * 32) blocks = 148LL * 32;
-  maxpool3x3s2_kernel<<<(int)blocks, 256, 0, st>>>(p);
+  const int per_img = p.OH * p.OW * (p.C / 8);
+  if (per_img <= 0 || p.nimg <= 0) return IDN_OK;
+  dim3 grid((per_img + 255) / 256, p.nimg);
+  maxpool3x3s2_kernel<<<grid, 256, 0, st>>>(p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }

@@ -135,6 +135,10 @@ __device__ __forceinline__ void pre_direct_pixel(const uint8_t* __restrict__ src
   out3[0] = clip8(acc[0] >> 22); out3[1] = clip8(acc[1] >> 22); out3[2] = clip8(acc[2] >> 22);
 }
 
+__device__ __forceinline__ int bsel(uint32_t v, int i) {          // byte i of v (one PRMT)
+  return (int)__byte_perm(v, 0u, 0x4440u + (uint32_t)i);
+}
+
 template <int OUT_MODE>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ meta,
@@ -143,161 +147,137 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
   extern __shared__ uint32_t sm[];
   uint32_t* s_raw = sm;                                        // staged source bytes
   uint32_t* s_h = sm + raw_cap_words;                          // [src rows][224] RGBx after pass 1
-  uint32_t* s_out = s_h + src_rows_cap * IDN_CROP;             // [kPreRows][224] RGBx resized tile
-  uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_out + kPreRows * IDN_CROP);
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_h + src_rows_cap * IDN_CROP);
   const int tid = threadIdx.x, n = blockIdx.y;
+  const int warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < 768; i += blockDim.x) s_lut[i] = lut[i];
   const PreMeta m = meta[n];
-  const int* ht = tables + m.htab;
-  const int* vt = tables + m.vtab;
-  const uint8_t* src = imgs + m.offset;
-  // rows of the 224x224 crop this CTA produces; S2D4 tiles are shifted by the stem's padding (2)
-  const int ybase = OUT_MODE == PRE_OUT_S2D4 ? kPreRows * (int)blockIdx.x - 2 : kPreRows * (int)blockIdx.x;
-  const int ylo = ybase < 0 ? 0 : ybase;
-  const int yhi = ybase + kPreRows > IDN_CROP ? IDN_CROP : ybase + kPreRows;   // exclusive
+  const int* __restrict__ ht = tables + m.htab;
+  const int* __restrict__ vt = tables + m.vtab;
+  const uint8_t* __restrict__ src = imgs + m.offset;
+  const int ylo = kPreRows * (int)blockIdx.x, yhi = ylo + kPreRows;      // 224 = 28 * 8
+  const int hks = ht[0], vks = vt[0];
+  const int ys0 = vt[1 + ylo];
+  const int nrows = vt[1 + yhi - 1] + vt[1 + IDN_CROP + yhi - 1] - ys0;
+  const int c0 = ht[1], c1 = ht[1 + IDN_CROP - 1] + ht[1 + 2 * IDN_CROP - 1];
+  const int rowbytes = (c1 - c0) * 3;
+  const int pitchw = (rowbytes + 3) / 4 + 4;                              // words per staged row
+  const bool tiled = hks <= 4 && vks <= 4 && nrows <= src_rows_cap && nrows * pitchw <= raw_cap_words;
+  const int rowstep = m.W * 3;
+  const uint8_t* g_first = src + ((long long)ys0 * m.W + c0) * 3;         // first needed byte
 
-  if (ylo < yhi) {
-    const int hks = ht[0], vks = vt[0];
-    const int ys0 = vt[1 + ylo];
-    const int ys1 = vt[1 + yhi - 1] + vt[1 + IDN_CROP + yhi - 1];              // exclusive
-    const int nrows = ys1 - ys0;
-    const int c0 = ht[1], c1 = ht[1 + IDN_CROP - 1] + ht[1 + 2 * IDN_CROP - 1];
-    const int rowbytes = (c1 - c0) * 3;
-    const int pitchw = (rowbytes + 3) / 4 + 4;                                  // words per staged row
-    const bool tiled = hks <= 4 && nrows <= src_rows_cap && nrows * pitchw <= raw_cap_words;
-    if (tiled) {
-      // ---- 1. stage source rows (word r*pitchw + w holds bytes of the 4-aligned word that
-      //         contains the row's first needed byte, onwards)
-      const int nwmax = (rowbytes + 6) >> 2;                  // words per row incl. both edge words
-#pragma unroll 4
-      for (int it = tid; it < nrows * nwmax; it += blockDim.x) {
-        const int r = it / nwmax, w = it - r * nwmax;
-        const uint8_t* g = src + ((long long)(ys0 + r) * m.W + c0) * 3;
-        const int shift = (int)(reinterpret_cast<uintptr_t>(g) & 3);
-        const int nw = (shift + rowbytes + 3) >> 2;
-        if (w >= nw) continue;
-        uint32_t v;
-        if (w == 0 || w == nw - 1) {            // edge words: only touch bytes inside the row
-          v = 0;
+  // ---- per-pixel output (bf16 bits of the three channels), shared by both paths
+  auto emit = [&](int y, int x, uint32_t rr, uint32_t gg, uint32_t bb) {
+    const uint32_t r = s_lut[rr], g = s_lut[256 + gg], b = s_lut[512 + bb];
+    if (OUT_MODE == PRE_OUT_NCHW) {
+      uint16_t* o = reinterpret_cast<uint16_t*>(out) + (long long)n * 3 * IDN_CROP * IDN_CROP + y * IDN_CROP + x;
+      o[0] = (uint16_t)r; o[IDN_CROP * IDN_CROP] = (uint16_t)g; o[2 * IDN_CROP * IDN_CROP] = (uint16_t)b;
+    } else if (OUT_MODE == PRE_OUT_STEM) {
+      reinterpret_cast<uint2*>(out)[((long long)n * IDN_CROP + y) * ws + left_pad + x] = make_uint2(r | (g << 16), b);
+    } else {   // PRE_OUT_S2D4: s2d pixel ((y+2)/4, (x+2)/4), channel (dy*4+dx)*3 + c; 57x57x64 per image.
+               // Channels 48..63 and the out-of-image border positions are never written: the buffer is
+               // zeroed once when it is allocated.
+      const int yy = y + 2, xx = x + 2;
+      uint16_t* o = reinterpret_cast<uint16_t*>(out) +
+                    (((long long)n * 57 + (yy >> 2)) * 57 + (xx >> 2)) * 64 + ((yy & 3) * 4 + (xx & 3)) * 3;
+      o[0] = (uint16_t)r; o[1] = (uint16_t)g; o[2] = (uint16_t)b;
+    }
+  };
+
+  if (tiled) {
+    // ---- 1. stage the source rows: warp w takes rows w, w+8, ...; aligned 32-bit loads, the two
+    //         edge words of a row byte by byte so that nothing outside the row is touched
+    for (int r = warp; r < nrows; r += 8) {
+      const uint8_t* g = g_first + (long long)r * rowstep;
+      const int shift = (int)(reinterpret_cast<uintptr_t>(g) & 3);
+      const int nw = (shift + rowbytes + 3) >> 2;
+      const uint32_t* gw = reinterpret_cast<const uint32_t*>(g - shift);
+      uint32_t* dst = s_raw + r * pitchw;
+      for (int w = lane + 1; w < nw - 1; w += 32) dst[w] = __ldg(gw + w);
+      if (lane < 2) {
+        const int w = lane == 0 ? 0 : nw - 1;
+        uint32_t v = 0;
 #pragma unroll
-          for (int b = 0; b < 4; ++b) {
-            const int off = 4 * w + b - shift;
-            if (off >= 0 && off < rowbytes) v |= (uint32_t)__ldg(g + off) << (8 * b);
-          }
-        } else {
-          v = __ldg(reinterpret_cast<const uint32_t*>(g - shift) + w);
+        for (int b = 0; b < 4; ++b) {
+          const int off = 4 * w + b - shift;
+          if (off >= 0 && off < rowbytes) v |= (uint32_t)__ldg(g + off) << (8 * b);
         }
-        s_raw[r * pitchw + w] = v;
+        dst[w] = v;
       }
-      __syncthreads();
-      // ---- 2. horizontal pass
-      if (tid < IDN_CROP) {
-        const int x = tid;
+    }
+    __syncthreads();
+    if (tid < IDN_CROP) {
+      const int x = tid;
+      // ---- 2. horizontal pass: <= 4 taps, coefficients in registers, 12 source bytes per row
+      {
         const int x0 = ht[1 + x], xn = ht[1 + IDN_CROP + x];
         const int* hk = ht + 1 + 2 * IDN_CROP + x * hks;
-        int k[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) k[i] = (i < xn) ? __ldg(hk + i) : 0;
+        int k0 = __ldg(hk), k1 = xn > 1 ? __ldg(hk + 1) : 0, k2 = xn > 2 ? __ldg(hk + 2) : 0,
+            k3 = xn > 3 ? __ldg(hk + 3) : 0;
+        const int boff = (x0 - c0) * 3;
+        int shift = (int)(reinterpret_cast<uintptr_t>(g_first) & 3);
+        const uint32_t* rowp = s_raw;
+        uint32_t* hp = s_h + x;
 #pragma unroll 2
         for (int r = 0; r < nrows; ++r) {
-          const uint8_t* g = src + ((long long)(ys0 + r) * m.W + c0) * 3;
-          const int bstart = (int)(reinterpret_cast<uintptr_t>(g) & 3) + (x0 - c0) * 3;
-          const uint32_t* wp = s_raw + r * pitchw + (bstart >> 2);
+          const int bstart = shift + boff;
+          const uint32_t* wp = rowp + (bstart >> 2);
           const int sh = (bstart & 3) * 8;
           const uint32_t a = wp[0], b = wp[1], c = wp[2], d = wp[3];
           const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
                          p2 = __funnelshift_r(c, d, sh);           // 12 bytes = 4 RGB pixels
           int h0 = 1 << 21, h1 = 1 << 21, h2 = 1 << 21;
-          h0 += (int)(p0 & 255) * k[0];         h1 += (int)((p0 >> 8) & 255) * k[0];  h2 += (int)((p0 >> 16) & 255) * k[0];
-          h0 += (int)(p0 >> 24) * k[1];         h1 += (int)(p1 & 255) * k[1];         h2 += (int)((p1 >> 8) & 255) * k[1];
-          h0 += (int)((p1 >> 16) & 255) * k[2]; h1 += (int)(p1 >> 24) * k[2];         h2 += (int)(p2 & 255) * k[2];
-          h0 += (int)((p2 >> 8) & 255) * k[3];  h1 += (int)((p2 >> 16) & 255) * k[3]; h2 += (int)(p2 >> 24) * k[3];
-          s_h[r * IDN_CROP + x] = (uint32_t)clip8(h0 >> 22) | ((uint32_t)clip8(h1 >> 22) << 8) |
-                                  ((uint32_t)clip8(h2 >> 22) << 16);
+          h0 += bsel(p0, 0) * k0; h1 += bsel(p0, 1) * k0; h2 += bsel(p0, 2) * k0;
+          h0 += bsel(p0, 3) * k1; h1 += bsel(p1, 0) * k1; h2 += bsel(p1, 1) * k1;
+          h0 += bsel(p1, 2) * k2; h1 += bsel(p1, 3) * k2; h2 += bsel(p2, 0) * k2;
+          h0 += bsel(p2, 1) * k3; h1 += bsel(p2, 2) * k3; h2 += bsel(p2, 3) * k3;
+          // coefficients are >= 0 and sum to 2^22 (+- rounding), so the result is already in [0, 255]
+          *hp = (uint32_t)(h0 >> 22) | ((uint32_t)(h1 >> 22) << 8) | ((uint32_t)(h2 >> 22) << 16);
+          hp += IDN_CROP;
+          rowp += pitchw;
+          shift = (shift + rowstep) & 3;
         }
       }
-      __syncthreads();
-      // ---- 3. vertical pass
-      if (tid < IDN_CROP) {
-        const int x = tid;
-        for (int y = ylo; y < yhi; ++y) {
-          const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
-          const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
-          int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-          for (int j = 0; j < yn; ++j) {
-            const uint32_t p = s_h[(y0 + j) * IDN_CROP + x];
-            const int kv = __ldg(vk + j);
-            a0 += (int)(p & 255) * kv; a1 += (int)((p >> 8) & 255) * kv; a2 += (int)((p >> 16) & 255) * kv;
-          }
-          s_out[(y - ybase) * IDN_CROP + x] = (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) |
-                                              ((uint32_t)clip8(a2 >> 22) << 16);
-        }
+    }
+    __syncthreads();
+    if (tid < IDN_CROP) {
+      const int x = tid;
+      // ---- 3. vertical pass over the uint8 intermediate + normalise + store
+#pragma unroll 2
+      for (int y = ylo; y < yhi; ++y) {
+        const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
+        const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
+        const int k0 = __ldg(vk), k1 = yn > 1 ? __ldg(vk + 1) : 0, k2 = yn > 2 ? __ldg(vk + 2) : 0,
+                  k3 = yn > 3 ? __ldg(vk + 3) : 0;
+        const int last = nrows - 1;
+        const uint32_t q0 = s_h[y0 * IDN_CROP + x];
+        const uint32_t q1 = s_h[min(y0 + 1, last) * IDN_CROP + x];
+        const uint32_t q2 = s_h[min(y0 + 2, last) * IDN_CROP + x];
+        const uint32_t q3 = s_h[min(y0 + 3, last) * IDN_CROP + x];
+        int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+        a0 += bsel(q0, 0) * k0; a1 += bsel(q0, 1) * k0; a2 += bsel(q0, 2) * k0;
+        a0 += bsel(q1, 0) * k1; a1 += bsel(q1, 1) * k1; a2 += bsel(q1, 2) * k1;
+        a0 += bsel(q2, 0) * k2; a1 += bsel(q2, 1) * k2; a2 += bsel(q2, 2) * k2;
+        a0 += bsel(q3, 0) * k3; a1 += bsel(q3, 1) * k3; a2 += bsel(q3, 2) * k3;
+        emit(y, x, (uint32_t)(a0 >> 22), (uint32_t)(a1 >> 22), (uint32_t)(a2 >> 22));
       }
-    } else if (tid < IDN_CROP) {
+    }
+  } else {
+    __syncthreads();                              // s_lut
+    if (tid < IDN_CROP) {
       for (int y = ylo; y < yhi; ++y) {
         int o[3];
         pre_direct_pixel(src, m.W, ht, vt, tid, y, o);
-        s_out[(y - ybase) * IDN_CROP + tid] = (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16);
+        emit(y, tid, (uint32_t)o[0], (uint32_t)o[1], (uint32_t)o[2]);
       }
     }
   }
-  __syncthreads();
-
-  // ---- 4. writers (128-bit stores)
-  auto norm = [&](int yy, int x, int c) -> uint32_t {     // bf16 bits of channel c at tile row yy
-    return (uint32_t)s_lut[c * 256 + ((s_out[yy * IDN_CROP + x] >> (8 * c)) & 255)];
-  };
-  if (OUT_MODE == PRE_OUT_NCHW) {
-    uint16_t* o = reinterpret_cast<uint16_t*>(out) + (long long)n * 3 * IDN_CROP * IDN_CROP;
-    const int nrow = yhi - ylo;
-    for (int it = tid; it < 3 * nrow * (IDN_CROP / 8); it += blockDim.x) {
-      const int xq = it % (IDN_CROP / 8);
-      const int yy = (it / (IDN_CROP / 8)) % nrow;
-      const int c = it / ((IDN_CROP / 8) * nrow);
-      uint32_t w[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e)
-        w[e] = norm(yy, xq * 8 + 2 * e, c) | (norm(yy, xq * 8 + 2 * e + 1, c) << 16);
-      *reinterpret_cast<uint4*>(o + ((long long)c * IDN_CROP + ylo + yy) * IDN_CROP + xq * 8) =
-          make_uint4(w[0], w[1], w[2], w[3]);
-    }
-  } else if (OUT_MODE == PRE_OUT_STEM) {
-    uint4* o = reinterpret_cast<uint4*>(out);
-    const int pairs = ws >> 1, nrow = yhi - ylo;
-    for (int it = tid; it < nrow * pairs; it += blockDim.x) {
-      const int pr = it % pairs, yy = it / pairs;
-      uint32_t w[4] = {0u, 0u, 0u, 0u};
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int x = 2 * pr + e - left_pad;
-        if (x >= 0 && x < IDN_CROP) {
-          w[2 * e] = norm(yy, x, 0) | (norm(yy, x, 1) << 16);
-          w[2 * e + 1] = norm(yy, x, 2);
-        }
-      }
-      o[((long long)n * IDN_CROP + ylo + yy) * pairs + pr] = make_uint4(w[0], w[1], w[2], w[3]);
-    }
-  } else {   // PRE_OUT_S2D4: pixel (by, bx) = 4x4 block of crop pixels starting at (4by-2, 4bx-2),
-             // channel (dy*4+dx)*3+c, 48..63 zero; image = 57 x 57 pixels of 64 channels
-    uint4* o = reinterpret_cast<uint4*>(out);
-    const int by0 = 2 * (int)blockIdx.x;
-    for (int it = tid; it < 2 * 57 * 8; it += blockDim.x) {
-      const int j = it & 7, bx = (it >> 3) % 57, byl = it / (8 * 57);
-      if (by0 + byl >= 57) continue;
-      uint32_t w[4] = {0u, 0u, 0u, 0u};
-      if (j < 6) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int e = 8 * j + i;
-          const int dy = e / 12, rem = e - 12 * dy, dx = rem / 3, c = rem - 3 * dx;
-          const int yy = 4 * byl + dy;                 // tile row (ybase + yy is the crop row)
-          const int x = 4 * bx - 2 + dx;
-          uint32_t v = 0;
-          if (ybase + yy >= 0 && ybase + yy < IDN_CROP && x >= 0 && x < IDN_CROP) v = norm(yy, x, c);
-          w[i >> 1] |= v << (16 * (i & 1));
-        }
-      }
-      o[(((long long)n * 57 + by0 + byl) * 57 + bx) * 8 + j] = make_uint4(w[0], w[1], w[2], w[3]);
+  if (OUT_MODE == PRE_OUT_STEM && tid >= IDN_CROP) {      // the stem layout's horizontal zero padding
+    const int padpx = tid - IDN_CROP;
+    if (padpx < ws - IDN_CROP) {
+      const int px = padpx < left_pad ? padpx : IDN_CROP + padpx;
+      for (int y = ylo; y < yhi; ++y)
+        reinterpret_cast<uint2*>(out)[((long long)n * IDN_CROP + y) * ws + px] = make_uint2(0u, 0u);
     }
   }
 }
@@ -306,15 +286,15 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
                       int stem_ws, int raw_words, int src_rows, cudaStream_t st) {
   if (n <= 0) return IDN_OK;
-  if (out_mode == PRE_OUT_STEM && (stem_ws & 1)) {
-    set_error("preprocess: stem row pitch must be even");
+  if (out_mode == PRE_OUT_STEM && stem_ws - IDN_CROP > 32) {
+    set_error("preprocess: stem row pitch too wide");
     return IDN_EINVAL;
   }
   // shared memory for the largest staged tile of this batch (images beyond the caps take the
   // direct path inside the kernel)
   const int raw_cap = raw_words < 64 ? 64 : (raw_words > kPreMaxRawWords ? kPreMaxRawWords : raw_words);
   const int rows_cap = src_rows < 1 ? 1 : (src_rows > kPreMaxSrcRows ? kPreMaxSrcRows : src_rows);
-  const int smem = (raw_cap + rows_cap * IDN_CROP + kPreRows * IDN_CROP) * 4 + 768 * 2;
+  const int smem = (raw_cap + rows_cap * IDN_CROP) * 4 + 768 * 2;
   if (out_mode == PRE_OUT_NCHW) {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_NCHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     preprocess_kernel<PRE_OUT_NCHW><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
@@ -325,7 +305,7 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
         d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap);
   } else {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, smem, st>>>(
+    preprocess_kernel<PRE_OUT_S2D4><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
         d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap);
   }
   IDN_CUDA_TRY(cudaGetLastError());

@@ -262,6 +262,8 @@ def run_reference(args, rank, world):
     import torch
     from idunno_b200.synth import make_state_dict
     from oracle import ref_path
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host core it can
+    torch.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     per_step = 32
     res = {}
     for model in ("alexnet", "resnet18"):

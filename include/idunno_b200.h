@@ -140,7 +140,7 @@ int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h,
  * (NULL = the legacy default stream) and d_out_nchw_bf16 is complete once that stream has been
  * synchronised.  offsets/hw are host arrays as elsewhere.
  * The first call on a device looks up the array's device address and uploads the normalisation
- * table (a blocking copy); make that first call before starting any stream capture.
+ * table (an extra copy on cuda_stream); make that first call before starting any stream capture.
  * Every call on a device shares the one array: it is rewritten by each call (nothing from an
  * earlier call is read), so two calls whose GPU work overlaps -- different streams, or different
  * threads -- race on it.  Serialise calls per device, or order them on one stream. */

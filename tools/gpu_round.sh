@@ -37,8 +37,8 @@ ncu)
 ncufull)
   m=${NCU_MODEL:-resnet18}
   timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_full.log 2>&1 &&
-  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:conv_tc_kernel \
-      -s ${NCU_SKIP:-60} -c ${NCU_COUNT:-20} -o gpurun_out/prof_$m -f python bench.py --steps 2 --warmup 3 --models $m \
+  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:${NCU_REGEX:-conv_tc_kernel} \
+      -s ${NCU_SKIP:-60} -c ${NCU_COUNT:-20} -o gpurun_out/prof_${NCU_TAG:-$m} -f python bench.py --steps 2 --warmup 3 --models $m \
       > gpurun_out/ncu_full_$m.log 2>&1
   echo "ncu full $m rc=$?" ;;
 esac

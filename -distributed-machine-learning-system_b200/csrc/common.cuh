@@ -58,14 +58,16 @@ inline float bf16_bits_to_f32(uint16_t b) {
 // a pad column).  A filter tap (r, s) of a stride-1 convolution is then the constant row offset
 // (r-pad)*Wp + (s-pad), i.e. a plain 2-D TMA box over the [rows][C] matrix.  Stride-2 convolutions
 // read "parity planes" (the producing layer scatters pixel (h,w) to plane (h&1, w&1)), which makes
-// their taps constant row offsets as well.  The two stem convolutions (C=3) use a 5-D tensor map
-// with overlapping strides over a 4-channel NHWC image (see conv_tc.cu).
+// their taps constant row offsets as well.  ResNet18's 7x7/s2 stem reads a 4-channel NHWC image
+// through a no-swizzle descriptor whose core matrices overlap (stem_toeplitz_kernel, conv_tc.cu);
+// AlexNet's 11x11/s4 stem is a 3x3 convolution over a 4x4 space-to-depth image.
 // ---------------------------------------------------------------------------------------------
 constexpr int kMaxTaps = 32;
 constexpr int kBlockM = 128;   // GEMM rows (pixels) per tile == TMEM lanes
 constexpr int kBlockK = 64;    // bf16 channels per k-block == one 128-byte swizzle row
-constexpr int kStemTW = 16;    // stem tile: 16 x 8 output pixels
-constexpr int kStemTH = 8;
+constexpr int kStemTW = 8;     // ResNet stem tile: 16 rows x 8 columns of output pixels
+constexpr int kStemTH = 16;
+constexpr int kStemWin = 32;   // elements per filter row: 8-pixel window x 4 channels (7 taps used)
 
 enum { MODE_FLAT = 0, MODE_STEM = 1 };
 enum { DEST_GEOM = 0, DEST_PARITY = 1 };
@@ -102,6 +104,7 @@ struct ConvParams {
   int ktot;                   // elements per B row (= num_taps * c_blocks * 64)
   int st_stride, st_ws, st_h, st_ow, st_nrow;   // stem image: conv stride, row pitch (px), rows,
                                                 // window starts per row, row groups per image
+  const bf16* stem_w;         // stem weights in the shared-memory order of stem_toeplitz_kernel
   // halo kernel (conv_halo_kernel): one staged A tile per 64-channel block serves every tap
   int halo_lo;                // smallest tap offset (rows)
   int halo_r1, halo_r2;       // rows of the two TMA boxes that make up the staged tile (r2 may be 0)
@@ -126,8 +129,8 @@ int conv_tc_configure();   // cudaFuncSetAttribute for every instantiation; once
 // tensor maps (conv_tc.cu)
 int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner_elems, uint64_t rows,
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
-int make_tmap_stem(CUtensorMap* tm, const void* base, int conv_stride, int ws_px, int img_h, int ow,
-                   int nimg_cap);
+int make_tmap_stem(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
+int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st);
 
 // other kernels (pool_head.cu)
 struct PoolParams {

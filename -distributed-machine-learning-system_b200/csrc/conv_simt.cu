@@ -7,23 +7,27 @@
 namespace idn {
 
 __device__ __forceinline__ float simt_load_a(const ConvParams& p, int m_tile, int i, int k) {
+  if (p.mode == MODE_STEM) {           // k = r * 32 + (window pixel * 4 + channel)
+    const int per_img = p.tiles_w * p.tiles_h;
+    const int n = m_tile / per_img;
+    const int t = m_tile - n * per_img;
+    const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
+    const int oh = th * kStemTH + i / kStemTW;
+    const int ow = tw * kStemTW + i % kStemTW;
+    const int r = k / kStemWin, e = k - r * kStemWin;
+    const int grp = oh + p.tap_off[r];
+    if (grp < 0 || grp >= p.st_nrow) return 0.0f;
+    const long long row = (long long)n * p.st_h + (long long)grp * 2 + p.tap_par[r];
+    return __bfloat162float(p.a_ptr[(row * p.st_ws + 2LL * ow) * 4 + e]);
+  }
   const int tap = k / (p.c_blocks * kBlockK);
   const int c = k - tap * (p.c_blocks * kBlockK);
-  if (p.mode == MODE_FLAT) {
+  {
     const long long row = (long long)m_tile * kBlockM + i + p.tap_off[tap];
     if (row < 0 || row >= p.a_rows) return 0.0f;
     return __bfloat162float(p.a_ptr[row * p.a_ld + c]);
   }
-  const int per_img = p.tiles_w * p.tiles_h;
-  const int n = m_tile / per_img;
-  const int t = m_tile - n * per_img;
-  const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
-  const int oh = th * kStemTH + i / kStemTW;
-  const int ow = tw * kStemTW + i % kStemTW;
-  const int grp = oh + p.tap_off[tap];
-  if (ow >= p.st_ow || grp < 0 || grp >= p.st_nrow) return 0.0f;
-  const long long row = (long long)n * p.st_h + (long long)grp * p.st_stride + p.tap_par[tap];
-  return __bfloat162float(p.a_ptr[(row * p.st_ws + (long long)ow * p.st_stride) * 4 + c]);
+  return 0.0f;
 }
 
 struct SimtRow {

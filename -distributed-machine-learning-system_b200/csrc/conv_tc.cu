@@ -14,12 +14,7 @@
 //   residual add -> optional ReLU -> bf16 (or fp32 logits) with 128-bit stores, written either in
 //   the tile's own geometry or scattered to the parity planes a following stride-2 layer reads.
 //
-// Stem convolutions (C = 3; ResNet18 7x7 s2 p3, AlexNet 11x11 s4 p2) use MODE_STEM: the
-// preprocess kernel writes the normalised image as 4-channel NHWC with the convolution's left
-// padding materialised, and a 5-D tensor map with OVERLAPPING strides does the im2col: dim0 is a
-// 16-pixel (64-element, 128-byte) window, dim1 steps by `stride` pixels (16/32 bytes) per output
-// column, dim2 is the row phase, dim3 the row group (OOB rows = zero padding), dim4 the image.
-// One k-block per filter row; window positions beyond the filter width meet zero weights.
+// ResNet18's stem (7x7 s2 p3, C = 3) has its own kernel, stem_toeplitz_kernel, below.
 #include <algorithm>
 #include <cstdlib>
 
@@ -292,7 +287,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo
   }
 }
 
-template <int BLOCK_N, int MODE>
+template <int BLOCK_N>
 __global__ void __launch_bounds__(256, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ ConvParams p) {
@@ -346,27 +341,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
         const int m_tile = tile / p.num_n_tiles;
         const int n_tile = tile - m_tile * p.num_n_tiles;
-        int st_n = 0, st_th = 0, st_tw = 0;
-        if (MODE == MODE_STEM) {
-          const int per_img = p.tiles_w * p.tiles_h;
-          st_n = m_tile / per_img;
-          const int t = m_tile - st_n * per_img;
-          st_th = t / p.tiles_w;
-          st_tw = t - st_th * p.tiles_w;
-        }
         int tap = 0, cb = 0;
         for (int kb = 0; kb < k_blocks; ++kb) {
           if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb)) { alive = false; break; }
           const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
           const uint32_t b_dst = a_dst + Cfg::A_BYTES;
           ptx::mbar_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
-          if (MODE == MODE_FLAT) {
-            ptx::tma_load_2d(a_dst, &tmA, full_bar(s), cb * kBlockK,
-                             m_tile * kBlockM + p.tap_off[tap]);
-          } else {
-            ptx::tma_load_5d(a_dst, &tmA, full_bar(s), 0, st_tw * kStemTW, p.tap_par[tap],
-                             st_th * kStemTH + p.tap_off[tap], st_n);
-          }
+          ptx::tma_load_2d(a_dst, &tmA, full_bar(s), cb * kBlockK,
+                           m_tile * kBlockM + p.tap_off[tap]);
           ptx::tma_load_2d(b_dst, &tmB, full_bar(s), kb * kBlockK, n_tile * BLOCK_N);
           if (++cb == p.c_blocks) { cb = 0; ++tap; }
           if (++s == kStages) { s = 0; ph ^= 1u; }
@@ -632,10 +614,148 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   }
 }
 
+// =============================================================================================
+// stem_toeplitz_kernel: ResNet18 conv1 (7x7, stride 2, pad 3, C = 3 -> 64) + BN + ReLU.
+//
+// The preprocess kernel writes the image as 4-channel NHWC bf16 with 3 zero pixels of left padding,
+// so output column ow reads stored pixels 2*ow .. 2*ow+7 of a row (7 taps + one zero-weight pixel):
+// 32 contiguous elements that START 16 BYTES AFTER the previous column's.  A no-swizzle K-major
+// UMMA descriptor with leading-dimension offset 16 B describes exactly that overlapping matrix,
+//     A[m = 8g + i][k] = strip_g[8 i + k],   address = start + g * SBO + i * 16 + (k / 8) * LBO,
+// so the tensor core performs the im2col itself from the RAW image strips (verified on hardware with
+// tools/exp_toeplitz.cu).  Per filter row r a 16 x 8 output tile needs 16 strips of 11 pixel pairs
+// (176 B each, SBO = 176): 2.8 KB instead of the 16 KB an im2col'ed box would take, which removes the
+// L2 -> SM traffic that bounded the first version of this layer.  The 28 KB of weights stay resident
+// in shared memory in the canonical no-swizzle order.  K per filter row = 32 -> two MMAs.
+// =============================================================================================
+constexpr int kStemStripBytes = 176;
+constexpr int kStemABytes = kStemTH * kStemStripBytes;          // 2816 bytes per TMA box
+constexpr int kStemAStageBytes = 3072;
+constexpr int kStemAStages = 16;
+constexpr int kStemWBytes = 7 * 4096;                           // [r][k chunk][n][8] bf16
+constexpr int kStemSmemBytes = kStemAStages * kStemAStageBytes + kStemWBytes + 512 + 1024;
+
+__device__ __forceinline__ uint64_t make_nosw_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(sbo_bytes >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;                                                     // layout type 0 = no swizzle
+}
+
+__global__ void __launch_bounds__(256, 1)
+stem_toeplitz_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+  const uint32_t w_base = base + kStemAStages * kStemAStageBytes;
+  const uint32_t bar_base = w_base + kStemWBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStemAStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStemAStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStemAStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStemAStages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.num_m_tiles;
+  const int per_img = p.tiles_w * p.tiles_h;
+
+  if (warp == 0 && lane == 0) ptx::prefetch_tmap(&tmA);
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStemAStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 4); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<128>(tmem_slot);
+  {   // resident weights: plain copy (already in shared-memory order), then hand over to the async proxy
+    const uint4* src = reinterpret_cast<const uint4*>(p.stem_w);
+    uint4* dst = reinterpret_cast<uint4*>(smem_raw + (w_base - raw_u32));
+    for (int i = threadIdx.x; i < kStemWBytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool alive = true;
+      for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+        const int n = tile / per_img;
+        const int t = tile - n * per_img;
+        const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
+        for (int r = 0; r < 7; ++r) {
+          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, r)) { alive = false; break; }
+          ptx::mbar_expect_tx(full_bar(s), kStemABytes);
+          ptx::tma_load_5d(base + s * kStemAStageBytes, &tmA, full_bar(s), 0, tw * kStemTW,
+                           p.tap_par[r], th * kStemTH + p.tap_off[r], n);
+          if (++s == kStemAStages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(kBlockM, 64);
+    int s = 0, as = 0;
+    uint32_t ph = 0, aph = 0;
+    bool alive = true;
+    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile)) break;
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * 64);
+      for (int r = 0; r < 7; ++r) {
+        if (!mbar_wait(full_bar(s), ph, 2, r)) { alive = false; break; }
+        ptx::tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = base + s * kStemAStageBytes;
+          const uint32_t b_addr = w_base + r * 4096;
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            const uint64_t da = make_nosw_desc(a_addr + 32u * k, 16u, kStemStripBytes);
+            const uint64_t db = make_nosw_desc(b_addr + 2048u * k, 1024u, 128u);
+            ptx::umma_bf16(d_tmem, da, db, idesc, (r | k) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(empty_bar(s));
+          if (r == 6) ptx::umma_commit(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++s == kStemAStages) { s = 0; ph ^= 1u; }
+      }
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    const int ew = warp - 4;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const RowInfo ri = decode_row(p, tile, ew * 32 + lane);
+      if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64);
+      epilogue_tile<64>(p, ri, taddr, 0);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<128>(tmem_base);
+  }
+}
+
 // --------------------------------------------------------------------------------------- host
-template <int BLOCK_N, int MODE>
+template <int BLOCK_N>
 static int configure_one() {
-  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_tc_kernel<BLOCK_N, MODE>,
+  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_tc_kernel<BLOCK_N>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     TcCfg<BLOCK_N>::SMEM_BYTES));
   return IDN_OK;
@@ -657,21 +777,20 @@ int read_tc_watchdog() {
 }
 
 int conv_tc_configure() {
-  IDN_TRY((configure_one<64, MODE_FLAT>()));
-  IDN_TRY((configure_one<128, MODE_FLAT>()));
-  IDN_TRY((configure_one<192, MODE_FLAT>()));
-  IDN_TRY((configure_one<256, MODE_FLAT>()));
-  IDN_TRY((configure_one<64, MODE_STEM>()));
+  IDN_TRY((configure_one<64>()));
+  IDN_TRY((configure_one<128>()));
+  IDN_TRY((configure_one<192>()));
+  IDN_TRY((configure_one<256>()));
   return IDN_OK;
 }
 
-template <int BLOCK_N, int MODE>
+template <int BLOCK_N>
 static int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
                       int num_sms, cudaStream_t st) {
   const int total = p.num_m_tiles * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   const int grid = total < num_sms ? total : num_sms;
-  conv_tc_kernel<BLOCK_N, MODE><<<grid, 256, TcCfg<BLOCK_N>::SMEM_BYTES, st>>>(tmA, tmB, p);
+  conv_tc_kernel<BLOCK_N><<<grid, 256, TcCfg<BLOCK_N>::SMEM_BYTES, st>>>(tmA, tmB, p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
@@ -682,15 +801,12 @@ int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvPar
     set_error("launch_conv_tc: n_total is not a multiple of the N tile");
     return IDN_EINVAL;
   }
-  if (p.mode == MODE_STEM) {
-    if (block_n != 64) { set_error("launch_conv_tc: stem uses BLOCK_N=64"); return IDN_EINVAL; }
-    return launch_one<64, MODE_STEM>(tmA, tmB, p, num_sms, st);
-  }
+  if (p.mode != MODE_FLAT) { set_error("launch_conv_tc: flat layouts only"); return IDN_EINVAL; }
   switch (block_n) {
-    case 64: return launch_one<64, MODE_FLAT>(tmA, tmB, p, num_sms, st);
-    case 128: return launch_one<128, MODE_FLAT>(tmA, tmB, p, num_sms, st);
-    case 192: return launch_one<192, MODE_FLAT>(tmA, tmB, p, num_sms, st);
-    case 256: return launch_one<256, MODE_FLAT>(tmA, tmB, p, num_sms, st);
+    case 64: return launch_one<64>(tmA, tmB, p, num_sms, st);
+    case 128: return launch_one<128>(tmA, tmB, p, num_sms, st);
+    case 192: return launch_one<192>(tmA, tmB, p, num_sms, st);
+    case 256: return launch_one<256>(tmA, tmB, p, num_sms, st);
   }
   set_error("launch_conv_tc: unsupported N tile");
   return IDN_EINVAL;
@@ -740,26 +856,35 @@ int make_tmap_2d(CUtensorMap* tm, const void* base_ptr, uint64_t inner_elems, ui
   return IDN_OK;
 }
 
-int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int conv_stride, int ws_px, int img_h,
-                   int ow, int nimg_cap) {
+// 5-D map over the 4-channel stem image: (8 elements = 2 pixels, pixel pair, row phase, row group,
+// image); one box = 16 row groups x 11 pixel pairs = the 16 strips (176 bytes each) of one filter
+// row of one 16 x 8 output tile.  Row groups outside the image read as zeros (the vertical padding).
+int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int ws_px, int img_h, int nimg_cap) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return IDN_ECUDA;
-  const uint64_t px = 8;                                   // 4 bf16 channels
-  const uint64_t row = (uint64_t)ws_px * px;
-  cuuint64_t gdim[5] = {64, (cuuint64_t)ow, (cuuint64_t)conv_stride,
-                        (cuuint64_t)(img_h / conv_stride), (cuuint64_t)nimg_cap};
-  cuuint64_t gstr[4] = {(cuuint64_t)conv_stride * px, row, (cuuint64_t)conv_stride * row,
-                        (cuuint64_t)img_h * row};
-  cuuint32_t box[5] = {64, (cuuint32_t)kStemTW, 1, (cuuint32_t)kStemTH, 1};
+  const uint64_t row = (uint64_t)ws_px * 8;                // bytes per image row (4 bf16 channels)
+  cuuint64_t gdim[5] = {8, (cuuint64_t)(ws_px / 2), 2, (cuuint64_t)(img_h / 2), (cuuint64_t)nimg_cap};
+  cuuint64_t gstr[4] = {16, row, 2 * row, (cuuint64_t)img_h * row};
+  cuuint32_t box[5] = {8, 11, 1, (cuuint32_t)kStemTH, 1};
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base_ptr), gdim, gstr,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled(stem 5d, overlapping strides) failed with CUresult " +
-              std::to_string((int)r));
+    set_error("cuTensorMapEncodeTiled(stem 5d) failed with CUresult " + std::to_string((int)r));
     return IDN_ECUDA;
   }
+  return IDN_OK;
+}
+
+int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st) {
+  const int total = p.num_m_tiles;
+  if (total <= 0) return IDN_OK;
+  if (p.mode != MODE_STEM || p.num_taps != 7 || p.stem_w == nullptr) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
+  IDN_CUDA_TRY(cudaFuncSetAttribute(stem_toeplitz_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmemBytes));
+  const int grid = total < num_sms ? total : num_sms;
+  stem_toeplitz_kernel<<<grid, 256, kStemSmemBytes, st>>>(tmA, p);
+  IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
 

@@ -37,6 +37,7 @@ struct ConvWeights {     // device, kernel layout
   float* scale = nullptr;
   float* shift = nullptr;
   int n_total = 0, ktot = 0, taps = 0, c_blocks = 0;
+  bf16* stem_flat = nullptr;   // ResNet stem only: weights in stem_toeplitz_kernel's smem order
 };
 
 enum StepKind { STEP_PRE = 0, STEP_CONV, STEP_POOL, STEP_RHEAD, STEP_SOFTMAX };
@@ -153,21 +154,27 @@ static int upload_conv_weights(idn_engine* e, ConvWeights* cw, const float* w, i
   return IDN_OK;
 }
 
-// Stem weights [64][3][R][S] -> [64][R*64]: k = r*64 + s*4 + c (window position s, channel c of the
-// 4-channel pixel); everything else zero.
+// ResNet stem weights [64][3][7][7] -> K-major [64][7*32] with k = r*32 + s*4 + c (window pixel s,
+// channel c of the 4-channel pixel; s = 7 and c = 3 are zero), plus the same values in the
+// shared-memory order of stem_toeplitz_kernel: [r][k chunk of 8][n][8].
 static int upload_stem_weights(idn_engine* e, ConvWeights* cw, const float* w, int cout, int R,
                                int S, const float* scale, const float* shift) {
-  cw->taps = R; cw->c_blocks = 1; cw->ktot = R * 64; cw->n_total = 64;
-  if (cout != 64 || S * 4 > 64) { set_error("stem: unsupported shape"); return IDN_EINVAL; }
-  std::vector<uint16_t> h((size_t)64 * cw->ktot, 0);
+  if (cout != 64 || R != 7 || S != 7) { set_error("stem: only the 7x7 stride-2 ResNet stem"); return IDN_EINVAL; }
+  cw->taps = R; cw->c_blocks = 1; cw->ktot = R * kStemWin; cw->n_total = 64;
+  std::vector<uint16_t> h((size_t)64 * cw->ktot, 0), flat((size_t)64 * cw->ktot, 0);
   for (int n = 0; n < cout; ++n)
     for (int c = 0; c < 3; ++c)
       for (int r = 0; r < R; ++r)
-        for (int s = 0; s < S; ++s)
-          h[(size_t)n * cw->ktot + r * 64 + s * 4 + c] =
-              f32_to_bf16_bits(w[(((size_t)n * 3 + c) * R + r) * S + s]);
+        for (int s = 0; s < S; ++s) {
+          const uint16_t v = f32_to_bf16_bits(w[(((size_t)n * 3 + c) * R + r) * S + s]);
+          const int kk = s * 4 + c;                       // 0..31 inside the filter row
+          h[(size_t)n * cw->ktot + r * kStemWin + kk] = v;
+          flat[((size_t)(r * 4 + kk / 8) * 64 + n) * 8 + kk % 8] = v;
+        }
   IDN_TRY(dev_alloc(e, &cw->wt, h.size(), false));
   IDN_CUDA_TRY(cudaMemcpy(cw->wt, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+  IDN_TRY(dev_alloc(e, &cw->stem_flat, flat.size(), false));
+  IDN_CUDA_TRY(cudaMemcpy(cw->stem_flat, flat.data(), flat.size() * 2, cudaMemcpyHostToDevice));
   std::vector<float> sc(64), sh(64);
   for (int n = 0; n < 64; ++n) { sc[n] = scale ? scale[n] : 1.0f; sh[n] = shift ? shift[n] : 0.0f; }
   IDN_TRY(dev_alloc(e, &cw->scale, 64, false));
@@ -288,7 +295,9 @@ static int add_stem(idn_engine* e, const std::string& name, const void* xs, int 
   ConvParams& cp = st.cp;
   std::memset(&cp, 0, sizeof(cp));
   cp.mode = MODE_STEM;
+  if (R != 7 || stride != 2 || pad != 3 || OH != 112 || OW != 112) { set_error(name + ": unsupported stem"); return IDN_EINVAL; }
   cp.num_taps = R; cp.c_blocks = 1;
+  cp.stem_w = cw.stem_flat;
   for (int r = 0; r < R; ++r) {             // input row = stride*oh + r - pad = stride*(oh+a) + b
     const int d = r - pad;
     const int a = (int)std::floor((double)d / stride);
@@ -305,8 +314,7 @@ static int add_stem(idn_engine* e, const std::string& name, const void* xs, int 
   cp.st_stride = stride; cp.st_ws = ws; cp.st_h = IDN_CROP; cp.st_ow = OW;
   cp.st_nrow = IDN_CROP / stride;
   st.block_n = 64;
-  if (!e->stem_simt) IDN_TRY(make_tmap_stem(&st.tmA, xs, stride, ws, IDN_CROP, OW, cap));
-  IDN_TRY(make_tmap_2d(&st.tmB, cw.wt, (uint64_t)cw.ktot, 64, (uint64_t)cw.ktot * 2, kBlockK, 64));
+  if (!e->stem_simt) IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
   e->steps.push_back(st);
   return IDN_OK;
 }
@@ -584,7 +592,7 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
   else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
   if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
-  if (cp.mode == MODE_STEM && e->stem_simt) return launch_conv_simt(cp, st);
+  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, cp, e->num_sms, st);
   if (s.use_halo) {
     const int item_rows = kBlockM * cp.msub;
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
@@ -923,8 +931,8 @@ int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h,
   std::vector<uint16_t> hbuf;
   if (cin == 3) {
     // stem path: x must be [n][3][224][224]
-    if (h != IDN_CROP || w != IDN_CROP || cout != 64 || !((r == 7 && stride == 2 && pad == 3) || (r == 11 && stride == 4 && pad == 2))) {
-      set_error("idn_conv2d_nchw: cin=3 supports the two stem shapes only"); return done(IDN_EINVAL);
+    if (h != IDN_CROP || w != IDN_CROP || cout != 64 || !(r == 7 && stride == 2 && pad == 3)) {
+      set_error("idn_conv2d_nchw: cin=3 supports the 7x7 stride-2 stem only"); return done(IDN_EINVAL);
     }
     const int ws = 232, left = pad;
     bf16* xs = nullptr;

@@ -42,8 +42,8 @@ SHAPES = [
     (20, 512, 7, 7, 512, 3, 1, 1, True, True),      # layer4
     (4, 64, 27, 27, 192, 5, 1, 2, False, True),     # AlexNet features.3 (25 taps, N=192)
     (6, 192, 13, 13, 384, 3, 1, 1, False, True),    # AlexNet features.6
-    (2, 3, 224, 224, 64, 7, 2, 3, False, True),     # ResNet18 stem (5-D overlapping-stride TMA)
-    (2, 3, 224, 224, 64, 11, 4, 2, False, True),    # AlexNet stem
+    (2, 3, 224, 224, 64, 7, 2, 3, False, True),     # ResNet18 stem (overlapping no-swizzle descriptor)
+    (5, 3, 224, 224, 64, 7, 2, 3, False, False),    # same, more tiles than SMs, no ReLU
 ]
 
 

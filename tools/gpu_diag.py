@@ -59,7 +59,7 @@ for (r, s) in ((0, 0), (1, 1), (2, 2)):
     run(f"conv3x3s2_tap{r}{s}", xc, wc, stride=2, pad=1)
 # f. stems with one non-zero tap
 xs = bf(rng.standard_normal((1, 3, 224, 224)))
-for (R, st, pd) in ((7, 2, 3), (11, 4, 2)):
+for (R, st, pd) in ((7, 2, 3),):
     for (r, s) in ((0, 0), (R // 2, R // 2), (R - 1, R - 1)):
         ws = np.zeros((64, 3, R, R), np.float32)
         ws[0, 0, r, s] = 1.0; ws[1, 1, r, s] = 1.0; ws[2, 2, r, s] = 1.0

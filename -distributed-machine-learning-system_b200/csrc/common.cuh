@@ -124,13 +124,16 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
 int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                      const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st);
 int read_tc_watchdog();
+int read_tc_wait_cycles(unsigned long long* out8);
 int conv_tc_configure();   // cudaFuncSetAttribute for every instantiation; once per process/device
 
 // tensor maps (conv_tc.cu)
 int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner_elems, uint64_t rows,
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
 int make_tmap_stem(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
-int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st);
+int make_tmap_stem_w(CUtensorMap* tm, const void* wt, int ktot);
+int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int num_sms,
+                   cudaStream_t st);
 
 // other kernels (pool_head.cu)
 struct PoolParams {

@@ -65,6 +65,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
       ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                            int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
                                             int c0, int c1, int c2, int c3, int c4) {
   asm volatile(
@@ -123,6 +131,26 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)
       : "r"(taddr)
       : "memory");
 }
+// 256-bit global accesses (sm_100): a thread's 32 bytes are one full DRAM/L2 sector, so row-per-thread
+// epilogue stores do not turn into partial-sector writes.
+__device__ __forceinline__ void st_global_256(void* ptr, const uint32_t (&w)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "r"(w[0]), "r"(w[1]),
+               "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+__device__ __forceinline__ void ld_global_256(const void* ptr, uint32_t (&w)[8]) {
+  asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+               : "l"(ptr));
+}
+// One lane of a converged warp.  The compiler knows that exactly one lane survives an elect.sync, so
+// operands of the tcgen05 instructions issued under it move to uniform registers directly
+// (an `if (lane == 0)` makes it emit a waterfall loop around every descriptor).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -135,7 +163,24 @@ __device__ __forceinline__ void tmem_ld_wait() {
 // the kernel with an error the host can read (read_tc_watchdog) instead of hanging the GPU.
 __device__ unsigned int g_tc_watchdog[4];
 
+// Cycles spent blocked in each kind of pipeline wait, summed over all CTAs (one lane per waiting
+// warp counts): [0] A/TMA producer waits for a free stage, [1] MMA waits for the epilogue to drain
+// an accumulator, [2] MMA waits for A, [3] epilogue waits for the MMA, [4] B producer waits for a
+// free stage, [5] MMA waits for resident weights, [6] MMA waits for B, [7] unused.  Read and reset by
+// read_tc_wait_cycles(); used by bench.py to say which role a kernel is bound by.
+__device__ unsigned long long g_tc_wait_cycles[8];
+
 __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, int role, int where) {
+  // mbarrier.try_wait may itself block for a while before it answers, so the clock starts before
+  // the first probe; anything longer than a probe's own latency is booked as waiting.
+  const long long c0 = clock64();
+  struct Tally {
+    int role; long long c0;
+    __device__ ~Tally() {
+      const long long dt = clock64() - c0;
+      if (dt > 200 && (threadIdx.x & 31) == 0) atomicAdd(&g_tc_wait_cycles[role & 7], (unsigned long long)dt);
+    }
+  } tally{role, c0};
   if (ptx::mbar_try_wait(bar, parity)) return true;
   const unsigned long long t0 = ptx::globaltimer();
   unsigned int spins = 0;
@@ -229,37 +274,49 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 
 // TMEM accumulator rows -> scale/shift (+residual) (+ReLU) -> bf16 / fp32, 32 columns at a time.
 // Every lane of the warp must call it (tcgen05.ld is warp-collective); stores are predicated.
+// Eight epilogue warps share a tile: warps 4..7 and 8..11 own the same four TMEM lane quarters and
+// take alternate 32-column chunks (chunk0, chunk0 + 2, ...).  The TMEM load, the scale/shift loads
+// and the residual loads of a chunk are all issued before the first wait, so their latencies overlap.
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 128 + 32 * kEpiWarps;
+
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
-                                          int col0) {
+                                              int col0, int chunk0) {
 #pragma unroll 1
-  for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+  for (int c0 = chunk0 * 32; c0 < BLOCK_N; c0 += 64) {
     uint32_t v[32];
     ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, v);
+    const int col = col0 + c0;
+    const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
+    const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
+    float4 s4[8], b4[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s4[j] = __ldg(sc + j); b4[j] = __ldg(sh + j); }
+    const bool has_res = p.residual != nullptr && ri.valid;
+    uint32_t rr[2][8];
+    if (has_res) {
+      const bf16* rp = p.residual + ri.res_row * p.ldc + col;
+      ptx::ld_global_256(rp, rr[0]);
+      ptx::ld_global_256(rp + 16, rr[1]);
+    }
     ptx::tmem_ld_wait();
     if (ri.valid) {
-      const int col = col0 + c0;
-      const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
-      const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
       float y[32];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float4 s4 = __ldg(sc + j), b4 = __ldg(sh + j);
-        y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4.x, b4.x);
-        y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4.y, b4.y);
-        y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4.z, b4.z);
-        y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4.w, b4.w);
+        y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4[j].x, b4[j].x);
+        y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4[j].y, b4[j].y);
+        y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4[j].z, b4[j].z);
+        y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4[j].w, b4[j].w);
       }
-      if (p.residual != nullptr) {
-        const uint4* rp = reinterpret_cast<const uint4*>(p.residual + ri.res_row * p.ldc + col);
+      if (has_res) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint4 rr = __ldg(rp + j);
-          const uint32_t w4[4] = {rr.x, rr.y, rr.z, rr.w};
+        for (int j = 0; j < 2; ++j) {
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            y[8 * j + 2 * e + 0] += __uint_as_float(w4[e] << 16);
-            y[8 * j + 2 * e + 1] += __uint_as_float(w4[e] & 0xffff0000u);
+          for (int e = 0; e < 8; ++e) {
+            y[16 * j + 2 * e + 0] += __uint_as_float(rr[j][e] << 16);
+            y[16 * j + 2 * e + 1] += __uint_as_float(rr[j][e] & 0xffff0000u);
           }
         }
       }
@@ -268,27 +325,30 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo
         for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], 0.0f);
       }
       if (p.out_f32) {
-        float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
-                                               ri.dst_row * p.ldc + col);
+        float* op = reinterpret_cast<float*>(p.out) + ri.dst_row * p.ldc + col;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          op[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+        for (int j = 0; j < 4; ++j) {
+          uint32_t w[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) w[e] = __float_as_uint(y[8 * j + e]);
+          ptx::st_global_256(op + 8 * j, w);
+        }
       } else {
-        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) +
-                                             ri.dst_row * p.ldc + col);
+        bf16* op = reinterpret_cast<bf16*>(p.out) + ri.dst_row * p.ldc + col;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          op[j] = make_uint4(pack_bf16x2(y[8 * j + 0], y[8 * j + 1]),
-                             pack_bf16x2(y[8 * j + 2], y[8 * j + 3]),
-                             pack_bf16x2(y[8 * j + 4], y[8 * j + 5]),
-                             pack_bf16x2(y[8 * j + 6], y[8 * j + 7]));
+        for (int j = 0; j < 2; ++j) {
+          uint32_t w[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) w[e] = pack_bf16x2(y[16 * j + 2 * e], y[16 * j + 2 * e + 1]);
+          ptx::st_global_256(op + 16 * j, w);
+        }
       }
     }
   }
 }
 
 template <int BLOCK_N>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ ConvParams p) {
   using Cfg = TcCfg<BLOCK_N>;
@@ -322,7 +382,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
-      ptx::mbar_init(tempty_bar(a), 4);   // one arrive per epilogue warp
+      ptx::mbar_init(tempty_bar(a), kEpiWarps);   // one arrive per epilogue warp
     }
     ptx::fence_barrier_init();
   }
@@ -370,7 +430,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int kb = 0; kb < k_blocks; ++kb) {
         if (!mbar_wait(full_bar(s), ph, 2, kb)) { alive = false; break; }   // TMA bytes landed
         ptx::tc_fence_after();
-        if (lane == 0) {
+        if (ptx::elect_one()) {
           const uint32_t a_addr = base + s * Cfg::STAGE_BYTES;
           const uint64_t da = make_sw128_desc(a_addr);
           const uint64_t db = make_sw128_desc(a_addr + Cfg::A_BYTES);
@@ -390,7 +450,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp >= 4) {
     // ================================ epilogue ====================================
-    const int ew = warp - 4;                 // == warp % 4: TMEM lanes [32*ew, 32*ew+32)
+    const int ew = (warp - 4) & 3;           // == warp % 4: TMEM lanes [32*ew, 32*ew+32)
+    const int chunk0 = (warp - 4) >> 2;      // which alternate 32-column chunks this warp takes
     const int row_in_tile = ew * 32 + lane;
     int as = 0;
     uint32_t aph = 0;
@@ -401,7 +462,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N);
+      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
@@ -437,7 +498,7 @@ constexpr int kMaxAStages = 4;
 constexpr int kMaxBStages = 16;
 
 template <int BLOCK_N, int MSUB, bool BRES>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
   constexpr int B_BYTES = BLOCK_N * kBlockK * 2;
@@ -474,7 +535,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kMaxAStages; ++s) { ptx::mbar_init(a_full(s), 1); ptx::mbar_init(a_empty(s), 1); }
     for (int s = 0; s < kMaxBStages; ++s) { ptx::mbar_init(b_full(s), 1); ptx::mbar_init(b_empty(s), 1); }
-    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 4); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
     ptx::mbar_init(bres_bar, 1);
     ptx::fence_barrier_init();
   }
@@ -557,7 +618,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
             ptx::tc_fence_after();
             b_tile = b_base + (uint32_t)(sb * B_BYTES);
           }
-          if (lane == 0) {
+          if (ptx::elect_one()) {
             const uint64_t db = make_sw128_desc(b_tile);
             const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
 #pragma unroll
@@ -573,7 +634,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           __syncwarp();
           if (!BRES) { if (++sb == p.b_stages) { sb = 0; phb ^= 1u; } }
         }
-        if (lane == 0 && alive) {
+        if (alive && ptx::elect_one()) {
           ptx::umma_commit(a_empty(sa));
           if (cb == p.c_blocks - 1) ptx::umma_commit(tfull_bar(as));
         }
@@ -584,7 +645,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     }
   } else if (warp >= 4) {
     // ================================ epilogue ====================================
-    const int ew = warp - 4;
+    const int ew = (warp - 4) & 3;
+    const int chunk0 = (warp - 4) >> 2;
     int as = 0;
     uint32_t aph = 0;
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
@@ -597,7 +659,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         const RowInfo ri = decode_row(p, m_item * MSUB + sub, ew * 32 + lane);
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) +
                                (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
-        epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N);
+        epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -615,66 +677,64 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 }
 
 // =============================================================================================
-// stem_toeplitz_kernel: ResNet18 conv1 (7x7, stride 2, pad 3, C = 3 -> 64) + BN + ReLU.
+// stem_kernel: ResNet18 conv1 (7x7, stride 2, pad 3, C = 3 -> 64) + BN + ReLU.
 //
 // The preprocess kernel writes the image as 4-channel NHWC bf16 with 3 zero pixels of left padding,
 // so output column ow reads stored pixels 2*ow .. 2*ow+7 of a row (7 taps + one zero-weight pixel):
-// 32 contiguous elements that START 16 BYTES AFTER the previous column's.  A no-swizzle K-major
-// UMMA descriptor with leading-dimension offset 16 B describes exactly that overlapping matrix,
-//     A[m = 8g + i][k] = strip_g[8 i + k],   address = start + g * SBO + i * 16 + (k / 8) * LBO,
-// so the tensor core performs the im2col itself from the RAW image strips (verified on hardware with
-// tools/exp_toeplitz.cu).  Per filter row r a 16 x 8 output tile needs 16 strips of 11 pixel pairs
-// (176 B each, SBO = 176): 2.8 KB instead of the 16 KB an im2col'ed box would take, which removes the
-// L2 -> SM traffic that bounded the first version of this layer.  The 28 KB of weights stay resident
-// in shared memory in the canonical no-swizzle order.  K per filter row = 32 -> two MMAs.
+// 32 contiguous elements (64 bytes) that start 16 bytes after the previous column's.  A 5-D tensor
+// map with OVERLAPPING strides lets TMA do the im2col: dim0 = the 64-byte window, dim1 = output
+// column (stride 16 B), dim2 = row phase, dim3 = row group (out of range = zero padding), dim4 =
+// image.  One box = 8 columns x 16 rows of output pixels = 128 rows of 64 bytes, 64B-swizzled; one
+// k-block (K = 32, two MMAs) per filter row.  The 28 KB of weights stay resident in shared memory.
+// (Tried first: 128-byte windows -- twice the bytes and MMAs; and a no-swizzle "Toeplitz" descriptor
+// that reads the raw image strips with overlapping core matrices, tools/exp_toeplitz.cu -- correct,
+// 6x less operand traffic, but no-swizzle operands are fetched at a fraction of the swizzled rate:
+// 280 cycles per 128x64x16 MMA instead of ~83.)
 // =============================================================================================
-constexpr int kStemStripBytes = 176;
-constexpr int kStemABytes = kStemTH * kStemStripBytes;          // 2816 bytes per TMA box
-constexpr int kStemAStageBytes = 3072;
-constexpr int kStemAStages = 16;
-constexpr int kStemWBytes = 7 * 4096;                           // [r][k chunk][n][8] bf16
-constexpr int kStemSmemBytes = kStemAStages * kStemAStageBytes + kStemWBytes + 512 + 1024;
+constexpr int kStemABytes = kBlockM * kStemWin * 2;              // 8 KiB per k-block
+constexpr int kStemAStages = 8;
+constexpr int kStemWTile = 64 * kStemWin * 2;                    // 4 KiB of weights per filter row
+constexpr int kStemSmemBytes = kStemAStages * kStemABytes + 7 * kStemWTile + 512 + 1024;
 
-__device__ __forceinline__ uint64_t make_nosw_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// K-major, 64B-swizzled tile: rows of 64 bytes, 8-row groups 512 bytes apart, layout type 4.
+__device__ __forceinline__ uint64_t make_sw64_desc(uint32_t smem_addr) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
-  d |= (uint64_t)(lbo_bytes >> 4) << 16;
-  d |= (uint64_t)(sbo_bytes >> 4) << 32;
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(512 >> 4) << 32;
   d |= (uint64_t)1 << 46;
-  return d;                                                     // layout type 0 = no swizzle
+  d |= (uint64_t)4 << 61;
+  return d;
 }
 
-__global__ void __launch_bounds__(256, 1)
-stem_toeplitz_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ ConvParams p) {
+__global__ void __launch_bounds__(kThreads, 1)
+stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw_u32 + 1023u) & ~1023u;
-  const uint32_t w_base = base + kStemAStages * kStemAStageBytes;
-  const uint32_t bar_base = w_base + kStemWBytes;
+  const uint32_t w_base = base + kStemAStages * kStemABytes;
+  const uint32_t bar_base = w_base + 7 * kStemWTile;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStemAStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStemAStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStemAStages + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kStemAStages + 4);
+  const uint32_t w_bar = bar_base + 8u * (2 * kStemAStages + 4);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStemAStages + 5);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.num_m_tiles;
   const int per_img = p.tiles_w * p.tiles_h;
 
-  if (warp == 0 && lane == 0) ptx::prefetch_tmap(&tmA);
+  if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmA); ptx::prefetch_tmap(&tmB); }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStemAStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 4); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
+    ptx::mbar_init(w_bar, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<128>(tmem_slot);
-  {   // resident weights: plain copy (already in shared-memory order), then hand over to the async proxy
-    const uint4* src = reinterpret_cast<const uint4*>(p.stem_w);
-    uint4* dst = reinterpret_cast<uint4*>(smem_raw + (w_base - raw_u32));
-    for (int i = threadIdx.x; i < kStemWBytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -692,18 +752,25 @@ stem_toeplitz_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         for (int r = 0; r < 7; ++r) {
           if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, r)) { alive = false; break; }
           ptx::mbar_expect_tx(full_bar(s), kStemABytes);
-          ptx::tma_load_5d(base + s * kStemAStageBytes, &tmA, full_bar(s), 0, tw * kStemTW,
-                           p.tap_par[r], th * kStemTH + p.tap_off[r], n);
+          ptx::tma_load_5d(base + s * kStemABytes, &tmA, full_bar(s), 0, tw * kStemTW, p.tap_par[r],
+                           th * kStemTH + p.tap_off[r], n);
           if (++s == kStemAStages) { s = 0; ph ^= 1u; }
         }
       }
+    }
+    __syncwarp();
+  } else if (warp == 3) {
+    if (lane == 0) {                                   // resident weights: 7 boxes of 64 x 32
+      ptx::mbar_expect_tx(w_bar, 7 * kStemWTile);
+      for (int r = 0; r < 7; ++r)
+        ptx::tma_load_2d(w_base + r * kStemWTile, &tmB, w_bar, r * kStemWin, 0);
     }
     __syncwarp();
   } else if (warp == 1) {
     constexpr uint32_t idesc = make_idesc(kBlockM, 64);
     int s = 0, as = 0;
     uint32_t ph = 0, aph = 0;
-    bool alive = true;
+    bool alive = mbar_wait(w_bar, 0u, 5, 0);
     for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
       if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile)) break;
       ptx::tc_fence_after();
@@ -711,15 +778,12 @@ stem_toeplitz_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       for (int r = 0; r < 7; ++r) {
         if (!mbar_wait(full_bar(s), ph, 2, r)) { alive = false; break; }
         ptx::tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = base + s * kStemAStageBytes;
-          const uint32_t b_addr = w_base + r * 4096;
+        if (ptx::elect_one()) {
+          const uint64_t da = make_sw64_desc(base + s * kStemABytes);
+          const uint64_t db = make_sw64_desc(w_base + r * kStemWTile);
 #pragma unroll
-          for (int k = 0; k < 2; ++k) {
-            const uint64_t da = make_nosw_desc(a_addr + 32u * k, 16u, kStemStripBytes);
-            const uint64_t db = make_nosw_desc(b_addr + 2048u * k, 1024u, 128u);
-            ptx::umma_bf16(d_tmem, da, db, idesc, (r | k) != 0 ? 1u : 0u);
-          }
+          for (int k = 0; k < 2; ++k)
+            ptx::umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (r | k) != 0 ? 1u : 0u);
           ptx::umma_commit(empty_bar(s));
           if (r == 6) ptx::umma_commit(tfull_bar(as));
         }
@@ -729,7 +793,8 @@ stem_toeplitz_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       if (++as == 2) { as = 0; aph ^= 1u; }
     }
   } else if (warp >= 4) {
-    const int ew = warp - 4;
+    const int ew = (warp - 4) & 3;
+    const int chunk0 = (warp - 4) >> 2;
     int as = 0;
     uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -737,7 +802,7 @@ stem_toeplitz_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64);
-      epilogue_tile<64>(p, ri, taddr, 0);
+      epilogue_tile<64>(p, ri, taddr, 0, chunk0);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
@@ -776,6 +841,13 @@ int read_tc_watchdog() {
   return IDN_OK;
 }
 
+int read_tc_wait_cycles(unsigned long long* out8) {
+  unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  IDN_CUDA_TRY(cudaMemcpyFromSymbol(out8, g_tc_wait_cycles, sizeof(z)));
+  IDN_CUDA_TRY(cudaMemcpyToSymbol(g_tc_wait_cycles, z, sizeof(z)));
+  return IDN_OK;
+}
+
 int conv_tc_configure() {
   IDN_TRY((configure_one<64>()));
   IDN_TRY((configure_one<128>()));
@@ -790,7 +862,7 @@ static int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const Conv
   const int total = p.num_m_tiles * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   const int grid = total < num_sms ? total : num_sms;
-  conv_tc_kernel<BLOCK_N><<<grid, 256, TcCfg<BLOCK_N>::SMEM_BYTES, st>>>(tmA, tmB, p);
+  conv_tc_kernel<BLOCK_N><<<grid, kThreads, TcCfg<BLOCK_N>::SMEM_BYTES, st>>>(tmA, tmB, p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
@@ -856,34 +928,48 @@ int make_tmap_2d(CUtensorMap* tm, const void* base_ptr, uint64_t inner_elems, ui
   return IDN_OK;
 }
 
-// 5-D map over the 4-channel stem image: (8 elements = 2 pixels, pixel pair, row phase, row group,
-// image); one box = 16 row groups x 11 pixel pairs = the 16 strips (176 bytes each) of one filter
-// row of one 16 x 8 output tile.  Row groups outside the image read as zeros (the vertical padding).
+// 5-D map over the 4-channel stem image with overlapping strides (see stem_kernel); weights:
+// [64][7*32] K-major, one 64-row x 32-element box per filter row; both 64B-swizzled.
 int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int ws_px, int img_h, int nimg_cap) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return IDN_ECUDA;
   const uint64_t row = (uint64_t)ws_px * 8;                // bytes per image row (4 bf16 channels)
-  cuuint64_t gdim[5] = {8, (cuuint64_t)(ws_px / 2), 2, (cuuint64_t)(img_h / 2), (cuuint64_t)nimg_cap};
+  cuuint64_t gdim[5] = {(cuuint64_t)kStemWin, 112, 2, (cuuint64_t)(img_h / 2), (cuuint64_t)nimg_cap};
   cuuint64_t gstr[4] = {16, row, 2 * row, (cuuint64_t)img_h * row};
-  cuuint32_t box[5] = {8, 11, 1, (cuuint32_t)kStemTH, 1};
+  cuuint32_t box[5] = {(cuuint32_t)kStemWin, (cuuint32_t)kStemTW, 1, (cuuint32_t)kStemTH, 1};
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base_ptr), gdim, gstr,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled(stem 5d) failed with CUresult " + std::to_string((int)r));
+    set_error("cuTensorMapEncodeTiled(stem 5d, overlapping strides) failed with CUresult " + std::to_string((int)r));
     return IDN_ECUDA;
   }
   return IDN_OK;
 }
 
-int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st) {
+int make_tmap_stem_w(CUtensorMap* tm, const void* wt, int ktot) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return IDN_ECUDA;
+  cuuint64_t gdim[2] = {(cuuint64_t)ktot, 64};
+  cuuint64_t gstr[1] = {(cuuint64_t)ktot * 2};
+  cuuint32_t box[2] = {(cuuint32_t)kStemWin, 64};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wt), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(stem weights) failed"); return IDN_ECUDA; }
+  return IDN_OK;
+}
+
+int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int num_sms,
+                   cudaStream_t st) {
   const int total = p.num_m_tiles;
   if (total <= 0) return IDN_OK;
-  if (p.mode != MODE_STEM || p.num_taps != 7 || p.stem_w == nullptr) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
-  IDN_CUDA_TRY(cudaFuncSetAttribute(stem_toeplitz_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmemBytes));
+  if (p.mode != MODE_STEM || p.num_taps != 7) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
+  IDN_CUDA_TRY(cudaFuncSetAttribute(stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmemBytes));
   const int grid = total < num_sms ? total : num_sms;
-  stem_toeplitz_kernel<<<grid, 256, kStemSmemBytes, st>>>(tmA, p);
+  stem_kernel<<<grid, kThreads, kStemSmemBytes, st>>>(tmA, tmB, p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
@@ -902,18 +988,21 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   int bn = 0;
   bool res = false;
   const int k_total = p->num_taps * p->c_blocks;
-  // Measured on B200 (profiles/): the halo kernel wins for the 64-channel layers (weights resident,
-  // 1.7x over one-box-per-tap) and loses for wider layers, where 128 x 128 SS-mode MMAs read
-  // 128 B/clk of operands from shared memory and 128 x 256 tiles of conv_tc_kernel do better.
-  // The streamed-weights instantiations stay available behind IDN_HALO_WIDE=1 for experiments.
-  bool wide = false;
-  if (const char* v = std::getenv("IDN_HALO_WIDE")) wide = v[0] == '1';
-  if (n_total == 64) { bn = 64; res = (k_total * 64 * 128) <= 80 * 1024; }
-  else if (wide && n_total % 128 == 0) bn = 128;
-  else if (wide && n_total % 96 == 0) bn = 96;
+  // Measured on B200 (profiles/): every convolution here is bound by the tensor pipe's shared-memory
+  // operand fetch (about 72 B/clk/SM) or, with one TMA box per tap, by the L2 -> SM fabric (about
+  // 42 B/clk/SM).  Staging A once per channel block removes most of the fabric traffic; the widest N
+  // tile that divides Cout minimises operand bytes per MMA.  64-channel layers keep their weights
+  // resident and share them between two 128-row sub-tiles.
+  int msub = 1;
+  if (n_total == 64) { bn = 64; msub = 2; res = (k_total * 64 * 128) <= 80 * 1024; if (!res) return false; }
+  else if (n_total % 256 == 0) bn = 256;
+  else if (n_total % 192 == 0) bn = 192;
+  else if (n_total % 128 == 0) bn = 128;
   else return false;
-  if (bn == 64 && !res) return false;
-  const int msub = 2;
+  if (const char* v = std::getenv("IDN_HALO_BN")) {            // experiments: force an N tile
+    const int f = std::atoi(v);
+    if (n_total != 64 && (f == 128 || f == 192 || f == 256) && n_total % f == 0) bn = f;
+  }
   const int total_rows = kBlockM * msub + span;
   p->msub = msub;
   p->halo_lo = lo;
@@ -949,17 +1038,19 @@ static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
   IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, MSUB, BRES>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int grid = total < num_sms ? total : num_sms;
-  conv_halo_kernel<BLOCK_N, MSUB, BRES><<<grid, 256, smem, st>>>(tmA1, tmA2, tmB, p);
+  conv_halo_kernel<BLOCK_N, MSUB, BRES><<<grid, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
 
 int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                      const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st) {
-  if (p.msub != 2) { set_error("launch_conv_halo: msub"); return IDN_EINVAL; }
-  if (block_n == 64 && b_resident) return launch_halo_one<64, 2, true>(tmA1, tmA2, tmB, p, num_sms, st);
-  if (block_n == 128 && !b_resident) return launch_halo_one<128, 2, false>(tmA1, tmA2, tmB, p, num_sms, st);
-  if (block_n == 96 && !b_resident) return launch_halo_one<96, 2, false>(tmA1, tmA2, tmB, p, num_sms, st);
+  if (block_n == 64 && b_resident && p.msub == 2) return launch_halo_one<64, 2, true>(tmA1, tmA2, tmB, p, num_sms, st);
+  if (!b_resident && p.msub == 1) {
+    if (block_n == 128) return launch_halo_one<128, 1, false>(tmA1, tmA2, tmB, p, num_sms, st);
+    if (block_n == 192) return launch_halo_one<192, 1, false>(tmA1, tmA2, tmB, p, num_sms, st);
+    if (block_n == 256) return launch_halo_one<256, 1, false>(tmA1, tmA2, tmB, p, num_sms, st);
+  }
   set_error("launch_conv_halo: unsupported configuration");
   return IDN_EINVAL;
 }

@@ -60,6 +60,7 @@ struct Step {
   long long out_plane_rows = 0;
   int out_H = 0, out_W = 0;   // logical image extent (parity: 2x plane extent)
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  unsigned long long wait_cycles[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // filled in timing mode
 };
 
 }  // namespace idn
@@ -314,7 +315,10 @@ static int add_stem(idn_engine* e, const std::string& name, const void* xs, int 
   cp.st_stride = stride; cp.st_ws = ws; cp.st_h = IDN_CROP; cp.st_ow = OW;
   cp.st_nrow = IDN_CROP / stride;
   st.block_n = 64;
-  if (!e->stem_simt) IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
+  if (!e->stem_simt) {
+    IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
+    IDN_TRY(make_tmap_stem_w(&st.tmB, cw.wt, cw.ktot));
+  }
   e->steps.push_back(st);
   return IDN_OK;
 }
@@ -592,7 +596,7 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
   else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
   if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
-  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, cp, e->num_sms, st);
+  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, s.tmB, cp, e->num_sms, st);
   if (s.use_halo) {
     const int item_rows = kBlockM * cp.msub;
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
@@ -636,7 +640,13 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
         break;
     }
     e->launches += 1;
-    if (e->timing) IDN_CUDA_TRY(cudaEventRecord(s.ev1, st));
+    if (e->timing) {
+      IDN_CUDA_TRY(cudaEventRecord(s.ev1, st));
+      if (s.kind == STEP_CONV) {            // per-role wait cycles of this kernel alone
+        IDN_CUDA_TRY(cudaStreamSynchronize(st));
+        IDN_TRY(read_tc_wait_cycles(s.wait_cycles));
+      }
+    }
   }
   return IDN_OK;
 }
@@ -901,6 +911,12 @@ int idn_debug_stop_after(idn_handle h, int step) {
 int64_t idn_kernel_launches(idn_handle h) { return h ? h->launches : -1; }
 
 int idn_set_timing(idn_handle h, int on) { if (!h) return IDN_EINVAL; h->timing = on != 0; return IDN_OK; }
+
+int idn_step_wait_cycles(idn_handle h, int step, uint64_t* out8) {
+  if (!h || !out8 || step < 0 || step >= (int)h->steps.size()) { set_error("bad step"); return IDN_EINVAL; }
+  for (int i = 0; i < 8; ++i) out8[i] = h->steps[step].wait_cycles[i];
+  return IDN_OK;
+}
 
 int idn_step_time_ms(idn_handle h, int step, float* ms) {
   if (!h || !ms || step < 0 || step >= (int)h->steps.size()) { set_error("bad step"); return IDN_EINVAL; }

@@ -139,6 +139,14 @@ class Engine:
             out.append((name, ms.value))
         return out
 
+    def step_wait_cycles(self):
+        out = []
+        for i, (name, _) in enumerate(self.steps()):
+            w = np.zeros(8, dtype=np.uint64)
+            _lib.check(self._lib.idn_step_wait_cycles(self._h, i, w.ctypes.data), "idn_step_wait_cycles")
+            out.append((name, w))
+        return out
+
     @property
     def kernel_launches(self) -> int:
         return int(self._lib.idn_kernel_launches(self._h))

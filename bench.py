@@ -204,6 +204,7 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
             continue                               # first timed pass creates the events
         for name, t in eng.step_times_ms():
             acc[name] = acc.get(name, 0.0) + t / reps
+    waits = {name: [int(x) for x in w] for name, w in eng.step_wait_cycles() if int(w.sum()) > 0}
     eng.set_timing(False)
     flops = STEP_FLOPS[model]
     tc_steps = {k: v for k, v in acc.items() if k in flops}
@@ -230,6 +231,7 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
             "ms": round(pre_ms, 4), "gbps": round(PRE_BYTES_PER_IMG * BATCH / (pre_ms * 1e-3) / 1e9, 1),
             "frac_of_measured_hbm": round(PRE_BYTES_PER_IMG * BATCH / (pre_ms * 1e-3) / 1e9 / peaks["hbm"], 4)},
         "kernel_ms": {k: round(v, 4) for k, v in acc.items()},
+        "wait_cycles": waits,
         "gpu_launches": int(launches), "clocks": clk.summary(),
     }
     if do_cpu_baseline:

@@ -115,6 +115,11 @@ int idn_debug_stop_after(idn_handle h, int step);
 int64_t idn_kernel_launches(idn_handle h);
 int idn_set_timing(idn_handle h, int on);
 int idn_step_time_ms(idn_handle h, int step, float* ms);
+/* With timing on: SM cycles the tensor-core kernel of plan step `step` spent blocked in each kind of
+ * pipeline wait during the last pass, summed over CTAs -- [0] TMA producer on a free stage, [1] MMA on
+ * the epilogue, [2] MMA on activations, [3] epilogue on the MMA, [4] weight producer on a free stage,
+ * [5] MMA on resident weights, [6] MMA on streamed weights. */
+int idn_step_wait_cycles(idn_handle h, int step, uint64_t* out8);
 
 /* Stand-alone layer entry (tests): y = act(conv(x, w) * scale + shift (+ residual)) with NCHW fp32
  * host tensors, computed through the same operand layouts and kernels as the model plans.

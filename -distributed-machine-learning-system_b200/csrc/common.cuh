@@ -72,6 +72,26 @@ constexpr int kStemWin = 32;   // elements per filter row: 8-pixel window x 4 ch
 enum { MODE_FLAT = 0, MODE_STEM = 1 };
 enum { DEST_GEOM = 0, DEST_PARITY = 1 };
 
+// Division by a run-time constant for the row decode of the epilogues: q / d == umulhi(q, mul) >> shift
+// for 0 <= q < 2^31 (d = 1: mul = 0 means "q itself").
+struct FastDiv {
+  unsigned int mul, shift, d;
+};
+inline FastDiv make_fastdiv(unsigned int d) {
+  FastDiv f; f.d = d; f.mul = 0; f.shift = 0;
+  if (d > 1) {
+    unsigned int lg = 0;
+    while ((1ull << lg) < d) ++lg;
+    const unsigned int p = 31 + lg;
+    f.mul = (unsigned int)(((1ull << p) + d - 1) / d);
+    f.shift = p - 32;
+  }
+  return f;
+}
+__device__ __forceinline__ unsigned int fastdiv(unsigned int q, const FastDiv& f) {
+  return f.mul == 0 ? q : (__umulhi(q, f.mul) >> f.shift);
+}
+
 struct ConvParams {
   // K loop
   int num_taps;
@@ -111,6 +131,8 @@ struct ConvParams {
   int a_stage_bytes;          // (r1 + r2) * 128 rounded up to 1024
   int a_stages, b_stages;     // ring depths chosen by the host from the shared-memory budget
   int msub;                   // 128-row sub-tiles per work item (1 or 2)
+  FastDiv fd_img_rows, fd_wp, fd_per_img, fd_tiles_w;   // row decode without integer division
+  int profile;                // 1: book pipeline-wait cycles per role (bench.py timing mode)
 };
 
 // launchers (conv_tc.cu / conv_simt.cu)
@@ -131,9 +153,7 @@ int conv_tc_configure();   // cudaFuncSetAttribute for every instantiation; once
 int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner_elems, uint64_t rows,
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
 int make_tmap_stem(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
-int make_tmap_stem_w(CUtensorMap* tm, const void* wt, int ktot);
-int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int num_sms,
-                   cudaStream_t st);
+int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st);
 
 // other kernels (pool_head.cu)
 struct PoolParams {

@@ -151,6 +151,16 @@ __device__ __forceinline__ bool elect_one() {
   asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
   return pred != 0;
 }
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -170,17 +180,19 @@ __device__ unsigned int g_tc_watchdog[4];
 // read_tc_wait_cycles(); used by bench.py to say which role a kernel is bound by.
 __device__ unsigned long long g_tc_wait_cycles[8];
 
-__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, int role, int where) {
-  // mbarrier.try_wait may itself block for a while before it answers, so the clock starts before
-  // the first probe; anything longer than a probe's own latency is booked as waiting.
-  const long long c0 = clock64();
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, int role, int where,
+                                          int prof) {
+  // mbarrier.try_wait may itself block for a while before it answers, so (when profiling) the clock
+  // starts before the first probe; anything longer than a probe's own latency is booked as waiting.
   struct Tally {
-    int role; long long c0;
+    int role, prof; long long c0;
     __device__ ~Tally() {
-      const long long dt = clock64() - c0;
-      if (dt > 200 && (threadIdx.x & 31) == 0) atomicAdd(&g_tc_wait_cycles[role & 7], (unsigned long long)dt);
+      if (prof) {
+        const long long dt = clock64() - c0;
+        if (dt > 200 && (threadIdx.x & 31) == 0) atomicAdd(&g_tc_wait_cycles[role & 7], (unsigned long long)dt);
+      }
     }
-  } tally{role, c0};
+  } tally{role, prof, prof ? clock64() : 0ll};
   if (ptx::mbar_try_wait(bar, parity)) return true;
   const unsigned long long t0 = ptx::globaltimer();
   unsigned int spins = 0;
@@ -242,17 +254,17 @@ __device__ __forceinline__ RowInfo decode_row(const ConvParams& p, int m_tile, i
   RowInfo r;
   int n, h, w;
   if (p.mode == MODE_FLAT) {
-    const long long q = (long long)m_tile * kBlockM + i;
-    n = (int)(q / p.img_rows);
-    const int rem = (int)(q - (long long)n * p.img_rows);
-    h = rem / p.wp;
-    w = rem - h * p.wp;
+    const unsigned int q = (unsigned int)m_tile * kBlockM + (unsigned int)i;     // < 2^31 rows
+    n = (int)fastdiv(q, p.fd_img_rows);
+    const unsigned int rem = q - (unsigned int)n * (unsigned int)p.img_rows;
+    h = (int)fastdiv(rem, p.fd_wp);
+    w = (int)rem - h * p.wp;
     r.res_row = q;
   } else {
     const int per_img = p.tiles_w * p.tiles_h;
-    n = m_tile / per_img;
+    n = (int)fastdiv((unsigned int)m_tile, p.fd_per_img);
     const int t = m_tile - n * per_img;
-    const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
+    const int th = (int)fastdiv((unsigned int)t, p.fd_tiles_w), tw = t - th * p.tiles_w;
     h = th * kStemTH + i / kStemTW;
     w = tw * kStemTW + i % kStemTW;
     r.res_row = 0;
@@ -267,44 +279,48 @@ __device__ __forceinline__ RowInfo decode_row(const ConvParams& p, int m_tile, i
   return r;
 }
 
+__device__ __forceinline__ uint32_t relu_bf16x2(uint32_t v) {
+  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&v);
+  x = __hmax2(x, __float2bfloat162_rn(0.0f));
+  return *reinterpret_cast<uint32_t*>(&x);
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-// TMEM accumulator rows -> scale/shift (+residual) (+ReLU) -> bf16 / fp32, 32 columns at a time.
+// TMEM accumulator rows -> scale/shift (+residual) (+ReLU) -> bf16 / fp32, 16 columns at a time.
 // Every lane of the warp must call it (tcgen05.ld is warp-collective); stores are predicated.
-// Eight epilogue warps share a tile: warps 4..7 and 8..11 own the same four TMEM lane quarters and
-// take alternate 32-column chunks (chunk0, chunk0 + 2, ...).  The TMEM load, the scale/shift loads
-// and the residual loads of a chunk are all issued before the first wait, so their latencies overlap.
-constexpr int kEpiWarps = 8;
+// Sixteen epilogue warps share a tile: warp w owns TMEM lane quarter w % 4 and the 16-column chunks
+// chunk0, chunk0 + 4, ... (chunk0 = (w - 4) / 4).  The epilogue of the 64-channel layers is bound by
+// instruction issue and latency, not by bandwidth: many light warps (<= 102 registers) hide it better
+// than few heavy ones.  The TMEM load, the scale/shift loads and the residual load of a chunk are all
+// issued before the first wait; a thread's 32 output bytes are one full sector (256-bit store).
+constexpr int kEpiWarps = 16;
 constexpr int kThreads = 128 + 32 * kEpiWarps;
 
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
                                               int col0, int chunk0) {
 #pragma unroll 1
-  for (int c0 = chunk0 * 32; c0 < BLOCK_N; c0 += 64) {
-    uint32_t v[32];
-    ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)c0, v);
+  for (int c0 = chunk0 * 16; c0 < BLOCK_N; c0 += 64) {
+    uint32_t v[16];
+    ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)c0, v);
     const int col = col0 + c0;
     const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
     const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
-    float4 s4[8], b4[8];
+    float4 s4[4], b4[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { s4[j] = __ldg(sc + j); b4[j] = __ldg(sh + j); }
+    for (int j = 0; j < 4; ++j) { s4[j] = __ldg(sc + j); b4[j] = __ldg(sh + j); }
     const bool has_res = p.residual != nullptr && ri.valid;
-    uint32_t rr[2][8];
-    if (has_res) {
-      const bf16* rp = p.residual + ri.res_row * p.ldc + col;
-      ptx::ld_global_256(rp, rr[0]);
-      ptx::ld_global_256(rp + 16, rr[1]);
-    }
+    uint32_t rr[8];
+    if (has_res) ptx::ld_global_256(p.residual + ri.res_row * p.ldc + col, rr);
     ptx::tmem_ld_wait();
     if (ri.valid) {
-      float y[32];
+      float y[16];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < 4; ++j) {
         y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4[j].x, b4[j].x);
         y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4[j].y, b4[j].y);
         y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4[j].z, b4[j].z);
@@ -312,36 +328,33 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo
       }
       if (has_res) {
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            y[16 * j + 2 * e + 0] += __uint_as_float(rr[j][e] << 16);
-            y[16 * j + 2 * e + 1] += __uint_as_float(rr[j][e] & 0xffff0000u);
-          }
+        for (int e = 0; e < 8; ++e) {
+          y[2 * e + 0] += __uint_as_float(rr[e] << 16);
+          y[2 * e + 1] += __uint_as_float(rr[e] & 0xffff0000u);
         }
       }
-      if (p.relu) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], 0.0f);
-      }
       if (p.out_f32) {
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) y[j] = fmaxf(y[j], 0.0f);
+        }
         float* op = reinterpret_cast<float*>(p.out) + ri.dst_row * p.ldc + col;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 2; ++j) {
           uint32_t w[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) w[e] = __float_as_uint(y[8 * j + e]);
           ptx::st_global_256(op + 8 * j, w);
         }
       } else {
-        bf16* op = reinterpret_cast<bf16*>(p.out) + ri.dst_row * p.ldc + col;
+        uint32_t w[8];
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          uint32_t w[8];
+        for (int e = 0; e < 8; ++e) w[e] = pack_bf16x2(y[2 * e], y[2 * e + 1]);
+        if (p.relu) {                // max(round(x), 0) == round(max(x, 0)): two channels per instruction
 #pragma unroll
-          for (int e = 0; e < 8; ++e) w[e] = pack_bf16x2(y[16 * j + 2 * e], y[16 * j + 2 * e + 1]);
-          ptx::st_global_256(op + 16 * j, w);
+          for (int e = 0; e < 8; ++e) w[e] = relu_bf16x2(w[e]);
         }
+        ptx::st_global_256(reinterpret_cast<bf16*>(p.out) + ri.dst_row * p.ldc + col, w);
       }
     }
   }
@@ -403,7 +416,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int n_tile = tile - m_tile * p.num_n_tiles;
         int tap = 0, cb = 0;
         for (int kb = 0; kb < k_blocks; ++kb) {
-          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb)) { alive = false; break; }
+          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
           const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
           const uint32_t b_dst = a_dst + Cfg::A_BYTES;
           ptx::mbar_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
@@ -424,11 +437,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     bool alive = true;
     for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
       // epilogue has drained this accumulator
-      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile)) break;
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
       for (int kb = 0; kb < k_blocks; ++kb) {
-        if (!mbar_wait(full_bar(s), ph, 2, kb)) { alive = false; break; }   // TMA bytes landed
+        if (!mbar_wait(full_bar(s), ph, 2, kb, p.profile)) { alive = false; break; }   // TMA bytes landed
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           const uint32_t a_addr = base + s * Cfg::STAGE_BYTES;
@@ -459,7 +472,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
       const RowInfo ri = decode_row(p, m_tile, row_in_tile);
-      if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
+      if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
       epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
@@ -497,7 +510,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 constexpr int kMaxAStages = 4;
 constexpr int kMaxBStages = 16;
 
-template <int BLOCK_N, int MSUB, bool BRES>
+template <int BLOCK_N, int MSUB, bool BRES, int TAPS>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
@@ -556,7 +569,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         const int m_item = item / p.num_n_tiles;
         const int row0 = m_item * (kBlockM * MSUB) + p.halo_lo;
         for (int cb = 0; cb < p.c_blocks; ++cb) {
-          if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb)) { alive = false; break; }
+          if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb, p.profile)) { alive = false; break; }
           const uint32_t dst = a_base + (uint32_t)(sa * p.a_stage_bytes);
           ptx::mbar_expect_tx(a_full(sa), a_bytes);
           ptx::tma_load_2d(dst, &tmA1, a_full(sa), cb * kBlockK, row0);
@@ -583,7 +596,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           const int n_tile = item % p.num_n_tiles;
           for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
             for (int tap = 0; tap < p.num_taps; ++tap) {
-              if (!mbar_wait(b_empty(sb), phb ^ 1u, 4, tap)) { alive = false; break; }
+              if (!mbar_wait(b_empty(sb), phb ^ 1u, 4, tap, p.profile)) { alive = false; break; }
               ptx::mbar_expect_tx(b_full(sb), B_BYTES);
               ptx::tma_load_2d(b_base + (uint32_t)(sb * B_BYTES), &tmB, b_full(sb),
                                (tap * p.c_blocks + cb) * kBlockK, n_tile * BLOCK_N);
@@ -600,39 +613,56 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     int sa = 0, sb = 0, as = 0;
     uint32_t pha = 0, phb = 0, aph = 0;
     bool alive = true;
-    if (BRES) alive = mbar_wait(bres_bar, 0u, 5, 0);
+    if (BRES) alive = mbar_wait(bres_bar, 0u, 5, 0, p.profile);
     for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
-      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, item)) break;
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, item, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * ACC_COLS);
       for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
-        if (!mbar_wait(a_full(sa), pha, 2, cb)) { alive = false; break; }
+        if (!mbar_wait(a_full(sa), pha, 2, cb, p.profile)) { alive = false; break; }
         ptx::tc_fence_after();
         const uint32_t a_tile = a_base + (uint32_t)(sa * p.a_stage_bytes);
-        for (int tap = 0; tap < p.num_taps; ++tap) {
-          uint32_t b_tile;
-          if (BRES) {
-            b_tile = b_base + (uint32_t)((tap * p.c_blocks + cb) * B_BYTES);
-          } else {
-            if (!mbar_wait(b_full(sb), phb, 6, tap)) { alive = false; break; }
-            ptx::tc_fence_after();
-            b_tile = b_base + (uint32_t)(sb * B_BYTES);
-          }
+        if (BRES) {
+          // resident weights: no waits inside the tap loop, so one elected lane issues every MMA of
+          // the channel block in a single straight-line burst (TAPS > 0: fully unrolled, descriptor
+          // arithmetic hoisted ahead of the back-pressured MMA issue)
           if (ptx::elect_one()) {
-            const uint64_t db = make_sw128_desc(b_tile);
-            const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
 #pragma unroll
-            for (int sub = 0; sub < MSUB; ++sub) {
-              const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+            for (int tap = 0; tap < (TAPS > 0 ? TAPS : p.num_taps); ++tap) {
+              const uint64_t db = make_sw128_desc(b_base + (uint32_t)((tap * p.c_blocks + cb) * B_BYTES));
+              const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
 #pragma unroll
-              for (int k = 0; k < kBlockK / 16; ++k)
-                ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
-                               db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+              for (int sub = 0; sub < MSUB; ++sub) {
+                const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k)
+                  ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
+                                 db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+              }
             }
-            if (!BRES) ptx::umma_commit(b_empty(sb));
           }
           __syncwarp();
-          if (!BRES) { if (++sb == p.b_stages) { sb = 0; phb ^= 1u; } }
+        } else {
+          for (int tap = 0; tap < p.num_taps; ++tap) {
+            if (!mbar_wait(b_full(sb), phb, 6, tap, p.profile)) { alive = false; break; }
+            ptx::tc_fence_after();
+            const uint32_t b_tile = b_base + (uint32_t)(sb * B_BYTES);
+            if (ptx::elect_one()) {
+              const uint64_t db = make_sw128_desc(b_tile);
+              const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
+#pragma unroll
+              for (int sub = 0; sub < MSUB; ++sub) {
+                const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k)
+                  ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
+                                 db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+              }
+              ptx::umma_commit(b_empty(sb));
+            }
+            __syncwarp();
+            if (++sb == p.b_stages) { sb = 0; phb ^= 1u; }
+          }
         }
         if (alive && ptx::elect_one()) {
           ptx::umma_commit(a_empty(sa));
@@ -652,7 +682,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
       const int m_item = item / p.num_n_tiles;
       const int n_tile = item - m_item * p.num_n_tiles;
-      if (!mbar_wait(tfull_bar(as), aph, 3, item)) break;
+      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
       ptx::tc_fence_after();
 #pragma unroll 1
       for (int sub = 0; sub < MSUB; ++sub) {
@@ -681,60 +711,65 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 //
 // The preprocess kernel writes the image as 4-channel NHWC bf16 with 3 zero pixels of left padding,
 // so output column ow reads stored pixels 2*ow .. 2*ow+7 of a row (7 taps + one zero-weight pixel):
-// 32 contiguous elements (64 bytes) that start 16 bytes after the previous column's.  A 5-D tensor
-// map with OVERLAPPING strides lets TMA do the im2col: dim0 = the 64-byte window, dim1 = output
-// column (stride 16 B), dim2 = row phase, dim3 = row group (out of range = zero padding), dim4 =
-// image.  One box = 8 columns x 16 rows of output pixels = 128 rows of 64 bytes, 64B-swizzled; one
-// k-block (K = 32, two MMAs) per filter row.  The 28 KB of weights stay resident in shared memory.
-// (Tried first: 128-byte windows -- twice the bytes and MMAs; and a no-swizzle "Toeplitz" descriptor
-// that reads the raw image strips with overlapping core matrices, tools/exp_toeplitz.cu -- correct,
-// 6x less operand traffic, but no-swizzle operands are fetched at a fraction of the swizzled rate:
-// 280 cycles per 128x64x16 MMA instead of ~83.)
+// 32 contiguous elements that START 16 BYTES AFTER the previous column's.  A no-swizzle K-major
+// UMMA descriptor with leading-dimension offset 16 B describes exactly that overlapping matrix,
+//     A[m = 8g + i][k] = strip_g[8 i + k],   address = start + g * SBO + i * 16 + (k / 8) * LBO,
+// so the tensor core performs the im2col itself from the RAW image strips (verified on hardware with
+// tools/exp_toeplitz.cu; tools/exp_mma_rate.cu shows such operands run at the same MMA rate as
+// swizzled ones).  Per filter row a 16 x 8 output tile needs 16 strips of 11 pixel pairs (176 B each,
+// SBO = 176) = 2.8 KB, fetched as ONE 4-D TMA box of 16 rows -- an im2col'ed box would be 8-16 KB made
+// of 128 short rows, and measured TMA request rate (not bandwidth) then bounds the kernel.  All seven
+// filter rows of a tile form one pipeline stage, so the MMA warp pays its wait/commit latency once per
+// 14 MMAs.  The 28 KB of weights stay resident in shared memory in the canonical no-swizzle order.
 // =============================================================================================
-constexpr int kStemABytes = kBlockM * kStemWin * 2;              // 8 KiB per k-block
-constexpr int kStemAStages = 8;
-constexpr int kStemWTile = 64 * kStemWin * 2;                    // 4 KiB of weights per filter row
-constexpr int kStemSmemBytes = kStemAStages * kStemABytes + 7 * kStemWTile + 512 + 1024;
+constexpr int kStemStripBytes = 176;
+constexpr int kStemABytes = kStemTH * kStemStripBytes;          // 2816 bytes per TMA box
+constexpr int kStemABoxPitch = 3072;
+constexpr int kStemStageBytes = 7 * kStemABoxPitch;
+constexpr int kStemAStages = 6;
+constexpr int kStemWBytes = 7 * 4096;                           // [r][k chunk][n][8] bf16
+constexpr int kStemSmemBytes = kStemAStages * kStemStageBytes + kStemWBytes + 512 + 1024;
 
-// K-major, 64B-swizzled tile: rows of 64 bytes, 8-row groups 512 bytes apart, layout type 4.
-__device__ __forceinline__ uint64_t make_sw64_desc(uint32_t smem_addr) {
+__device__ __forceinline__ uint64_t make_nosw_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
-  d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(512 >> 4) << 32;
+  d |= (uint64_t)(lbo_bytes >> 4) << 16;
+  d |= (uint64_t)(sbo_bytes >> 4) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)4 << 61;
-  return d;
+  return d;                                                     // layout type 0 = no swizzle
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __grid_constant__ ConvParams p) {
+stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw_u32 + 1023u) & ~1023u;
-  const uint32_t w_base = base + kStemAStages * kStemABytes;
-  const uint32_t bar_base = w_base + 7 * kStemWTile;
+  const uint32_t w_base = base + kStemAStages * kStemStageBytes;
+  const uint32_t bar_base = w_base + kStemWBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStemAStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStemAStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStemAStages + 2 + a); };
-  const uint32_t w_bar = bar_base + 8u * (2 * kStemAStages + 4);
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kStemAStages + 5);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStemAStages + 4);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.num_m_tiles;
   const int per_img = p.tiles_w * p.tiles_h;
 
-  if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmA); ptx::prefetch_tmap(&tmB); }
+  if (warp == 0 && lane == 0) ptx::prefetch_tmap(&tmA);
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStemAStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
-    ptx::mbar_init(w_bar, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<128>(tmem_slot);
+  {   // resident weights: plain copy (already in shared-memory order), then hand over to the async proxy
+    const uint4* src = reinterpret_cast<const uint4*>(p.stem_w);
+    uint4* dst = reinterpret_cast<uint4*>(smem_raw + (w_base - raw_u32));
+    for (int i = threadIdx.x; i < kStemWBytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -744,52 +779,45 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      bool alive = true;
-      for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n = tile / per_img;
         const int t = tile - n * per_img;
         const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
-        for (int r = 0; r < 7; ++r) {
-          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, r)) { alive = false; break; }
-          ptx::mbar_expect_tx(full_bar(s), kStemABytes);
-          ptx::tma_load_5d(base + s * kStemABytes, &tmA, full_bar(s), 0, tw * kStemTW, p.tap_par[r],
-                           th * kStemTH + p.tap_off[r], n);
-          if (++s == kStemAStages) { s = 0; ph ^= 1u; }
-        }
+        if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, tile, p.profile)) break;
+        ptx::mbar_expect_tx(full_bar(s), 7 * kStemABytes);
+#pragma unroll
+        for (int r = 0; r < 7; ++r)
+          ptx::tma_load_4d(base + s * kStemStageBytes + r * kStemABoxPitch, &tmA, full_bar(s),
+                           tw * kStemTW * 8, p.tap_par[r], th * kStemTH + p.tap_off[r], n);
+        if (++s == kStemAStages) { s = 0; ph ^= 1u; }
       }
-    }
-    __syncwarp();
-  } else if (warp == 3) {
-    if (lane == 0) {                                   // resident weights: 7 boxes of 64 x 32
-      ptx::mbar_expect_tx(w_bar, 7 * kStemWTile);
-      for (int r = 0; r < 7; ++r)
-        ptx::tma_load_2d(w_base + r * kStemWTile, &tmB, w_bar, r * kStemWin, 0);
     }
     __syncwarp();
   } else if (warp == 1) {
     constexpr uint32_t idesc = make_idesc(kBlockM, 64);
     int s = 0, as = 0;
     uint32_t ph = 0, aph = 0;
-    bool alive = mbar_wait(w_bar, 0u, 5, 0);
-    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
-      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile)) break;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * 64);
-      for (int r = 0; r < 7; ++r) {
-        if (!mbar_wait(full_bar(s), ph, 2, r)) { alive = false; break; }
-        ptx::tc_fence_after();
-        if (ptx::elect_one()) {
-          const uint64_t da = make_sw64_desc(base + s * kStemABytes);
-          const uint64_t db = make_sw64_desc(w_base + r * kStemWTile);
+      if (!mbar_wait(full_bar(s), ph, 2, tile, p.profile)) break;
+      ptx::tc_fence_after();
+      if (ptx::elect_one()) {
+        const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, kStemStripBytes);
+        const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
 #pragma unroll
-          for (int k = 0; k < 2; ++k)
-            ptx::umma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (r | k) != 0 ? 1u : 0u);
-          ptx::umma_commit(empty_bar(s));
-          if (r == 6) ptx::umma_commit(tfull_bar(as));
+        for (int r = 0; r < 7; ++r) {
+#pragma unroll
+          for (int k = 0; k < 2; ++k)     // K = 32 per filter row: A +32 bytes, B +2 core-matrix columns
+            ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * kStemABoxPitch + 32 * k) >> 4),
+                           db0 + (uint64_t)((r * 4096 + 2048 * k) >> 4), idesc, (r | k) != 0 ? 1u : 0u);
         }
-        __syncwarp();
-        if (++s == kStemAStages) { s = 0; ph ^= 1u; }
+        ptx::umma_commit(empty_bar(s));
+        ptx::umma_commit(tfull_bar(as));
       }
+      __syncwarp();
+      if (++s == kStemAStages) { s = 0; ph ^= 1u; }
       if (++as == 2) { as = 0; aph ^= 1u; }
     }
   } else if (warp >= 4) {
@@ -799,7 +827,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const RowInfo ri = decode_row(p, tile, ew * 32 + lane);
-      if (!mbar_wait(tfull_bar(as), aph, 3, tile)) break;
+      if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64);
       epilogue_tile<64>(p, ri, taddr, 0, chunk0);
@@ -928,48 +956,35 @@ int make_tmap_2d(CUtensorMap* tm, const void* base_ptr, uint64_t inner_elems, ui
   return IDN_OK;
 }
 
-// 5-D map over the 4-channel stem image with overlapping strides (see stem_kernel); weights:
-// [64][7*32] K-major, one 64-row x 32-element box per filter row; both 64B-swizzled.
+// 4-D map over the 4-channel stem image: (element within an image row, row phase, row group, image);
+// one box = 16 row groups x 88 elements (11 pixel pairs = 176 contiguous bytes) = the 16 strips of one
+// filter row of one 16 x 8 output tile.  Row groups outside the image read as zeros (the vertical
+// padding).
 int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int ws_px, int img_h, int nimg_cap) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return IDN_ECUDA;
   const uint64_t row = (uint64_t)ws_px * 8;                // bytes per image row (4 bf16 channels)
-  cuuint64_t gdim[5] = {(cuuint64_t)kStemWin, 112, 2, (cuuint64_t)(img_h / 2), (cuuint64_t)nimg_cap};
-  cuuint64_t gstr[4] = {16, row, 2 * row, (cuuint64_t)img_h * row};
-  cuuint32_t box[5] = {(cuuint32_t)kStemWin, (cuuint32_t)kStemTW, 1, (cuuint32_t)kStemTH, 1};
-  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base_ptr), gdim, gstr,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+  cuuint64_t gdim[4] = {(cuuint64_t)ws_px * 4, 2, (cuuint64_t)(img_h / 2), (cuuint64_t)nimg_cap};
+  cuuint64_t gstr[3] = {row, 2 * row, (cuuint64_t)img_h * row};
+  cuuint32_t box[4] = {88, 1, (cuuint32_t)kStemTH, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base_ptr), gdim, gstr,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    set_error("cuTensorMapEncodeTiled(stem 5d, overlapping strides) failed with CUresult " + std::to_string((int)r));
+    set_error("cuTensorMapEncodeTiled(stem 4d) failed with CUresult " + std::to_string((int)r));
     return IDN_ECUDA;
   }
   return IDN_OK;
 }
 
-int make_tmap_stem_w(CUtensorMap* tm, const void* wt, int ktot) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return IDN_ECUDA;
-  cuuint64_t gdim[2] = {(cuuint64_t)ktot, 64};
-  cuuint64_t gstr[1] = {(cuuint64_t)ktot * 2};
-  cuuint32_t box[2] = {(cuuint32_t)kStemWin, 64};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wt), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(stem weights) failed"); return IDN_ECUDA; }
-  return IDN_OK;
-}
-
-int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int num_sms,
-                   cudaStream_t st) {
+int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st) {
   const int total = p.num_m_tiles;
   if (total <= 0) return IDN_OK;
-  if (p.mode != MODE_STEM || p.num_taps != 7) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
+  if (p.mode != MODE_STEM || p.num_taps != 7 || p.stem_w == nullptr) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
   IDN_CUDA_TRY(cudaFuncSetAttribute(stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmemBytes));
   const int grid = total < num_sms ? total : num_sms;
-  stem_kernel<<<grid, kThreads, kStemSmemBytes, st>>>(tmA, tmB, p);
+  stem_kernel<<<grid, kThreads, kStemSmemBytes, st>>>(tmA, p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
@@ -1028,28 +1043,31 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   return true;
 }
 
-template <int BLOCK_N, int MSUB, bool BRES>
+template <int BLOCK_N, int MSUB, bool BRES, int TAPS>
 static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                            const ConvParams& p, int num_sms, cudaStream_t st) {
   const int total = p.num_m_tiles * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   const int k_total = p.num_taps * p.c_blocks;
   const int smem = p.a_stages * p.a_stage_bytes + (BRES ? k_total : p.b_stages) * BLOCK_N * 128 + 1024 + 1024;
-  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, MSUB, BRES>,
+  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int grid = total < num_sms ? total : num_sms;
-  conv_halo_kernel<BLOCK_N, MSUB, BRES><<<grid, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
+  conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS><<<grid, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
 
 int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                      const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st) {
-  if (block_n == 64 && b_resident && p.msub == 2) return launch_halo_one<64, 2, true>(tmA1, tmA2, tmB, p, num_sms, st);
+  if (block_n == 64 && b_resident && p.msub == 2) {
+    if (p.num_taps == 9) return launch_halo_one<64, 2, true, 9>(tmA1, tmA2, tmB, p, num_sms, st);
+    return launch_halo_one<64, 2, true, 0>(tmA1, tmA2, tmB, p, num_sms, st);
+  }
   if (!b_resident && p.msub == 1) {
-    if (block_n == 128) return launch_halo_one<128, 1, false>(tmA1, tmA2, tmB, p, num_sms, st);
-    if (block_n == 192) return launch_halo_one<192, 1, false>(tmA1, tmA2, tmB, p, num_sms, st);
-    if (block_n == 256) return launch_halo_one<256, 1, false>(tmA1, tmA2, tmB, p, num_sms, st);
+    if (block_n == 128) return launch_halo_one<128, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
+    if (block_n == 192) return launch_halo_one<192, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
+    if (block_n == 256) return launch_halo_one<256, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   }
   set_error("launch_conv_halo: unsupported configuration");
   return IDN_EINVAL;

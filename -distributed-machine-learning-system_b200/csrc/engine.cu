@@ -96,6 +96,7 @@ struct idn_engine {
   bool stem_simt = false;   // bring-up switch IDN_STEM_SIMT=1: run the two C=3 stem layers on the
                             // CUDA-core kernel (explicit, never automatic)
   bool timing = false;
+  bool wait_profile = false;  // timing mode 2: also book per-role pipeline waits (slower kernels)
   int stop_after = -1;      // diagnostic: run the plan up to and including this step
   int last_n = 0;
 };
@@ -315,10 +316,7 @@ static int add_stem(idn_engine* e, const std::string& name, const void* xs, int 
   cp.st_stride = stride; cp.st_ws = ws; cp.st_h = IDN_CROP; cp.st_ow = OW;
   cp.st_nrow = IDN_CROP / stride;
   st.block_n = 64;
-  if (!e->stem_simt) {
-    IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
-    IDN_TRY(make_tmap_stem_w(&st.tmB, cw.wt, cw.ktot));
-  }
+  if (!e->stem_simt) IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
   e->steps.push_back(st);
   return IDN_OK;
 }
@@ -592,11 +590,16 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
 static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_t st) {
   ConvParams& cp = s.cp;
   cp.nimg = n;
+  cp.profile = (e->timing && e->wait_profile) ? 1 : 0;
+  cp.fd_img_rows = make_fastdiv((unsigned)std::max(cp.img_rows, 1));
+  cp.fd_wp = make_fastdiv((unsigned)std::max(cp.wp, 1));
+  cp.fd_per_img = make_fastdiv((unsigned)std::max(cp.tiles_w * cp.tiles_h, 1));
+  cp.fd_tiles_w = make_fastdiv((unsigned)std::max(cp.tiles_w, 1));
   const long long rows = (long long)n * cp.img_rows;
   if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
   else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
   if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
-  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, s.tmB, cp, e->num_sms, st);
+  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, cp, e->num_sms, st);
   if (s.use_halo) {
     const int item_rows = kBlockM * cp.msub;
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
@@ -642,7 +645,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     e->launches += 1;
     if (e->timing) {
       IDN_CUDA_TRY(cudaEventRecord(s.ev1, st));
-      if (s.kind == STEP_CONV) {            // per-role wait cycles of this kernel alone
+      if (s.kind == STEP_CONV && e->wait_profile) {   // per-role wait cycles of this kernel alone
         IDN_CUDA_TRY(cudaStreamSynchronize(st));
         IDN_TRY(read_tc_wait_cycles(s.wait_cycles));
       }
@@ -910,7 +913,12 @@ int idn_debug_stop_after(idn_handle h, int step) {
 
 int64_t idn_kernel_launches(idn_handle h) { return h ? h->launches : -1; }
 
-int idn_set_timing(idn_handle h, int on) { if (!h) return IDN_EINVAL; h->timing = on != 0; return IDN_OK; }
+int idn_set_timing(idn_handle h, int on) {
+  if (!h) return IDN_EINVAL;
+  h->timing = on != 0;
+  h->wait_profile = on == 2;
+  return IDN_OK;
+}
 
 int idn_step_wait_cycles(idn_handle h, int step, uint64_t* out8) {
   if (!h || !out8 || step < 0 || step >= (int)h->steps.size()) { set_error("bad step"); return IDN_EINVAL; }

@@ -77,7 +77,8 @@ class Engine:
     def set_stream(self, cuda_stream_ptr: int):
         _lib.check(self._lib.idn_set_stream(self._h, C.c_void_p(cuda_stream_ptr)), "idn_set_stream")
 
-    def set_timing(self, on: bool):
+    def set_timing(self, on):
+        """0/False off, 1/True CUDA events per plan step, 2 events + per-role pipeline-wait cycles."""
         _lib.check(self._lib.idn_set_timing(self._h, int(on)), "idn_set_timing")
 
     # -- inference -----------------------------------------------------------------------------

@@ -204,6 +204,9 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
             continue                               # first timed pass creates the events
         for name, t in eng.step_times_ms():
             acc[name] = acc.get(name, 0.0) + t / reps
+    eng.set_timing(2)                              # one more pass with the pipeline-wait counters on
+    step_device(0)
+    eng.sync()
     waits = {name: [int(x) for x in w] for name, w in eng.step_wait_cycles() if int(w.sum()) > 0}
     eng.set_timing(False)
     flops = STEP_FLOPS[model]

@@ -111,7 +111,8 @@ int idn_debug_stop_after(idn_handle h, int step);
 
 /* Counters for bench.py: kernels launched by this handle since creation, and the duration in
  * milliseconds of plan step `step` in the last pass when timing was switched on
- * (idn_set_timing(h, 1) records CUDA events around every step). */
+ * (idn_set_timing(h, 1) records CUDA events around every step; 2 additionally books the pipeline
+ * waits idn_step_wait_cycles reports, which slows the kernels a little). */
 int64_t idn_kernel_launches(idn_handle h);
 int idn_set_timing(idn_handle h, int on);
 int idn_step_time_ms(idn_handle h, int step, float* ms);

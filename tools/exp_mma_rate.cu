@@ -51,10 +51,14 @@ rate_kernel(long long* out_cycles, int layout, int n, int chain, int k_adv) {
     }
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (((uint32_t)n >> 3) << 17) | ((128u >> 4) << 24);
     const long long t0 = clock64();
-    for (int i = 0; i < chain; ++i) {
-      const uint64_t adv = (uint64_t)(2 * (i % k_adv));            // walk K inside the swizzle row
-      asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
-                   ::"r"(tmem), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(i) : "memory");
+    // fully unrolled groups of 8 MMAs with constant descriptor increments (what a tuned issue loop does)
+    for (int i = 0; i < chain; i += 8) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint64_t adv = (uint64_t)(2 * (j % 4 < k_adv ? j % 4 : 0));
+        asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+                     ::"r"(tmem), "l"(da + adv), "l"(db + adv), "r"(idesc), "r"(1) : "memory");
+      }
     }
     const long long t1 = clock64();
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");

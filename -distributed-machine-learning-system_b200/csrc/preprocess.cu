@@ -155,7 +155,11 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
   const int* __restrict__ ht = tables + m.htab;
   const int* __restrict__ vt = tables + m.vtab;
   const uint8_t* __restrict__ src = imgs + m.offset;
-  const int ylo = kPreRows * (int)blockIdx.x, yhi = ylo + kPreRows;      // 224 = 28 * 8
+  // crop rows of this CTA: 8 rows; the S2D4 tiles are shifted by the stem's padding (2) so that a CTA
+  // owns two complete rows of 4x4 blocks (29 CTAs per image)
+  const int ybase = OUT_MODE == PRE_OUT_S2D4 ? kPreRows * (int)blockIdx.x - 2 : kPreRows * (int)blockIdx.x;
+  const int ylo = ybase < 0 ? 0 : ybase;
+  const int yhi = ybase + kPreRows > IDN_CROP ? IDN_CROP : ybase + kPreRows;
   const int hks = ht[0], vks = vt[0];
   const int ys0 = vt[1 + ylo];
   const int nrows = vt[1 + yhi - 1] + vt[1 + IDN_CROP + yhi - 1] - ys0;
@@ -174,13 +178,37 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       o[0] = (uint16_t)r; o[IDN_CROP * IDN_CROP] = (uint16_t)g; o[2 * IDN_CROP * IDN_CROP] = (uint16_t)b;
     } else if (OUT_MODE == PRE_OUT_STEM) {
       reinterpret_cast<uint2*>(out)[((long long)n * IDN_CROP + y) * ws + left_pad + x] = make_uint2(r | (g << 16), b);
-    } else {   // PRE_OUT_S2D4: s2d pixel ((y+2)/4, (x+2)/4), channel (dy*4+dx)*3 + c; 57x57x64 per image.
-               // Channels 48..63 and the out-of-image border positions are never written: the buffer is
-               // zeroed once when it is allocated.
-      const int yy = y + 2, xx = x + 2;
-      uint16_t* o = reinterpret_cast<uint16_t*>(out) +
-                    (((long long)n * 57 + (yy >> 2)) * 57 + (xx >> 2)) * 64 + ((yy & 3) * 4 + (xx & 3)) * 3;
-      o[0] = (uint16_t)r; o[1] = (uint16_t)g; o[2] = (uint16_t)b;
+    }
+  };
+  // S2D4 writer: s2d pixel (by, bx) = the 4x4 block of crop pixels starting at (4by-2, 4bx-2), channel
+  // (dy*4+dx)*3 + c, 57 x 57 pixels of 64 channels per image.  One item = one block row (by, bx, dy):
+  // 4 pixels x 3 channels = 24 contiguous bytes, so the four dy of a block fill 96 contiguous bytes.
+  // Channels 48..63 are never written (the buffer is zeroed when it is allocated); positions outside
+  // the crop are written as zeros.
+  auto write_s2d4 = [&](auto pixel) {
+    const int by0 = 2 * (int)blockIdx.x;
+    for (int it = tid; it < 2 * 57 * 4; it += blockDim.x) {
+      const int dy = it & 3, bx = (it >> 2) % 57, byl = it / (4 * 57);
+      const int by = by0 + byl, y = ybase + 4 * byl + dy;
+      if (by >= 57) continue;
+      uint32_t w[6] = {0u, 0u, 0u, 0u, 0u, 0u};
+      if (y >= 0 && y < IDN_CROP) {
+#pragma unroll
+        for (int dx = 0; dx < 4; ++dx) {
+          const int x = 4 * bx - 2 + dx;
+          if (x < 0 || x >= IDN_CROP) continue;
+          const uint32_t px = pixel(y, x);
+          const uint32_t c[3] = {s_lut[px & 255u], s_lut[256 + ((px >> 8) & 255u)], s_lut[512 + (px >> 16)]};
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) {
+            const int e = dx * 3 + ch;
+            w[e >> 1] |= c[ch] << (16 * (e & 1));
+          }
+        }
+      }
+      uint2* o = reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(out) +
+                                         (((long long)n * 57 + by) * 57 + bx) * 64 + dy * 12);
+      o[0] = make_uint2(w[0], w[1]); o[1] = make_uint2(w[2], w[3]); o[2] = make_uint2(w[4], w[5]);
     }
   };
 
@@ -240,35 +268,46 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       }
     }
     __syncthreads();
-    if (tid < IDN_CROP) {
-      const int x = tid;
-      // ---- 3. vertical pass over the uint8 intermediate + normalise + store
+    // ---- 3. vertical pass over the uint8 intermediate (Pillow's order) -> packed uint8 RGB
+    auto vertical = [&](int y, int x) -> uint32_t {
+      const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
+      const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
+      const int k0 = __ldg(vk), k1 = yn > 1 ? __ldg(vk + 1) : 0, k2 = yn > 2 ? __ldg(vk + 2) : 0,
+                k3 = yn > 3 ? __ldg(vk + 3) : 0;
+      const int last = nrows - 1;
+      const uint32_t q0 = s_h[y0 * IDN_CROP + x];
+      const uint32_t q1 = s_h[min(y0 + 1, last) * IDN_CROP + x];
+      const uint32_t q2 = s_h[min(y0 + 2, last) * IDN_CROP + x];
+      const uint32_t q3 = s_h[min(y0 + 3, last) * IDN_CROP + x];
+      int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+      a0 += bsel(q0, 0) * k0; a1 += bsel(q0, 1) * k0; a2 += bsel(q0, 2) * k0;
+      a0 += bsel(q1, 0) * k1; a1 += bsel(q1, 1) * k1; a2 += bsel(q1, 2) * k1;
+      a0 += bsel(q2, 0) * k2; a1 += bsel(q2, 1) * k2; a2 += bsel(q2, 2) * k2;
+      a0 += bsel(q3, 0) * k3; a1 += bsel(q3, 1) * k3; a2 += bsel(q3, 2) * k3;
+      return (uint32_t)(a0 >> 22) | ((uint32_t)(a1 >> 22) << 8) | ((uint32_t)(a2 >> 22) << 16);
+    };
+    if (OUT_MODE == PRE_OUT_S2D4) {
+      write_s2d4(vertical);
+    } else if (tid < IDN_CROP) {
 #pragma unroll 2
       for (int y = ylo; y < yhi; ++y) {
-        const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
-        const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
-        const int k0 = __ldg(vk), k1 = yn > 1 ? __ldg(vk + 1) : 0, k2 = yn > 2 ? __ldg(vk + 2) : 0,
-                  k3 = yn > 3 ? __ldg(vk + 3) : 0;
-        const int last = nrows - 1;
-        const uint32_t q0 = s_h[y0 * IDN_CROP + x];
-        const uint32_t q1 = s_h[min(y0 + 1, last) * IDN_CROP + x];
-        const uint32_t q2 = s_h[min(y0 + 2, last) * IDN_CROP + x];
-        const uint32_t q3 = s_h[min(y0 + 3, last) * IDN_CROP + x];
-        int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-        a0 += bsel(q0, 0) * k0; a1 += bsel(q0, 1) * k0; a2 += bsel(q0, 2) * k0;
-        a0 += bsel(q1, 0) * k1; a1 += bsel(q1, 1) * k1; a2 += bsel(q1, 2) * k1;
-        a0 += bsel(q2, 0) * k2; a1 += bsel(q2, 1) * k2; a2 += bsel(q2, 2) * k2;
-        a0 += bsel(q3, 0) * k3; a1 += bsel(q3, 1) * k3; a2 += bsel(q3, 2) * k3;
-        emit(y, x, (uint32_t)(a0 >> 22), (uint32_t)(a1 >> 22), (uint32_t)(a2 >> 22));
+        const uint32_t px = vertical(y, tid);
+        emit(y, tid, px & 255u, (px >> 8) & 255u, px >> 16);
       }
     }
   } else {
     __syncthreads();                              // s_lut
-    if (tid < IDN_CROP) {
+    auto direct = [&](int y, int x) -> uint32_t {
+      int o[3];
+      pre_direct_pixel(src, m.W, ht, vt, x, y, o);
+      return (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16);
+    };
+    if (OUT_MODE == PRE_OUT_S2D4) {
+      write_s2d4(direct);
+    } else if (tid < IDN_CROP) {
       for (int y = ylo; y < yhi; ++y) {
-        int o[3];
-        pre_direct_pixel(src, m.W, ht, vt, tid, y, o);
-        emit(y, tid, (uint32_t)o[0], (uint32_t)o[1], (uint32_t)o[2]);
+        const uint32_t px = direct(y, tid);
+        emit(y, tid, px & 255u, (px >> 8) & 255u, px >> 16);
       }
     }
   }
@@ -305,7 +344,7 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
         d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap);
   } else {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    preprocess_kernel<PRE_OUT_S2D4><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
+    preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, smem, st>>>(
         d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap);
   }
   IDN_CUDA_TRY(cudaGetLastError());

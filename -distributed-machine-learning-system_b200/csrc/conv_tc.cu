@@ -1018,6 +1018,9 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
     const int f = std::atoi(v);
     if (n_total != 64 && (f == 128 || f == 192 || f == 256) && n_total % f == 0) bn = f;
   }
+  if (const char* v = std::getenv("IDN_HALO_MSUB")) {          // experiments: two sub-tiles share B
+    if (v[0] == '2' && bn == 128) msub = 2;
+  }
   const int total_rows = kBlockM * msub + span;
   p->msub = msub;
   p->halo_lo = lo;
@@ -1064,6 +1067,8 @@ int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUt
     if (p.num_taps == 9) return launch_halo_one<64, 2, true, 9>(tmA1, tmA2, tmB, p, num_sms, st);
     return launch_halo_one<64, 2, true, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   }
+  if (!b_resident && p.msub == 2 && block_n == 128)
+    return launch_halo_one<128, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   if (!b_resident && p.msub == 1) {
     if (block_n == 128) return launch_halo_one<128, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
     if (block_n == 192) return launch_halo_one<192, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);

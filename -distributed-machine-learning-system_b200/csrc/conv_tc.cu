@@ -300,19 +300,31 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 constexpr int kEpiWarps = 16;
 constexpr int kThreads = 128 + 32 * kEpiWarps;
 
+// Per-channel scale/shift of one 16-column chunk.  With a 64-wide N tile and one N tile per layer a warp
+// always handles the same chunk, so these 32 values are loaded once per kernel (their L2 latency used to
+// be exposed on every tile).
+struct ChunkAffine {
+  float4 s4[4], b4[4];
+  __device__ __forceinline__ void load(const ConvParams& p, int col) {
+    const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
+    const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { s4[j] = __ldg(sc + j); b4[j] = __ldg(sh + j); }
+  }
+};
+
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
-                                              int col0, int chunk0) {
+                                              int col0, int chunk0, const ChunkAffine* hoisted = nullptr) {
 #pragma unroll 1
   for (int c0 = chunk0 * 16; c0 < BLOCK_N; c0 += 64) {
     uint32_t v[16];
     ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)c0, v);
     const int col = col0 + c0;
-    const float4* sc = reinterpret_cast<const float4*>(p.scale + col);
-    const float4* sh = reinterpret_cast<const float4*>(p.shift + col);
-    float4 s4[4], b4[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { s4[j] = __ldg(sc + j); b4[j] = __ldg(sh + j); }
+    ChunkAffine loc;
+    if (BLOCK_N > 64 || hoisted == nullptr) loc.load(p, col);
+    const float4* s4 = (BLOCK_N > 64 || hoisted == nullptr) ? loc.s4 : hoisted->s4;
+    const float4* b4 = (BLOCK_N > 64 || hoisted == nullptr) ? loc.b4 : hoisted->b4;
     const bool has_res = p.residual != nullptr && ri.valid;
     uint32_t rr[8];
     if (has_res) ptx::ld_global_256(p.residual + ri.res_row * p.ldc + col, rr);
@@ -677,6 +689,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     // ================================ epilogue ====================================
     const int ew = (warp - 4) & 3;
     const int chunk0 = (warp - 4) >> 2;
+    ChunkAffine aff;
+    if (BLOCK_N == 64) aff.load(p, chunk0 * 16);       // n_total == 64: the same 16 channels every tile
     int as = 0;
     uint32_t aph = 0;
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
@@ -689,7 +703,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         const RowInfo ri = decode_row(p, m_item * MSUB + sub, ew * 32 + lane);
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) +
                                (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
-        epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
+        epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0, BLOCK_N == 64 ? &aff : nullptr);
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -823,6 +837,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
   } else if (warp >= 4) {
     const int ew = (warp - 4) & 3;
     const int chunk0 = (warp - 4) >> 2;
+    ChunkAffine aff;
+    aff.load(p, chunk0 * 16);
     int as = 0;
     uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -830,7 +846,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
       if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64);
-      epilogue_tile<64>(p, ri, taddr, 0, chunk0);
+      epilogue_tile<64>(p, ri, taddr, 0, chunk0, &aff);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
@@ -1012,11 +1028,11 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   if (n_total == 64) { bn = 64; msub = 2; res = (k_total * 64 * 128) <= 80 * 1024; if (!res) return false; }
   else if (n_total % 256 == 0) bn = 256;
   else if (n_total % 192 == 0) bn = 192;
-  else if (n_total % 128 == 0) bn = 128;
+  else if (n_total % 128 == 0) { bn = 128; msub = 2; }   // measured: sharing B between two sub-tiles wins at N = 128
   else return false;
   if (const char* v = std::getenv("IDN_HALO_BN")) {            // experiments: force an N tile
     const int f = std::atoi(v);
-    if (n_total != 64 && (f == 128 || f == 192 || f == 256) && n_total % f == 0) bn = f;
+    if (n_total != 64 && (f == 128 || f == 192 || f == 256) && n_total % f == 0) { bn = f; msub = 1; }
   }
   if (const char* v = std::getenv("IDN_HALO_MSUB")) {          // experiments: two sub-tiles share B
     if (v[0] == '2' && bn == 128) msub = 2;

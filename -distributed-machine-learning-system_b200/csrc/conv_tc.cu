@@ -998,7 +998,13 @@ int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cud
   const int total = p.num_m_tiles;
   if (total <= 0) return IDN_OK;
   if (p.mode != MODE_STEM || p.num_taps != 7 || p.stem_w == nullptr) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
-  IDN_CUDA_TRY(cudaFuncSetAttribute(stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmemBytes));
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStemSmemBytes));
+    configured[dev & 63] = true;
+  }
   const int grid = total < num_sms ? total : num_sms;
   stem_kernel<<<grid, kThreads, kStemSmemBytes, st>>>(tmA, p);
   IDN_CUDA_TRY(cudaGetLastError());
@@ -1069,8 +1075,14 @@ static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
   if (total <= 0) return IDN_OK;
   const int k_total = p.num_taps * p.c_blocks;
   const int smem = p.a_stages * p.a_stage_bytes + (BRES ? k_total : p.b_stages) * BLOCK_N * 128 + 1024 + 1024;
-  IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  static int configured_smem[64] = {0};       // per device: cudaFuncSetAttribute costs tens of microseconds
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_smem[dev & 63] < smem) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured_smem[dev & 63] = smem;
+  }
   const int grid = total < num_sms ? total : num_sms;
   conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS><<<grid, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
   IDN_CUDA_TRY(cudaGetLastError());

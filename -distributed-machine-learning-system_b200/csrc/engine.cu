@@ -85,6 +85,21 @@ struct idn_engine {
   int stem_left = 0, stem_ws = 232;
   // io staging
   uint8_t* d_imgs = nullptr; size_t d_imgs_cap = 0;
+  // host-buffer entry point: the H2D copy of sub-batch k+1 (copy stream, second staging buffer)
+  // overlaps the kernels of sub-batch k
+  // Two submission slots: each has its own staging buffer, pinned metadata, device and pinned
+  // result buffers and events, so that the H2D copy of one tensor batch runs (on the copy stream)
+  // while the kernels of the previous batch run (on the handle's stream).
+  struct Slot {
+    uint8_t* d_stage = nullptr; size_t d_stage_cap = 0;
+    PreMeta* h_meta = nullptr;
+    int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
+    int32_t* h_idx = nullptr; float* h_prob = nullptr;
+    cudaEvent_t ev_copied = nullptr, ev_done = nullptr;
+    int n = 0; bool busy = false, logits = false;
+  } slot[2];
+  cudaStream_t copy_stream = nullptr;
+  int next_slot = 0;
   int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
   // head
   const bf16* head_act = nullptr; Geom head_g; int head_C = 0;
@@ -561,7 +576,9 @@ static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int*
   return IDN_OK;
 }
 
-static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, int n, int64_t base) {
+static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, int n, int64_t base,
+                     PreMeta* hm = nullptr) {
+  if (hm == nullptr) hm = e->h_meta;
   e->pre_raw_words = 0; e->pre_src_rows = 0;
   int last_h = -1, last_v = -1;
   for (int i = 0; i < n; ++i) {
@@ -569,7 +586,7 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
     if (H <= 0 || W <= 0) { set_error("image with non-positive size"); return IDN_EINVAL; }
     int nh, nw;
     resized_size(H, W, &nh, &nw);
-    PreMeta& m = e->h_meta[i];
+    PreMeta& m = hm[i];
     m.offset = offsets[i] - base; m.H = H; m.W = W;
     IDN_TRY(ensure_table(e, W, nw, crop_offset(nw), &m.htab));
     IDN_TRY(ensure_table(e, H, nh, crop_offset(nh), &m.vtab));
@@ -581,8 +598,7 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
       last_h = m.htab; last_v = m.vtab;
     }
   }
-  IDN_CUDA_TRY(cudaMemcpyAsync(e->d_meta, e->h_meta, sizeof(PreMeta) * n, cudaMemcpyHostToDevice,
-                               e->stream));
+  IDN_CUDA_TRY(cudaMemcpyAsync(e->d_meta, hm, sizeof(PreMeta) * n, cudaMemcpyHostToDevice, e->stream));
   return IDN_OK;
 }
 
@@ -695,6 +711,19 @@ int idn_destroy(idn_handle h) {
   for (void* p : h->dev_allocs) cudaFree(p);
   if (h->d_tables) cudaFree(h->d_tables);
   if (h->d_imgs) cudaFree(h->d_imgs);
+  for (int b = 0; b < 2; ++b) {
+    idn_engine::Slot& sl = h->slot[b];
+    if (sl.d_stage) cudaFree(sl.d_stage);
+    if (sl.d_idx) cudaFree(sl.d_idx);
+    if (sl.d_prob) cudaFree(sl.d_prob);
+    if (sl.d_logits) cudaFree(sl.d_logits);
+    if (sl.h_meta) cudaFreeHost(sl.h_meta);
+    if (sl.h_idx) cudaFreeHost(sl.h_idx);
+    if (sl.h_prob) cudaFreeHost(sl.h_prob);
+    if (sl.ev_copied) cudaEventDestroy(sl.ev_copied);
+    if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+  }
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->h_meta) cudaFreeHost(h->h_meta);
   for (Step& s : h->steps) { if (s.ev0) cudaEventDestroy(s.ev0); if (s.ev1) cudaEventDestroy(s.ev1); }
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -783,39 +812,103 @@ int idn_infer_u8hwc_device(idn_handle h, const uint8_t* d_imgs, const int64_t* o
   return run_plan(h, d_imgs, n, d_idx, d_prob, d_logits);
 }
 
+// ---- asynchronous host-buffer path: submit one tensor batch, collect it later -----------------
+static int slot_setup(idn_handle h, idn_engine::Slot& sl) {
+  if (!h->copy_stream) IDN_CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+  if (sl.ev_done) return IDN_OK;
+  IDN_CUDA_TRY(cudaEventCreateWithFlags(&sl.ev_copied, cudaEventDisableTiming));
+  IDN_CUDA_TRY(cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+  IDN_CUDA_TRY(cudaMallocHost(&sl.h_meta, sizeof(PreMeta) * (size_t)h->cap));
+  IDN_CUDA_TRY(cudaMallocHost(&sl.h_idx, sizeof(int32_t) * (size_t)h->cap));
+  IDN_CUDA_TRY(cudaMallocHost(&sl.h_prob, sizeof(float) * (size_t)h->cap));
+  IDN_CUDA_TRY(cudaMalloc(&sl.d_idx, sizeof(int32_t) * (size_t)h->cap));
+  IDN_CUDA_TRY(cudaMalloc(&sl.d_prob, sizeof(float) * (size_t)h->cap));
+  IDN_CUDA_TRY(cudaMalloc(&sl.d_logits, sizeof(float) * (size_t)h->cap * IDN_NUM_CLASSES));
+  return IDN_OK;
+}
+
+int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, const int32_t* hw,
+                     int n, int want_logits, int* ticket) {
+  if (!h || !imgs || !offsets || !hw || !ticket || n <= 0 || n > h->cap) {
+    set_error("idn_submit_u8hwc: bad argument (0 < n <= max_batch)");
+    return IDN_EINVAL;
+  }
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  const int b = h->next_slot;
+  idn_engine::Slot& sl = h->slot[b];
+  if (sl.busy) { set_error("idn_submit_u8hwc: two submissions are already in flight; collect one first"); return IDN_EINVAL; }
+  IDN_TRY(slot_setup(h, sl));
+  int64_t lo = offsets[0], hi = 0;
+  for (int i = 0; i < n; ++i) {
+    lo = std::min(lo, offsets[i]);
+    hi = std::max(hi, offsets[i] + (int64_t)hw[2 * i] * hw[2 * i + 1] * 3);
+  }
+  const size_t bytes = (size_t)(hi - lo);
+  if (bytes + 64 > sl.d_stage_cap) {          // the slot is free, so nothing reads its staging buffer
+    if (sl.d_stage) cudaFree(sl.d_stage);
+    sl.d_stage = nullptr; sl.d_stage_cap = 0;
+    IDN_CUDA_TRY(cudaMalloc(&sl.d_stage, bytes + 64));
+    sl.d_stage_cap = bytes + 64;
+  }
+  // copy stream: the image bytes; the handle's stream: everything else, after the copy has landed
+  IDN_CUDA_TRY(cudaMemcpyAsync(sl.d_stage, imgs + lo, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+  IDN_CUDA_TRY(cudaEventRecord(sl.ev_copied, h->copy_stream));
+  IDN_CUDA_TRY(cudaStreamWaitEvent(h->stream, sl.ev_copied, 0));
+  IDN_TRY(fill_meta(h, offsets, hw, n, lo, sl.h_meta));
+  IDN_TRY(run_plan(h, sl.d_stage, n, sl.d_idx, sl.d_prob, want_logits ? sl.d_logits : nullptr));
+  IDN_CUDA_TRY(cudaMemcpyAsync(sl.h_idx, sl.d_idx, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, h->stream));
+  IDN_CUDA_TRY(cudaMemcpyAsync(sl.h_prob, sl.d_prob, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+  IDN_CUDA_TRY(cudaEventRecord(sl.ev_done, h->stream));
+  sl.n = n; sl.busy = true; sl.logits = want_logits != 0;
+  *ticket = b;
+  h->next_slot = b ^ 1;
+  return IDN_OK;
+}
+
+int idn_collect(idn_handle h, int ticket, int32_t* top1_idx, float* top1_prob, float* logits) {
+  if (!h || ticket < 0 || ticket > 1 || !top1_idx || !top1_prob || !h->slot[ticket].busy) {
+    set_error("idn_collect: bad ticket or argument");
+    return IDN_EINVAL;
+  }
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  idn_engine::Slot& sl = h->slot[ticket];
+  sl.busy = false;
+  IDN_CUDA_TRY(cudaEventSynchronize(sl.ev_done));
+  std::memcpy(top1_idx, sl.h_idx, sizeof(int32_t) * (size_t)sl.n);
+  std::memcpy(top1_prob, sl.h_prob, sizeof(float) * (size_t)sl.n);
+  if (logits) {
+    if (!sl.logits) { set_error("idn_collect: the submission did not ask for logits"); return IDN_EINVAL; }
+    IDN_CUDA_TRY(cudaMemcpy(logits, sl.d_logits, sizeof(float) * (size_t)sl.n * IDN_NUM_CLASSES, cudaMemcpyDeviceToHost));
+  }
+  return read_tc_watchdog();
+}
+
 int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, const int32_t* hw,
                     int n, int32_t* top1_idx, float* top1_prob, float* logits) {
   if (!h || !imgs || !offsets || !hw || !top1_idx || !top1_prob || n < 0) {
     set_error("idn_infer_u8hwc: bad argument");
     return IDN_EINVAL;
   }
-  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  if (h->slot[0].busy || h->slot[1].busy) { set_error("idn_infer_u8hwc: collect pending submissions first"); return IDN_EINVAL; }
+  // tensor batches of max_batch images, two in flight: the copy of batch k+1 overlaps the kernels of k
+  int prev_ticket = -1, prev_i0 = 0;
   for (int i0 = 0; i0 < n; i0 += h->cap) {
     const int m = std::min(h->cap, n - i0);
-    int64_t lo = offsets[i0], hi = 0;
-    for (int i = i0; i < i0 + m; ++i) {
-      lo = std::min(lo, offsets[i]);
-      hi = std::max(hi, offsets[i] + (int64_t)hw[2 * i] * hw[2 * i + 1] * 3);
+    int ticket = -1;
+    int rc = idn_submit_u8hwc(h, imgs, offsets + i0, hw + 2 * i0, m, logits != nullptr, &ticket);
+    if (rc == IDN_OK && prev_ticket >= 0)
+      rc = idn_collect(h, prev_ticket, top1_idx + prev_i0, top1_prob + prev_i0,
+                       logits ? logits + (size_t)prev_i0 * IDN_NUM_CLASSES : nullptr);
+    if (rc != IDN_OK) {                         // drain so that the handle stays usable
+      cudaStreamSynchronize(h->stream);
+      h->slot[0].busy = h->slot[1].busy = false;
+      return rc;
     }
-    const size_t bytes = (size_t)(hi - lo);
-    if (bytes + 64 > h->d_imgs_cap) {
-      IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));
-      if (h->d_imgs) cudaFree(h->d_imgs);
-      h->d_imgs = nullptr; h->d_imgs_cap = 0;
-      IDN_CUDA_TRY(cudaMalloc(&h->d_imgs, bytes + 64));
-      h->d_imgs_cap = bytes + 64;
-    }
-    IDN_CUDA_TRY(cudaMemcpyAsync(h->d_imgs, imgs + lo, bytes, cudaMemcpyHostToDevice, h->stream));
-    IDN_TRY(fill_meta(h, offsets + i0, hw + 2 * i0, m, lo));
-    IDN_TRY(run_plan(h, h->d_imgs, m, h->d_idx, h->d_prob, logits ? h->d_logits : nullptr));
-    IDN_CUDA_TRY(cudaMemcpyAsync(top1_idx + i0, h->d_idx, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, h->stream));
-    IDN_CUDA_TRY(cudaMemcpyAsync(top1_prob + i0, h->d_prob, sizeof(float) * m, cudaMemcpyDeviceToHost, h->stream));
-    if (logits)
-      IDN_CUDA_TRY(cudaMemcpyAsync(logits + (size_t)i0 * IDN_NUM_CLASSES, h->d_logits,
-                                   sizeof(float) * m * IDN_NUM_CLASSES, cudaMemcpyDeviceToHost, h->stream));
-    IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));   // h_meta / staging are reused by the next chunk
-    IDN_TRY(read_tc_watchdog());
+    prev_ticket = ticket; prev_i0 = i0;
   }
+  if (prev_ticket >= 0)
+    return idn_collect(h, prev_ticket, top1_idx + prev_i0, top1_prob + prev_i0,
+                       logits ? logits + (size_t)prev_i0 * IDN_NUM_CLASSES : nullptr);
   return IDN_OK;
 }
 

@@ -25,6 +25,9 @@ SIGNATURES = {
     "idn_set_impl": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_infer_u8hwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                   C.c_void_p, C.c_void_p, C.c_void_p]),
+    "idn_submit_u8hwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                   C.POINTER(C.c_int)]),
+    "idn_collect": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "idn_infer_u8hwc_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "idn_sync": (C.c_int, [C.c_void_p]),

@@ -100,6 +100,26 @@ class Engine:
         packed, offsets, hw = pack_images(images)
         return self.infer_packed(packed, offsets, hw, want_logits)
 
+    def submit_packed(self, offsets: np.ndarray, hw: np.ndarray, packed_ptr: int, want_logits: bool = False):
+        """Enqueue one tensor batch (host buffer at ``packed_ptr``, best pinned; it must stay alive until
+        ``collect``).  Returns a ticket; at most two submissions may be in flight."""
+        n = int(offsets.shape[0])
+        t = C.c_int(-1)
+        hw32 = np.ascontiguousarray(hw, dtype=np.int32)
+        _lib.check(self._lib.idn_submit_u8hwc(self._h, C.c_void_p(packed_ptr), offsets.ctypes.data,
+                                              hw32.ctypes.data, n, int(want_logits), C.byref(t)),
+                   "idn_submit_u8hwc")
+        return (t.value, n, want_logits)
+
+    def collect(self, ticket):
+        t, n, want_logits = ticket
+        idx = np.zeros(n, dtype=np.int32)
+        prob = np.zeros(n, dtype=np.float32)
+        logits = np.zeros((n, 1000), dtype=np.float32) if want_logits else None
+        _lib.check(self._lib.idn_collect(self._h, t, idx.ctypes.data, prob.ctypes.data,
+                                         logits.ctypes.data if logits is not None else None), "idn_collect")
+        return idx, prob, logits
+
     def infer_device(self, d_imgs_ptr: int, offsets: np.ndarray, hw: np.ndarray, d_idx_ptr: int,
                      d_prob_ptr: int, d_logits_ptr: int | None = None):
         """Device-resident images and results; asynchronous on the handle's stream."""

@@ -84,6 +84,18 @@ int idn_set_impl(idn_handle h, int impl);
 int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* offsets,
                     const int32_t* hw, int n, int32_t* top1_idx, float* top1_prob, float* logits);
 
+/* The same call split in two, for hosts that stage the next query while the current one runs (the
+ * reference's worker loop decodes and classifies strictly one image after the other,
+ * alexnet_resnet.py:48-90).  idn_submit_u8hwc enqueues the H2D copy of one tensor batch
+ * (n <= max_batch) on a copy stream and the kernels on the handle's stream and returns at once;
+ * idn_collect blocks until that batch is done and copies the results out.  At most two submissions
+ * may be in flight, so the copy of batch k+1 overlaps the kernels of batch k; idn_infer_u8hwc uses
+ * exactly this for inputs longer than max_batch.  The image buffer must stay valid (and is best
+ * pinned) until the batch has been collected.  ticket identifies the submission. */
+int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* offsets,
+                     const int32_t* hw, int n, int want_logits, int* ticket);
+int idn_collect(idn_handle h, int ticket, int32_t* top1_idx, float* top1_prob, float* logits);
+
 /* Same computation with the image bytes and the results resident in DEVICE memory (offsets/hw stay
  * host arrays: a few bytes of metadata).  Asynchronous on the handle's stream; n <= max_batch. */
 int idn_infer_u8hwc_device(idn_handle h, const uint8_t* d_imgs_packed, const int64_t* offsets,

@@ -197,3 +197,31 @@ def test_deeplearning_dropin_matches_oracle(built_library, tmp_path, monkeypatch
         assert isinstance(secs, float) and secs > 0
         assert shim.deeplearning(model, model, 100, 105)[0] == []          # nothing found
         assert Image.open(f"{model}/test_6.JPEG").mode == "RGB"            # rewritten in place (:51-54)
+
+
+def test_submit_collect_overlaps_and_matches_infer(built_library):
+    """idn_submit_u8hwc / idn_collect: two tensor batches in flight give the same results as the
+    one-call form, a third submission is refused, and long inputs (which use the same slots inside
+    idn_infer_u8hwc) come back in order."""
+    import torch
+    from idunno_b200 import IdunnoError
+    sd = make_state_dict("resnet18", 0, "default")
+    a = [synth_image(i, mixed=True) for i in range(9)]
+    b = [synth_image(50 + i) for i in range(5)]
+    with Engine("resnet18", sd, max_batch=12) as eng:
+        ia, pa, la = eng.infer(a, want_logits=True)
+        ib, pb, _ = eng.infer(b)
+        pk_a, off_a, hw_a = pack_images(a)
+        pk_b, off_b, hw_b = pack_images(b)
+        ta = eng.submit_packed(off_a, hw_a, pk_a.ctypes.data, want_logits=True)
+        tb = eng.submit_packed(off_b, hw_b, pk_b.ctypes.data)
+        with pytest.raises(IdunnoError):
+            eng.submit_packed(off_b, hw_b, pk_b.ctypes.data)
+        ga = eng.collect(ta)
+        gb = eng.collect(tb)
+        assert np.array_equal(ga[0], ia) and np.array_equal(ga[1], pa) and np.array_equal(ga[2], la)
+        assert np.array_equal(gb[0], ib) and np.array_equal(gb[1], pb) and gb[2] is None
+        many = a + b + a + b + a                    # 37 images through a 12-image engine: 4 batches
+        im, pm, _ = eng.infer(many)
+        assert np.array_equal(im, np.concatenate([ia, ib, ia, ib, ia]))
+        assert np.array_equal(pm, np.concatenate([pa, pb, pa, pb, pa]))

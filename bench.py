@@ -54,7 +54,12 @@ WORKLOAD = {"alexnet": "AlexNet batch 400 over range 0-3999 (uint8 224x224 HWC -
             "resnet18": "ResNet18 batch 400 over range 0-79999 sharded by rank (uint8 224x224 HWC -> top-1)"}
 # dram__bytes_read+write per launch of the dominant kernel from the committed `ncu --set full`
 # capture (profiles/), keyed by (model, step); None until a capture exists for that kernel.
-NCU_TRAFFIC_BYTES: dict = {}
+NCU_TRAFFIC_BYTES: dict = {
+    # profiles/r01b_alexnet_conv2_ncu.txt: conv_halo_kernel<192,1,0,0>, 43.80 MB read + 58.78 MB written
+    ("alexnet", "features.3+relu"): 102577408,
+    # profiles/r01b_resnet18_convs_ncu_full.csv: stem_kernel, 166.53 MB read + 589.15 MB written
+    ("resnet18", "conv1+bn1+relu"): 755691776,
+}
 
 
 def load_peaks():
@@ -239,7 +244,7 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
     dom = max(tc_steps, key=tc_steps.get)
     achieved = flops[dom] * BATCH / (tc_steps[dom] * 1e-3) / 1e12
     peak = peaks["tf_sustained"]
-    roofline = {"bound": "tensor", "kernel": f"conv_tc_kernel[{dom}]", "achieved": round(achieved, 2),
+    roofline = {"bound": "tensor", "kernel": f"tcgen05 implicit-GEMM conv [{dom}]", "achieved": round(achieved, 2),
                 "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
                 "traffic": NCU_TRAFFIC_BYTES.get((model, dom)),
                 "peak_source": f"MEASURED_PEAKS.json bf16 sustained ({peaks['source']})",

@@ -698,6 +698,27 @@ extern "C" {
 const char* idn_last_error(void) { return idn::last_error_cstr(); }
 const char* idn_version(void) { return "idunno_b200 0.1 sm_100a"; }
 
+int idn_host_alloc(int device, size_t n_bytes, void** out) {
+  if (!out || n_bytes == 0) { set_error("idn_host_alloc: bad argument"); return IDN_EINVAL; }
+  *out = nullptr;
+  if (int rc = check_device(device)) return rc;
+  if (cudaSetDevice(device) != cudaSuccess) { set_error("idn_host_alloc: cudaSetDevice failed"); return IDN_ECUDA; }
+  cudaError_t err = cudaHostAlloc(out, n_bytes, cudaHostAllocPortable);
+  if (err != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_error(std::string("idn_host_alloc: ") + cudaGetErrorString(err));
+    *out = nullptr;
+    return IDN_ENOMEM;
+  }
+  return IDN_OK;
+}
+
+int idn_host_free(void* p) {
+  if (!p) return IDN_OK;
+  if (cudaFreeHost(p) != cudaSuccess) { (void)cudaGetLastError(); set_error("idn_host_free: not a pointer from idn_host_alloc"); return IDN_EINVAL; }
+  return IDN_OK;
+}
+
 int64_t idn_weight_count(int model_id) {
   if (model_id == IDN_MODEL_ALEXNET) return 61100840LL;
   if (model_id == IDN_MODEL_RESNET18) return 11699112LL;

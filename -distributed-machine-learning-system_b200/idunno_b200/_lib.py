@@ -45,6 +45,8 @@ SIGNATURES = {
     "idn_conv2d_nchw": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "idn_host_alloc": (C.c_int, [C.c_int, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "idn_host_free": (C.c_int, [C.c_void_p]),
     "idn_last_error": (C.c_char_p, []),
     "idn_version": (C.c_char_p, []),
 }

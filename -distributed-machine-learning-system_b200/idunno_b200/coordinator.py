@@ -44,9 +44,12 @@ class BoxCoordinator:
         self.finished = {"alexnet": [], "resnet18": []}            # (t_finish, images, seconds per 400)
 
     # ---------------------------------------------------------------- assignment (:501-539)
-    def assign(self, model: str, qnum, start: int, end: int):
+    def assign(self, model: str, qnum, start: int, end: int, n_workers: int | None = None):
+        """``n_workers`` overrides the fair-share count (a box that runs a single job uses every rank;
+        the reference always halves the pool because both jobs are assumed active, :504-514)."""
         alive = sorted(self.alive)
-        n = sharding.fair_share(model, self.avg_time, len(alive))
+        n = sharding.fair_share(model, self.avg_time, len(alive)) if n_workers is None else min(n_workers, len(alive))
+        n = max(n, 1) if alive else 0      # with measured times the formula can round to 0: a query still needs a rank
         workers = self.rng.sample(alive, n) if n > 0 else []
         now = self.clock()
         key = (model, qnum)
@@ -84,9 +87,12 @@ class BoxCoordinator:
         return self.finished[model]
 
     def _update_avg(self, model: str):
-        w = self._window(model)
-        if w:
-            self.avg_time[model] = mean(x[2] for x in w)   # the update the reference left commented out (:676)
+        # the update the reference left commented out (:676).  The ratio only means something once BOTH
+        # models have been measured; until then both stay at the reference's constant (equal shares).
+        wa, wr = self._window("alexnet"), self._window("resnet18")
+        if wa and wr:
+            self.avg_time["alexnet"] = mean(x[2] for x in wa)
+            self.avg_time["resnet18"] = mean(x[2] for x in wr)
 
     def query_done(self, model: str, qnum) -> bool:
         entries = self.worker_set[(model, qnum)]

@@ -204,3 +204,28 @@ def conv2d_nchw(x, w, scale=None, shift=None, residual=None, stride=1, pad=0, re
         sc.ctypes.data if sc is not None else None, sh.ctypes.data if sh is not None else None,
         rs.ctypes.data if rs is not None else None, int(relu), y.ctypes.data), "idn_conv2d_nchw")
     return y
+
+
+class PinnedBuffer:
+    """Page-locked host bytes from idn_host_alloc, exposed as a numpy uint8 array (``.array``).
+    Keep the object alive while a submission that reads it is in flight."""
+
+    def __init__(self, n_bytes: int, device: int = 0):
+        self._lib = _lib.load_library()
+        p = C.c_void_p()
+        _lib.check(self._lib.idn_host_alloc(device, int(n_bytes), C.byref(p)), "idn_host_alloc")
+        self.ptr = p.value
+        self.nbytes = int(n_bytes)
+        self.array = np.ctypeslib.as_array((C.c_uint8 * self.nbytes).from_address(self.ptr))
+
+    def close(self):
+        if getattr(self, "ptr", None):
+            self.array = None
+            self._lib.idn_host_free(C.c_void_p(self.ptr))
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

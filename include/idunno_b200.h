@@ -168,6 +168,15 @@ int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_packed, const
                                  const int32_t* hw, int n, uint16_t* d_out_nchw_bf16,
                                  void* cuda_stream);
 
+/* Page-locked host memory for image staging (no reference counterpart: the reference keeps decoded
+ * images in PIL objects and copies one 602 KB tensor per image, alexnet_resnet.py:67-72).  A batch
+ * staged in such a buffer is copied by DMA at the full host-link rate and lets idn_submit_u8hwc
+ * return before the copy has finished; pageable memory works too but is staged through a bounce
+ * buffer by the driver.  `device` only selects the context the allocation is made in; the memory is
+ * usable with every device (portable). */
+int idn_host_alloc(int device, size_t n_bytes, void** out);
+int idn_host_free(void* p);
+
 const char* idn_last_error(void);
 
 /* Library build identification ("idunno_b200 <version> sm_100a"). */

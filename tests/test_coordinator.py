@@ -30,9 +30,16 @@ def test_assign_covers_range_with_fair_share_of_workers():
     assert c.c1()["resnet18"] == pytest.approx(400 / 30.0)
     assert c.c2()["resnet18"][0] == pytest.approx(10.0)
     assert c.c2()["alexnet"] is None
-    # measured times now drive the fair share (the reference leaves them at 100/100)
-    assert c.avg_time["resnet18"] == pytest.approx(10.0)
-    assert sharding.fair_share("alexnet", c.avg_time, 8) > sharding.fair_share("resnet18", c.avg_time, 8)
+    # one model measured only: the ratio is not meaningful yet, both stay at the reference's constant
+    assert c.avg_time == {"alexnet": 100.0, "resnet18": 100.0}
+    # once both are measured the times drive the fair share (the reference leaves them at 100/100):
+    # the slower model gets more ranks
+    ea = c.assign("alexnet", 8, 0, 399)
+    clk.t += 0.5
+    for (r, s, e, *_rest) in ea:
+        assert c.mark_finished("alexnet", 8, s, e)
+    assert c.avg_time["resnet18"] == pytest.approx(10.0) and c.avg_time["alexnet"] == pytest.approx(2.5)
+    assert sharding.fair_share("resnet18", c.avg_time, 8) > sharding.fair_share("alexnet", c.avg_time, 8) >= 1
 
 
 def test_worker_loss_moves_whole_subranges():

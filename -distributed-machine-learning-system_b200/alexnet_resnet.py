@@ -67,11 +67,9 @@ def deeplearning(filename, modelname, start_image, end_image):
     time_start = time.time()
     eng = _engine(modelname)
     categories = staging.categories()
-    indices, images = staging.load_range(filename, start_image, end_image)
+    indices, idx, prob = staging.classify_range(eng, filename, start_image, end_image)
     inference_result = []
-    if images:
-        idx, prob, _ = eng.infer(images)
-        for i, k, p in zip(indices, idx, prob):
-            inference_result.append(("test_" + str(i) + ".JPEG", categories[int(k)], float(p)))
+    for i, k, p in zip(indices, idx, prob):
+        inference_result.append(("test_" + str(i) + ".JPEG", categories[int(k)], float(p)))
     time_end = time.time()
     return inference_result, (time_end - time_start)

@@ -271,7 +271,16 @@ class SyntheticImageSet:
         self.img_bytes = self.h * self.w * 3
         periods = (max_batch + SET_PERIOD - 1) // SET_PERIOD + 1
         self.buf = PinnedBuffer(periods * SET_PERIOD * self.img_bytes, device)
-        block = np.concatenate([synth_image(i, (self.h, self.w)).reshape(-1) for i in range(SET_PERIOD)])
+        import os
+        cache = os.environ.get("IDN_SYNTH_BLOCK")          # generating 400 images takes seconds: share it
+        if cache and os.path.exists(cache):
+            block = np.load(cache)
+        else:
+            block = np.concatenate([synth_image(i, (self.h, self.w)).reshape(-1) for i in range(SET_PERIOD)])
+            if cache:
+                np.save(cache + f".{os.getpid()}.npy", block)
+                os.replace(cache + f".{os.getpid()}.npy", cache)
+        assert block.size == SET_PERIOD * self.img_bytes
         view = self.buf.array.reshape(periods, SET_PERIOD * self.img_bytes)
         view[:] = block[None, :]
         self.max_batch = max_batch
@@ -335,9 +344,10 @@ def _exit_after(n_batches: int):
 
 
 def gpu_worker_main(host: str, port: int, rank: int, max_batch: int, die_after_batches: int | None = None,
-                    preload=("resnet18",)):
-    """Entry point of one GPU worker process (rank == CUDA device index)."""
-    classify = gpu_classifier(rank, max_batch)
+                    preload=("resnet18",), device: int | None = None):
+    """Entry point of one GPU worker process (CUDA device index = rank unless ``device`` says otherwise:
+    the single-GPU test runs two ranks on one device)."""
+    classify = gpu_classifier(rank if device is None else device, max_batch)
     for m in preload:                      # weights resident before the first heartbeat is sent
         classify.engine(m)
     worker_loop(host, port, rank, classify,

@@ -108,3 +108,38 @@ def test_no_cpu_fallback_without_a_device():
     # bad arguments are rejected before any device work
     assert lib.idn_create(0, 5, blob.ctypes.data, blob.nbytes, 8, ctypes.byref(h)) == -1
     assert lib.idn_create(0, 1, blob.ctypes.data, 16, 8, ctypes.byref(h)) == -4
+
+
+def test_stage_chunk_layout_and_reference_file_semantics(tmp_path, monkeypatch):
+    """Decode threads -> ragged buffer: 16-byte aligned starts, exact pixels, missing files skipped,
+    non-RGB files converted and rewritten in place (alexnet_resnet.py:46-54)."""
+    from concurrent.futures import ThreadPoolExecutor
+    from PIL import Image
+    from idunno_b200 import staging
+    from idunno_b200.synth import synth_image
+    monkeypatch.chdir(tmp_path)
+    os.makedirs("alexnet")
+    sizes = {3: (224, 224), 4: (37, 53), 6: (300, 200), 7: (64, 96)}          # index 5 is missing
+    want = {}
+    for i, hw in sizes.items():
+        a = synth_image(i, hw)
+        if i == 6:
+            a = a[:, :, 0]                                                     # grayscale file
+            Image.fromarray(a, mode="L").save(f"alexnet/test_{i}.JPEG", format="PNG")
+            want[i] = np.repeat(a[:, :, None], 3, axis=2)
+        else:
+            Image.fromarray(a).save(f"alexnet/test_{i}.JPEG", format="PNG")
+            want[i] = a
+    files = staging.discover("alexnet", "3", 8)
+    assert [f[0] for f in files] == [3, 4, 6, 7]
+    with ThreadPoolExecutor(max_workers=3) as pool:
+        c = staging.stage_chunk(files, lambda n: np.zeros(n, dtype=np.uint8), pool)
+    assert list(c.indices) == [3, 4, 6, 7]
+    assert all(int(o) % staging.ALIGN == 0 for o in c.offsets)
+    for k, i in enumerate(c.indices):
+        h, w = c.hw[k]
+        assert (h, w) == sizes[int(i)]
+        o = int(c.offsets[k])
+        assert np.array_equal(c.buf[o:o + h * w * 3].reshape(h, w, 3), want[int(i)])
+    assert Image.open("alexnet/test_6.JPEG").mode == "RGB"                    # rewritten like the reference
+    assert staging.discover("alexnet", 100, 105) == [] and staging.discover("nosuchfolder", 0, 5) == []

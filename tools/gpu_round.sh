@@ -10,7 +10,7 @@ case $w in
 diag)
   timeout 600 python tools/gpu_diag.py > gpurun_out/diag.log 2>&1; echo "diag rc=$?" ;;
 tests)
-  for f in tests/test_gpu_preprocess.py tests/test_gpu_conv.py tests/test_gpu_model.py tests/test_zz_no_alloc.py; do
+  for f in tests/test_gpu_preprocess.py tests/test_gpu_conv.py tests/test_gpu_model.py tests/test_gpu_boxrun.py tests/test_zz_no_alloc.py; do
     b=$(basename $f .py)
     timeout 1500 python -m pytest $f -m gpu -q -rA -s -p no:cacheprovider > gpurun_out/$b.log 2>&1
     echo "$b rc=$? $(tail -1 gpurun_out/$b.log)"
@@ -26,8 +26,8 @@ benchref)
   echo "benchref rc=$?"; cut -c1-600 gpurun_out/bench_ref.json ;;
 ncu)
   for m in alexnet resnet18; do
-    # one pass = 13 launches (alexnet) / 24 (resnet18); skip the 3 warm-up passes, list 2 passes
-    if [ $m = alexnet ]; then SK=39; CN=26; else SK=72; CN=48; fi
+    # one pass = 13 launches (alexnet) / 25 (resnet18); skip the 3 warm-up passes, list 2 passes
+    if [ $m = alexnet ]; then SK=39; CN=26; else SK=75; CN=50; fi
     timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_$m.log 2>&1 &&
     timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s $SK -c $CN --csv \
         --log-file gpurun_out/launches_$m.csv python bench.py --steps 2 --warmup 3 --models $m \
@@ -41,5 +41,15 @@ ncufull)
       -s ${NCU_SKIP:-60} -c ${NCU_COUNT:-20} -o gpurun_out/prof_${NCU_TAG:-$m} -f python bench.py --steps 2 --warmup 3 --models $m \
       > gpurun_out/ncu_full_$m.log 2>&1
   echo "ncu full $m rc=$?" ;;
+scen)
+  timeout 1500 python tools/box_scenarios.py --gpus ${SCEN_GPUS:-2} --scenario ${SCEN_WHAT:-all} \
+      --batches ${SCEN_BATCHES:-64,128,256,512,1024,2048,4096} --per-rank ${SCEN_PER_RANK:-10000} \
+      > gpurun_out/scen_${SCEN_GPUS:-2}gpu.log 2>&1
+  echo "scen rc=$?"; grep '^{' gpurun_out/scen_${SCEN_GPUS:-2}gpu.log | cut -c1-700 ;;
+benchN)
+  N=${BENCH_GPUS:-2}
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 \
+      bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err
+  echo "bench$N rc=$?"; cut -c1-900 gpurun_out/bench_${N}gpu.json ;;
 esac
 done

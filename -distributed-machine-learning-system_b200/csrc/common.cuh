@@ -169,6 +169,10 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
                        int32_t* idx, float* prob, cudaStream_t st);
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out_or_null,
                         int32_t* idx, float* prob, cudaStream_t st);
+// Copies n_words 32-bit words with SM loads/stores.  Used for the few KB of per-batch records that come
+// from page-locked host memory: a cudaMemcpyAsync would queue behind the 60 MB image copy of the NEXT
+// batch on the host-to-device copy engine and stall this batch's kernels for a millisecond.
+int launch_copy_words(void* dst, const void* src, size_t n_words, cudaStream_t st);
 
 // preprocess (preprocess.cu)
 struct PreMeta {            // one per image, device resident

@@ -74,7 +74,9 @@ struct idn_engine {
   std::vector<Step> steps;
   // preprocess
   PreMeta* d_meta = nullptr;
-  PreMeta* h_meta = nullptr;          // pinned
+  PreMeta* h_meta = nullptr;          // pinned, kMetaRing x cap records (device-resident entry point)
+  cudaEvent_t meta_ev[4] = {nullptr, nullptr, nullptr, nullptr};   // "ring entry has been read"
+  int meta_ring = 1, meta_next = 0;
   int* d_tables = nullptr;
   size_t tables_cap = 0, tables_used = 0;   // int32 units
   std::map<std::tuple<int, int, int>, int> table_index;
@@ -93,8 +95,8 @@ struct idn_engine {
   struct Slot {
     uint8_t* d_stage = nullptr; size_t d_stage_cap = 0;
     PreMeta* h_meta = nullptr;
-    int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
-    int32_t* h_idx = nullptr; float* h_prob = nullptr;
+    float* d_logits = nullptr;
+    int32_t* h_idx = nullptr; float* h_prob = nullptr;       // pinned; the last kernel stores into them
     cudaEvent_t ev_copied = nullptr, ev_done = nullptr;
     int n = 0; bool busy = false, logits = false;
   } slot[2];
@@ -578,7 +580,15 @@ static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int*
 
 static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, int n, int64_t base,
                      PreMeta* hm = nullptr) {
-  if (hm == nullptr) hm = e->h_meta;
+  int ring = -1;
+  if (hm == nullptr) {
+    // The records are read by a kernel when the stream gets there, not now: rotate through a few
+    // buffers and wait (normally not at all) until the previous reader of this one has run.
+    ring = e->meta_next;
+    e->meta_next = (e->meta_next + 1) % e->meta_ring;
+    if (e->meta_ev[ring]) IDN_CUDA_TRY(cudaEventSynchronize(e->meta_ev[ring]));
+    hm = e->h_meta + (size_t)ring * (e->meta_ring > 1 ? e->cap : 0);
+  }
   e->pre_raw_words = 0; e->pre_src_rows = 0;
   int last_h = -1, last_v = -1;
   for (int i = 0; i < n; ++i) {
@@ -598,7 +608,13 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
       last_h = m.htab; last_v = m.vtab;
     }
   }
-  IDN_CUDA_TRY(cudaMemcpyAsync(e->d_meta, hm, sizeof(PreMeta) * n, cudaMemcpyHostToDevice, e->stream));
+  static_assert(sizeof(PreMeta) % 4 == 0, "PreMeta is copied in 32-bit words");
+  IDN_TRY(launch_copy_words(e->d_meta, hm, sizeof(PreMeta) / 4 * (size_t)n, e->stream));
+  e->launches++;
+  if (ring >= 0) {
+    if (!e->meta_ev[ring]) IDN_CUDA_TRY(cudaEventCreateWithFlags(&e->meta_ev[ring], cudaEventDisableTiming));
+    IDN_CUDA_TRY(cudaEventRecord(e->meta_ev[ring], e->stream));
+  }
   return IDN_OK;
 }
 
@@ -735,8 +751,6 @@ int idn_destroy(idn_handle h) {
   for (int b = 0; b < 2; ++b) {
     idn_engine::Slot& sl = h->slot[b];
     if (sl.d_stage) cudaFree(sl.d_stage);
-    if (sl.d_idx) cudaFree(sl.d_idx);
-    if (sl.d_prob) cudaFree(sl.d_prob);
     if (sl.d_logits) cudaFree(sl.d_logits);
     if (sl.h_meta) cudaFreeHost(sl.h_meta);
     if (sl.h_idx) cudaFreeHost(sl.h_idx);
@@ -746,6 +760,7 @@ int idn_destroy(idn_handle h) {
   }
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   if (h->h_meta) cudaFreeHost(h->h_meta);
+  for (cudaEvent_t& ev : h->meta_ev) if (ev) { cudaEventDestroy(ev); ev = nullptr; }
   for (Step& s : h->steps) { if (s.ev0) cudaEventDestroy(s.ev0); if (s.ev1) cudaEventDestroy(s.ev1); }
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
@@ -781,7 +796,8 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   e->stream = e->own_stream;
   if ((rc = conv_tc_configure()) != IDN_OK) return fail(rc);
   if ((rc = dev_alloc(e.get(), &e->d_meta, (size_t)max_batch)) != IDN_OK) return fail(rc);
-  if (cudaMallocHost(&e->h_meta, sizeof(PreMeta) * max_batch) != cudaSuccess) {
+  e->meta_ring = 4;
+  if (cudaMallocHost(&e->h_meta, sizeof(PreMeta) * max_batch * e->meta_ring) != cudaSuccess) {
     set_error("cudaMallocHost failed"); return fail(IDN_ENOMEM);
   }
   uint16_t lut[768];
@@ -842,8 +858,6 @@ static int slot_setup(idn_handle h, idn_engine::Slot& sl) {
   IDN_CUDA_TRY(cudaMallocHost(&sl.h_meta, sizeof(PreMeta) * (size_t)h->cap));
   IDN_CUDA_TRY(cudaMallocHost(&sl.h_idx, sizeof(int32_t) * (size_t)h->cap));
   IDN_CUDA_TRY(cudaMallocHost(&sl.h_prob, sizeof(float) * (size_t)h->cap));
-  IDN_CUDA_TRY(cudaMalloc(&sl.d_idx, sizeof(int32_t) * (size_t)h->cap));
-  IDN_CUDA_TRY(cudaMalloc(&sl.d_prob, sizeof(float) * (size_t)h->cap));
   IDN_CUDA_TRY(cudaMalloc(&sl.d_logits, sizeof(float) * (size_t)h->cap * IDN_NUM_CLASSES));
   return IDN_OK;
 }
@@ -876,9 +890,9 @@ int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, 
   IDN_CUDA_TRY(cudaEventRecord(sl.ev_copied, h->copy_stream));
   IDN_CUDA_TRY(cudaStreamWaitEvent(h->stream, sl.ev_copied, 0));
   IDN_TRY(fill_meta(h, offsets, hw, n, lo, sl.h_meta));
-  IDN_TRY(run_plan(h, sl.d_stage, n, sl.d_idx, sl.d_prob, want_logits ? sl.d_logits : nullptr));
-  IDN_CUDA_TRY(cudaMemcpyAsync(sl.h_idx, sl.d_idx, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, h->stream));
-  IDN_CUDA_TRY(cudaMemcpyAsync(sl.h_prob, sl.d_prob, sizeof(float) * n, cudaMemcpyDeviceToHost, h->stream));
+  // The softmax/top-1 kernel stores its 8 bytes per image straight into the slot's page-locked host
+  // buffers (device-visible under unified addressing): no device-to-host copy to queue anywhere.
+  IDN_TRY(run_plan(h, sl.d_stage, n, sl.h_idx, sl.h_prob, want_logits ? sl.d_logits : nullptr));
   IDN_CUDA_TRY(cudaEventRecord(sl.ev_done, h->stream));
   sl.n = n; sl.busy = true; sl.logits = want_logits != 0;
   *ticket = b;
@@ -946,6 +960,7 @@ int idn_preprocess_u8hwc(int device, const uint8_t* imgs, const int64_t* offsets
     for (void* p : tmp.dev_allocs) cudaFree(p);
     if (tmp.d_tables) cudaFree(tmp.d_tables);
     if (tmp.h_meta) cudaFreeHost(tmp.h_meta);
+    for (cudaEvent_t& ev : tmp.meta_ev) if (ev) { cudaEventDestroy(ev); ev = nullptr; }
     if (d_in) cudaFree(d_in);
     if (d_out) cudaFree(d_out);
   };

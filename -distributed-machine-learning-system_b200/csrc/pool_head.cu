@@ -102,6 +102,20 @@ int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out
   return IDN_OK;
 }
 
+__global__ void __launch_bounds__(256)
+copy_words_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+
+int launch_copy_words(void* dst, const void* src, size_t n_words, cudaStream_t st) {
+  if (n_words == 0) return IDN_OK;
+  const unsigned blocks = (unsigned)std::min<size_t>((n_words + 255) / 256, 64);
+  copy_words_kernel<<<blocks, 256, 0, st>>>(static_cast<uint32_t*>(dst), static_cast<const uint32_t*>(src), n_words);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
 // ---------------------------------------------------------------------------------- ResNet head
 // avgpool (tv:models/resnet.py:278) -> fp32 features, fc (:280) in fp32 on fp32 weights, then the
 // warp-shuffle softmax/top-1 kernel above (alexnet_resnet.py:80-84).  The FC stays fp32

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include <type_traits>
 
 namespace idn {
 
@@ -185,7 +186,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
   // 4 pixels x 3 channels = 24 contiguous bytes, so the four dy of a block fill 96 contiguous bytes.
   // Channels 48..63 are never written (the buffer is zeroed when it is allocated); positions outside
   // the crop are written as zeros.
-  auto write_s2d4 = [&](auto pixel) {
+  auto write_s2d4 = [&](auto row_ctx, auto pixel) {
     const int by0 = 2 * (int)blockIdx.x;
     for (int it = tid; it < 2 * 57 * 4; it += blockDim.x) {
       const int dy = it & 3, bx = (it >> 2) % 57, byl = it / (4 * 57);
@@ -193,11 +194,12 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       if (by >= 57) continue;
       uint32_t w[6] = {0u, 0u, 0u, 0u, 0u, 0u};
       if (y >= 0 && y < IDN_CROP) {
+        const auto ctx = row_ctx(y);                  // everything that depends on y only, once per item
 #pragma unroll
         for (int dx = 0; dx < 4; ++dx) {
           const int x = 4 * bx - 2 + dx;
           if (x < 0 || x >= IDN_CROP) continue;
-          const uint32_t px = pixel(y, x);
+          const uint32_t px = pixel(ctx, x);
           const uint32_t c[3] = {s_lut[px & 255u], s_lut[256 + ((px >> 8) & 255u)], s_lut[512 + (px >> 16)]};
 #pragma unroll
           for (int ch = 0; ch < 3; ++ch) {
@@ -234,14 +236,18 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       }
     }
     __syncthreads();
-    if (tid < IDN_CROP) {
-      const int x = tid;
-      // ---- 2. horizontal pass: <= 4 taps, coefficients in registers, 12 source bytes per row
-      {
+    // Upscales and mild downscales (every 224x224 .. ~450-pixel source) have 2-tap kernels; the table
+    // format pads to 4.  The branch is uniform per image, the arithmetic is the same sum with the zero
+    // terms left out.
+    auto passes = [&](auto taps_c) {
+      constexpr int NT = decltype(taps_c)::value;
+      if (tid < IDN_CROP) {
+        const int x = tid;
+        // ---- 2. horizontal pass: <= NT taps, coefficients in registers, 3*NT source bytes per row
         const int x0 = ht[1 + x], xn = ht[1 + IDN_CROP + x];
         const int* hk = ht + 1 + 2 * IDN_CROP + x * hks;
-        int k0 = __ldg(hk), k1 = xn > 1 ? __ldg(hk + 1) : 0, k2 = xn > 2 ? __ldg(hk + 2) : 0,
-            k3 = xn > 3 ? __ldg(hk + 3) : 0;
+        const int k0 = __ldg(hk), k1 = xn > 1 ? __ldg(hk + 1) : 0;
+        const int k2 = (NT > 2 && xn > 2) ? __ldg(hk + 2) : 0, k3 = (NT > 2 && xn > 3) ? __ldg(hk + 3) : 0;
         const int boff = (x0 - c0) * 3;
         int shift = (int)(reinterpret_cast<uintptr_t>(g_first) & 3);
         const uint32_t* rowp = s_raw;
@@ -251,14 +257,16 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
           const int bstart = shift + boff;
           const uint32_t* wp = rowp + (bstart >> 2);
           const int sh = (bstart & 3) * 8;
-          const uint32_t a = wp[0], b = wp[1], c = wp[2], d = wp[3];
-          const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh),
-                         p2 = __funnelshift_r(c, d, sh);           // 12 bytes = 4 RGB pixels
+          const uint32_t a = wp[0], b = wp[1], c = wp[2];
+          const uint32_t p0 = __funnelshift_r(a, b, sh), p1 = __funnelshift_r(b, c, sh);
           int h0 = 1 << 21, h1 = 1 << 21, h2 = 1 << 21;
           h0 += bsel(p0, 0) * k0; h1 += bsel(p0, 1) * k0; h2 += bsel(p0, 2) * k0;
           h0 += bsel(p0, 3) * k1; h1 += bsel(p1, 0) * k1; h2 += bsel(p1, 1) * k1;
-          h0 += bsel(p1, 2) * k2; h1 += bsel(p1, 3) * k2; h2 += bsel(p2, 0) * k2;
-          h0 += bsel(p2, 1) * k3; h1 += bsel(p2, 2) * k3; h2 += bsel(p2, 3) * k3;
+          if (NT > 2) {
+            const uint32_t p2 = __funnelshift_r(c, wp[3], sh);             // 12 bytes = 4 RGB pixels
+            h0 += bsel(p1, 2) * k2; h1 += bsel(p1, 3) * k2; h2 += bsel(p2, 0) * k2;
+            h0 += bsel(p2, 1) * k3; h1 += bsel(p2, 2) * k3; h2 += bsel(p2, 3) * k3;
+          }
           // coefficients are >= 0 and sum to 2^22 (+- rounding), so the result is already in [0, 255]
           *hp = (uint32_t)(h0 >> 22) | ((uint32_t)(h1 >> 22) << 8) | ((uint32_t)(h2 >> 22) << 16);
           hp += IDN_CROP;
@@ -266,35 +274,44 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
           shift = (shift + rowstep) & 3;
         }
       }
-    }
-    __syncthreads();
-    // ---- 3. vertical pass over the uint8 intermediate (Pillow's order) -> packed uint8 RGB
-    auto vertical = [&](int y, int x) -> uint32_t {
-      const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
-      const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
-      const int k0 = __ldg(vk), k1 = yn > 1 ? __ldg(vk + 1) : 0, k2 = yn > 2 ? __ldg(vk + 2) : 0,
-                k3 = yn > 3 ? __ldg(vk + 3) : 0;
-      const int last = nrows - 1;
-      const uint32_t q0 = s_h[y0 * IDN_CROP + x];
-      const uint32_t q1 = s_h[min(y0 + 1, last) * IDN_CROP + x];
-      const uint32_t q2 = s_h[min(y0 + 2, last) * IDN_CROP + x];
-      const uint32_t q3 = s_h[min(y0 + 3, last) * IDN_CROP + x];
-      int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-      a0 += bsel(q0, 0) * k0; a1 += bsel(q0, 1) * k0; a2 += bsel(q0, 2) * k0;
-      a0 += bsel(q1, 0) * k1; a1 += bsel(q1, 1) * k1; a2 += bsel(q1, 2) * k1;
-      a0 += bsel(q2, 0) * k2; a1 += bsel(q2, 1) * k2; a2 += bsel(q2, 2) * k2;
-      a0 += bsel(q3, 0) * k3; a1 += bsel(q3, 1) * k3; a2 += bsel(q3, 2) * k3;
-      return (uint32_t)(a0 >> 22) | ((uint32_t)(a1 >> 22) << 8) | ((uint32_t)(a2 >> 22) << 16);
-    };
-    if (OUT_MODE == PRE_OUT_S2D4) {
-      write_s2d4(vertical);
-    } else if (tid < IDN_CROP) {
+      __syncthreads();
+      // ---- 3. vertical pass over the uint8 intermediate (Pillow's order) -> packed uint8 RGB
+      struct VRow { int r0, r1, r2, r3, k0, k1, k2, k3; };
+      auto vrow = [&](int y) -> VRow {
+        const int y0 = vt[1 + y] - ys0, yn = vt[1 + IDN_CROP + y];
+        const int* vk = vt + 1 + 2 * IDN_CROP + y * vks;
+        const int last = nrows - 1;
+        VRow v;
+        v.r0 = y0 * IDN_CROP; v.r1 = min(y0 + 1, last) * IDN_CROP;
+        v.r2 = min(y0 + 2, last) * IDN_CROP; v.r3 = min(y0 + 3, last) * IDN_CROP;
+        v.k0 = __ldg(vk); v.k1 = yn > 1 ? __ldg(vk + 1) : 0;
+        v.k2 = (NT > 2 && yn > 2) ? __ldg(vk + 2) : 0; v.k3 = (NT > 2 && yn > 3) ? __ldg(vk + 3) : 0;
+        return v;
+      };
+      auto vpix = [&](const VRow& v, int x) -> uint32_t {
+        const uint32_t q0 = s_h[v.r0 + x], q1 = s_h[v.r1 + x];
+        int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+        a0 += bsel(q0, 0) * v.k0; a1 += bsel(q0, 1) * v.k0; a2 += bsel(q0, 2) * v.k0;
+        a0 += bsel(q1, 0) * v.k1; a1 += bsel(q1, 1) * v.k1; a2 += bsel(q1, 2) * v.k1;
+        if (NT > 2) {
+          const uint32_t q2 = s_h[v.r2 + x], q3 = s_h[v.r3 + x];
+          a0 += bsel(q2, 0) * v.k2; a1 += bsel(q2, 1) * v.k2; a2 += bsel(q2, 2) * v.k2;
+          a0 += bsel(q3, 0) * v.k3; a1 += bsel(q3, 1) * v.k3; a2 += bsel(q3, 2) * v.k3;
+        }
+        return (uint32_t)(a0 >> 22) | ((uint32_t)(a1 >> 22) << 8) | ((uint32_t)(a2 >> 22) << 16);
+      };
+      if (OUT_MODE == PRE_OUT_S2D4) {
+        write_s2d4(vrow, vpix);
+      } else if (tid < IDN_CROP) {
 #pragma unroll 2
-      for (int y = ylo; y < yhi; ++y) {
-        const uint32_t px = vertical(y, tid);
-        emit(y, tid, px & 255u, (px >> 8) & 255u, px >> 16);
+        for (int y = ylo; y < yhi; ++y) {
+          const uint32_t px = vpix(vrow(y), tid);
+          emit(y, tid, px & 255u, (px >> 8) & 255u, px >> 16);
+        }
       }
-    }
+    };
+    if (hks <= 2 && vks <= 2) passes(std::integral_constant<int, 2>{});
+    else passes(std::integral_constant<int, 4>{});
   } else {
     __syncthreads();                              // s_lut
     auto direct = [&](int y, int x) -> uint32_t {
@@ -303,7 +320,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       return (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16);
     };
     if (OUT_MODE == PRE_OUT_S2D4) {
-      write_s2d4(direct);
+      write_s2d4([](int y) { return y; }, direct);
     } else if (tid < IDN_CROP) {
       for (int y = ylo; y < yhi; ++y) {
         const uint32_t px = direct(y, tid);

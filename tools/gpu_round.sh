@@ -26,8 +26,8 @@ benchref)
   echo "benchref rc=$?"; cut -c1-600 gpurun_out/bench_ref.json ;;
 ncu)
   for m in alexnet resnet18; do
-    # one pass = 13 launches (alexnet) / 25 (resnet18); skip the 3 warm-up passes, list 2 passes
-    if [ $m = alexnet ]; then SK=39; CN=26; else SK=75; CN=50; fi
+    # one pass = 14 launches (alexnet) / 26 (resnet18); skip the 3 warm-up passes, list 2 passes
+    if [ $m = alexnet ]; then SK=42; CN=28; else SK=78; CN=52; fi
     timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_$m.log 2>&1 &&
     timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s $SK -c $CN --csv \
         --log-file gpurun_out/launches_$m.csv python bench.py --steps 2 --warmup 3 --models $m \

@@ -67,6 +67,8 @@ struct Step {
 
 using namespace idn;
 
+constexpr int kSlots = 3;     // submissions that may be in flight (IDN_MAX_IN_FLIGHT)
+
 struct idn_engine {
   int device = 0, model = 0, cap = 0, num_sms = 148, impl = IDN_IMPL_TC;
   cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -94,12 +96,12 @@ struct idn_engine {
   // while the kernels of the previous batch run (on the handle's stream).
   struct Slot {
     uint8_t* d_stage = nullptr; size_t d_stage_cap = 0;
-    PreMeta* h_meta = nullptr;
+    PreMeta* h_meta = nullptr; PreMeta* d_meta = nullptr;
     float* d_logits = nullptr;
     int32_t* h_idx = nullptr; float* h_prob = nullptr;       // pinned; the last kernel stores into them
     cudaEvent_t ev_copied = nullptr, ev_done = nullptr;
     int n = 0; bool busy = false, logits = false;
-  } slot[2];
+  } slot[kSlots];
   cudaStream_t copy_stream = nullptr;
   int next_slot = 0;
   int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
@@ -579,7 +581,8 @@ static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int*
 }
 
 static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, int n, int64_t base,
-                     PreMeta* hm = nullptr) {
+                     PreMeta* hm = nullptr, PreMeta* d_dst = nullptr, cudaStream_t copy_on = nullptr) {
+  if (d_dst == nullptr) { d_dst = e->d_meta; copy_on = e->stream; }
   int ring = -1;
   if (hm == nullptr) {
     // The records are read by a kernel when the stream gets there, not now: rotate through a few
@@ -609,11 +612,11 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
     }
   }
   static_assert(sizeof(PreMeta) % 4 == 0, "PreMeta is copied in 32-bit words");
-  IDN_TRY(launch_copy_words(e->d_meta, hm, sizeof(PreMeta) / 4 * (size_t)n, e->stream));
+  IDN_TRY(launch_copy_words(d_dst, hm, sizeof(PreMeta) / 4 * (size_t)n, copy_on));
   e->launches++;
   if (ring >= 0) {
     if (!e->meta_ev[ring]) IDN_CUDA_TRY(cudaEventCreateWithFlags(&e->meta_ev[ring], cudaEventDisableTiming));
-    IDN_CUDA_TRY(cudaEventRecord(e->meta_ev[ring], e->stream));
+    IDN_CUDA_TRY(cudaEventRecord(e->meta_ev[ring], copy_on));
   }
   return IDN_OK;
 }
@@ -641,7 +644,8 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
 }
 
 static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx, float* d_prob,
-                    float* d_logits) {
+                    float* d_logits, const PreMeta* d_meta = nullptr) {
+  if (d_meta == nullptr) d_meta = e->d_meta;
   cudaStream_t st = e->stream;
   e->last_n = n;
   int step_no = 0;
@@ -654,7 +658,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     }
     switch (s.kind) {
       case STEP_PRE:
-        IDN_TRY(launch_preprocess(d_imgs, e->d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
+        IDN_TRY(launch_preprocess(d_imgs, d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
                                   e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st));
         break;
       case STEP_CONV:
@@ -748,10 +752,11 @@ int idn_destroy(idn_handle h) {
   for (void* p : h->dev_allocs) cudaFree(p);
   if (h->d_tables) cudaFree(h->d_tables);
   if (h->d_imgs) cudaFree(h->d_imgs);
-  for (int b = 0; b < 2; ++b) {
+  for (int b = 0; b < kSlots; ++b) {
     idn_engine::Slot& sl = h->slot[b];
     if (sl.d_stage) cudaFree(sl.d_stage);
     if (sl.d_logits) cudaFree(sl.d_logits);
+    if (sl.d_meta) cudaFree(sl.d_meta);
     if (sl.h_meta) cudaFreeHost(sl.h_meta);
     if (sl.h_idx) cudaFreeHost(sl.h_idx);
     if (sl.h_prob) cudaFreeHost(sl.h_prob);
@@ -859,6 +864,7 @@ static int slot_setup(idn_handle h, idn_engine::Slot& sl) {
   IDN_CUDA_TRY(cudaMallocHost(&sl.h_idx, sizeof(int32_t) * (size_t)h->cap));
   IDN_CUDA_TRY(cudaMallocHost(&sl.h_prob, sizeof(float) * (size_t)h->cap));
   IDN_CUDA_TRY(cudaMalloc(&sl.d_logits, sizeof(float) * (size_t)h->cap * IDN_NUM_CLASSES));
+  IDN_CUDA_TRY(cudaMalloc(&sl.d_meta, sizeof(PreMeta) * (size_t)h->cap));
   return IDN_OK;
 }
 
@@ -871,7 +877,7 @@ int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, 
   IDN_CUDA_TRY(cudaSetDevice(h->device));
   const int b = h->next_slot;
   idn_engine::Slot& sl = h->slot[b];
-  if (sl.busy) { set_error("idn_submit_u8hwc: two submissions are already in flight; collect one first"); return IDN_EINVAL; }
+  if (sl.busy) { set_error("idn_submit_u8hwc: three submissions are already in flight; collect one first"); return IDN_EINVAL; }
   IDN_TRY(slot_setup(h, sl));
   int64_t lo = offsets[0], hi = 0;
   for (int i = 0; i < n; ++i) {
@@ -886,22 +892,24 @@ int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, 
     sl.d_stage_cap = bytes + 64;
   }
   // copy stream: the image bytes; the handle's stream: everything else, after the copy has landed
+  // ... and the per-image records, so that nothing of this batch is left to fetch from the host when
+  // the kernels of the previous batch finish
   IDN_CUDA_TRY(cudaMemcpyAsync(sl.d_stage, imgs + lo, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+  IDN_TRY(fill_meta(h, offsets, hw, n, lo, sl.h_meta, sl.d_meta, h->copy_stream));
   IDN_CUDA_TRY(cudaEventRecord(sl.ev_copied, h->copy_stream));
   IDN_CUDA_TRY(cudaStreamWaitEvent(h->stream, sl.ev_copied, 0));
-  IDN_TRY(fill_meta(h, offsets, hw, n, lo, sl.h_meta));
   // The softmax/top-1 kernel stores its 8 bytes per image straight into the slot's page-locked host
   // buffers (device-visible under unified addressing): no device-to-host copy to queue anywhere.
-  IDN_TRY(run_plan(h, sl.d_stage, n, sl.h_idx, sl.h_prob, want_logits ? sl.d_logits : nullptr));
+  IDN_TRY(run_plan(h, sl.d_stage, n, sl.h_idx, sl.h_prob, want_logits ? sl.d_logits : nullptr, sl.d_meta));
   IDN_CUDA_TRY(cudaEventRecord(sl.ev_done, h->stream));
   sl.n = n; sl.busy = true; sl.logits = want_logits != 0;
   *ticket = b;
-  h->next_slot = b ^ 1;
+  h->next_slot = (b + 1) % kSlots;
   return IDN_OK;
 }
 
 int idn_collect(idn_handle h, int ticket, int32_t* top1_idx, float* top1_prob, float* logits) {
-  if (!h || ticket < 0 || ticket > 1 || !top1_idx || !top1_prob || !h->slot[ticket].busy) {
+  if (!h || ticket < 0 || ticket >= kSlots || !top1_idx || !top1_prob || !h->slot[ticket].busy) {
     set_error("idn_collect: bad ticket or argument");
     return IDN_EINVAL;
   }
@@ -924,27 +932,33 @@ int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, c
     set_error("idn_infer_u8hwc: bad argument");
     return IDN_EINVAL;
   }
-  if (h->slot[0].busy || h->slot[1].busy) { set_error("idn_infer_u8hwc: collect pending submissions first"); return IDN_EINVAL; }
-  // tensor batches of max_batch images, two in flight: the copy of batch k+1 overlaps the kernels of k
-  int prev_ticket = -1, prev_i0 = 0;
-  for (int i0 = 0; i0 < n; i0 += h->cap) {
+  for (int b = 0; b < kSlots; ++b)
+    if (h->slot[b].busy) { set_error("idn_infer_u8hwc: collect pending submissions first"); return IDN_EINVAL; }
+  // tensor batches of max_batch images, up to kSlots in flight: the copies of the next batches overlap
+  // the kernels of the current one
+  int tickets[kSlots], first[kSlots], head = 0, count = 0;
+  auto collect_oldest = [&]() {
+    const int i0 = first[head];
+    const int rc = idn_collect(h, tickets[head], top1_idx + i0, top1_prob + i0,
+                               logits ? logits + (size_t)i0 * IDN_NUM_CLASSES : nullptr);
+    head = (head + 1) % kSlots; --count;
+    return rc;
+  };
+  int rc = IDN_OK;
+  for (int i0 = 0; i0 < n && rc == IDN_OK; i0 += h->cap) {
+    if (count == kSlots) rc = collect_oldest();
+    if (rc != IDN_OK) break;
     const int m = std::min(h->cap, n - i0);
-    int ticket = -1;
-    int rc = idn_submit_u8hwc(h, imgs, offsets + i0, hw + 2 * i0, m, logits != nullptr, &ticket);
-    if (rc == IDN_OK && prev_ticket >= 0)
-      rc = idn_collect(h, prev_ticket, top1_idx + prev_i0, top1_prob + prev_i0,
-                       logits ? logits + (size_t)prev_i0 * IDN_NUM_CLASSES : nullptr);
-    if (rc != IDN_OK) {                         // drain so that the handle stays usable
-      cudaStreamSynchronize(h->stream);
-      h->slot[0].busy = h->slot[1].busy = false;
-      return rc;
-    }
-    prev_ticket = ticket; prev_i0 = i0;
+    const int at = (head + count) % kSlots;
+    rc = idn_submit_u8hwc(h, imgs, offsets + i0, hw + 2 * i0, m, logits != nullptr, &tickets[at]);
+    if (rc == IDN_OK) { first[at] = i0; ++count; }
   }
-  if (prev_ticket >= 0)
-    return idn_collect(h, prev_ticket, top1_idx + prev_i0, top1_prob + prev_i0,
-                       logits ? logits + (size_t)prev_i0 * IDN_NUM_CLASSES : nullptr);
-  return IDN_OK;
+  while (rc == IDN_OK && count > 0) rc = collect_oldest();
+  if (rc != IDN_OK) {                           // drain so that the handle stays usable
+    cudaStreamSynchronize(h->stream);
+    for (int b = 0; b < kSlots; ++b) h->slot[b].busy = false;
+  }
+  return rc;
 }
 
 int idn_preprocess_u8hwc(int device, const uint8_t* imgs, const int64_t* offsets, const int32_t* hw,

@@ -296,9 +296,9 @@ class SyntheticImageSet:
 
 def gpu_classifier(device: int, max_batch: int = 400, seed: int = 0, variant: str = "default"):
     """classify(model, start, end[, between_batches]) over the synthetic set, tensor batches of
-    ``max_batch`` images, two batches in flight (copy of k+1 under the kernels of k).  Engines are
+    ``max_batch`` images, up to three batches in flight (copies of k+1, k+2 under the kernels of k).  Engines are
     built on first use per model and stay resident, as in the drop-in ``deeplearning``."""
-    from .engine import Engine
+    from .engine import Engine, MAX_IN_FLIGHT
     from .synth import make_state_dict
     images = SyntheticImageSet(max_batch, device)
     engines = {}
@@ -318,7 +318,7 @@ def gpu_classifier(device: int, max_batch: int = 400, seed: int = 0, variant: st
         pending = []                                        # (ticket, position)
         pos, batches = 0, 0
         while pos < total or pending:
-            while pos < total and len(pending) < 2:
+            while pos < total and len(pending) < MAX_IN_FLIGHT:
                 n = min(max_batch, total - pos)
                 ptr, offsets, hw = images.window(start + pos, n)
                 pending.append((eng.submit_packed(offsets, hw, ptr), pos, n))

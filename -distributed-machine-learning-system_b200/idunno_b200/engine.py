@@ -34,6 +34,9 @@ def pack_images(images):
     return packed, offsets, hw
 
 
+MAX_IN_FLIGHT = 3          # IDN_MAX_IN_FLIGHT in include/idunno_b200.h
+
+
 class Engine:
     def __init__(self, modelname: str, state_dict, device: int = 0, max_batch: int = 400,
                  impl: str = "tc"):
@@ -102,7 +105,7 @@ class Engine:
 
     def submit_packed(self, offsets: np.ndarray, hw: np.ndarray, packed_ptr: int, want_logits: bool = False):
         """Enqueue one tensor batch (host buffer at ``packed_ptr``, best pinned; it must stay alive until
-        ``collect``).  Returns a ticket; at most two submissions may be in flight."""
+        ``collect``).  Returns a ticket; at most ``MAX_IN_FLIGHT`` (3) submissions may be in flight."""
         n = int(offsets.shape[0])
         t = C.c_int(-1)
         hw32 = np.ascontiguousarray(hw, dtype=np.int32)

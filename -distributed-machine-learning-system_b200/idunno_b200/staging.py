@@ -104,10 +104,10 @@ def stage_chunk(files, buf_for, pool):
 def classify_range(eng, filename: str, start_image, end_image, threads: int = 8, device: int = 0):
     """Folder range -> (indices, top1_idx, top1_prob), tensor batches of ``eng.max_batch`` files.
     While the GPU works on batch k (and the DMA engine copies it), the host threads decode batch
-    k+1 into the next pinned buffer; three buffers rotate (two submissions in flight + one being
+    k+1 into the next pinned buffer; four buffers rotate (three submissions in flight + one being
     filled, kept on the engine between calls).  Missing files are skipped exactly like the reference does."""
     from concurrent.futures import ThreadPoolExecutor
-    from .engine import PinnedBuffer
+    from .engine import MAX_IN_FLIGHT, PinnedBuffer
     files = discover(filename, start_image, end_image)
     n = len(files)
     indices = np.asarray([f[0] for f in files], dtype=np.int64)
@@ -116,7 +116,7 @@ def classify_range(eng, filename: str, start_image, end_image, threads: int = 8,
     if n == 0:
         return indices, idx, prob
     if not hasattr(eng, "_stage_ring"):               # page-locked memory is slow to allocate: keep it
-        eng._stage_ring = [None, None, None]
+        eng._stage_ring = [None] * (MAX_IN_FLIGHT + 1)
     ring = eng._stage_ring
 
     def buf_for(slot):
@@ -133,9 +133,9 @@ def classify_range(eng, filename: str, start_image, end_image, threads: int = 8,
     pending = []                                      # (ticket, first position, chunk)
     with ThreadPoolExecutor(max_workers=threads) as pool:
         for k, chunk_files in enumerate(chunks):
-            # slot k%3 last held chunk k-3, which was collected before chunk k-1 was submitted
-            c = stage_chunk(chunk_files, buf_for(k % 3), pool)
-            if len(pending) == 2:
+            # this buffer last held chunk k-4, which was collected before chunk k-1 was submitted
+            c = stage_chunk(chunk_files, buf_for(k % (MAX_IN_FLIGHT + 1)), pool)
+            if len(pending) == MAX_IN_FLIGHT:
                 t, at, _c = pending.pop(0)
                 i, p, _ = eng.collect(t)
                 idx[at:at + len(i)], prob[at:at + len(i)] = i, p

@@ -80,7 +80,8 @@ int idn_set_impl(idn_handle h, int impl);
  *   top1_prob[n]: softmax probability of that class, fp32
  *   logits      : optional [n][1000] fp32 (NULL to skip)
  * Host buffers in and out: the call copies inputs to the device, runs, copies results back and
- * returns after they have arrived. */
+ * returns after they have arrived.  Inputs longer than max_batch are processed as tensor batches of
+ * max_batch images with up to IDN_MAX_IN_FLIGHT of them in flight (see idn_submit_u8hwc). */
 int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* offsets,
                     const int32_t* hw, int n, int32_t* top1_idx, float* top1_prob, float* logits);
 
@@ -88,10 +89,13 @@ int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* off
  * reference's worker loop decodes and classifies strictly one image after the other,
  * alexnet_resnet.py:48-90).  idn_submit_u8hwc enqueues the H2D copy of one tensor batch
  * (n <= max_batch) on a copy stream and the kernels on the handle's stream and returns at once;
- * idn_collect blocks until that batch is done and copies the results out.  At most two submissions
- * may be in flight, so the copy of batch k+1 overlaps the kernels of batch k; idn_infer_u8hwc uses
- * exactly this for inputs longer than max_batch.  The image buffer must stay valid (and is best
+ * idn_collect blocks until that batch is done and copies the results out.  At most
+ * IDN_MAX_IN_FLIGHT submissions may be in flight (each owns a staging buffer of the batch's size on
+ * the device), so the copies of the next batches overlap the kernels of the current one and the copy
+ * engine never waits for the host to come back from idn_collect; idn_infer_u8hwc uses exactly this
+ * for inputs longer than max_batch.  The image buffer must stay valid (and is best
  * pinned) until the batch has been collected.  ticket identifies the submission. */
+#define IDN_MAX_IN_FLIGHT 3
 int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* offsets,
                      const int32_t* hw, int n, int want_logits, int* ticket);
 int idn_collect(idn_handle h, int ticket, int32_t* top1_idx, float* top1_prob, float* logits);

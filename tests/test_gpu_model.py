@@ -200,8 +200,8 @@ def test_deeplearning_dropin_matches_oracle(built_library, tmp_path, monkeypatch
 
 
 def test_submit_collect_overlaps_and_matches_infer(built_library):
-    """idn_submit_u8hwc / idn_collect: two tensor batches in flight give the same results as the
-    one-call form, a third submission is refused, and long inputs (which use the same slots inside
+    """idn_submit_u8hwc / idn_collect: tensor batches in flight give the same results as the
+    one-call form, a fourth submission is refused, and long inputs (which use the same slots inside
     idn_infer_u8hwc) come back in order."""
     import torch
     from idunno_b200 import IdunnoError
@@ -215,13 +215,16 @@ def test_submit_collect_overlaps_and_matches_infer(built_library):
         pk_b, off_b, hw_b = pack_images(b)
         ta = eng.submit_packed(off_a, hw_a, pk_a.ctypes.data, want_logits=True)
         tb = eng.submit_packed(off_b, hw_b, pk_b.ctypes.data)
-        with pytest.raises(IdunnoError):
+        tc = eng.submit_packed(off_a, hw_a, pk_a.ctypes.data)
+        with pytest.raises(IdunnoError):                     # IDN_MAX_IN_FLIGHT = 3
             eng.submit_packed(off_b, hw_b, pk_b.ctypes.data)
         ga = eng.collect(ta)
         gb = eng.collect(tb)
+        gc = eng.collect(tc)
+        assert np.array_equal(gc[0], ia) and np.array_equal(gc[1], pa)
         assert np.array_equal(ga[0], ia) and np.array_equal(ga[1], pa) and np.array_equal(ga[2], la)
         assert np.array_equal(gb[0], ib) and np.array_equal(gb[1], pb) and gb[2] is None
-        many = a + b + a + b + a                    # 37 images through a 12-image engine: 4 batches
+        many = a + b + a + b + a + b + a             # 51 images through a 12-image engine: 5 batches
         im, pm, _ = eng.infer(many)
-        assert np.array_equal(im, np.concatenate([ia, ib, ia, ib, ia]))
-        assert np.array_equal(pm, np.concatenate([pa, pb, pa, pb, pa]))
+        assert np.array_equal(im, np.concatenate([ia, ib, ia, ib, ia, ib, ia]))
+        assert np.array_equal(pm, np.concatenate([pa, pb, pa, pb, pa, pb, pa]))

@@ -1,4 +1,9 @@
-"""Does a pinned host->device copy slow down while the inference kernels run (and the other way round)?
+"""NOTE: superseded by tools/diag_overlap_steps.py and tools/diag_e2e_timing.py.  The "overlapped" copy
+time printed here includes the time the host needs to enqueue the kernel passes (the engine lets the host
+run at most 4 passes ahead), so it overstates the slowdown; kept because its FIRST result -- kernels twice
+as slow under a copy -- is what exposed the small per-batch cudaMemcpyAsync queued behind the image copy.
+
+Does a pinned host->device copy slow down while the inference kernels run (and the other way round)?
 Times, with CUDA events: (1) a 60 MB H2D copy alone, (2) a 400-image device-resident pass alone,
 (3) both at once on different streams.  Prints one JSON object."""
 import json

@@ -133,6 +133,10 @@ struct ConvParams {
   int msub;                   // 128-row sub-tiles per work item (1 or 2)
   FastDiv fd_img_rows, fd_wp, fd_per_img, fd_tiles_w;   // row decode without integer division
   int profile;                // 1: book pipeline-wait cycles per role (bench.py timing mode)
+  // stem only: 3x3 stride-2 pad-1 max-pool fused into the epilogue (ResNet18 conv1 -> maxpool).  The
+  // conv output is not stored; partial window maxima go to pool_out (zeroed beforehand) with red.max.
+  bf16* pool_out;             // nullptr: plain stem
+  int pool_img_rows, pool_wp, pool_oh, pool_ow;
 };
 
 // launchers (conv_tc.cu / conv_simt.cu)
@@ -183,7 +187,8 @@ struct PreMeta {            // one per image, device resident
 enum { PRE_OUT_NCHW = 0, PRE_OUT_STEM = 1, PRE_OUT_S2D4 = 2 };
 int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
-                      int stem_ws, int raw_words, int src_rows, cudaStream_t st);
+                      int stem_ws, int raw_words, int src_rows, cudaStream_t st,
+                      void* zero_ptr = nullptr, size_t zero_bytes_per_img = 0);
 void preprocess_tile_need(const int* htab, const int* vtab, int* raw_words, int* src_rows);
 // Builds the resample table (Pillow fixed point) of the 224 cropped outputs of one axis.
 void build_axis_table(int in_size, int out_size, int crop_off, std::string* ints /* int32 bytes */);

@@ -117,6 +117,13 @@ struct idn_engine {
   bool timing = false;
   bool wait_profile = false;  // timing mode 2: also book per-role pipeline waits (slower kernels)
   int stop_after = -1;      // diagnostic: run the plan up to and including this step
+  // ResNet18: conv1 and the max-pool behind it run as ONE kernel on the product path (the pool is folded
+  // into the stem's epilogue with red.max into a buffer that the preprocess kernel of the same pass has
+  // cleared on the side).
+  int fuse_stem_step = -1, fuse_pool_step = -1, pool_last_reader = -1;
+  bf16* pool_buf = nullptr; size_t pool_img_bytes = 0;
+  int pool_img_rows = 0, pool_wp = 0;
+  bool no_pool_fusion = false;
   int last_n = 0;
 };
 
@@ -402,6 +409,9 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
   Act a, t, o;       // block input, mid, block output (same geometry)
   IDN_TRY(alloc_act(e, &a, make_geom(56, 56, 1), 64, cap));
   add_pool(e, "maxpool", s1, a, 1);
+  e->fuse_stem_step = (int)e->steps.size() - 2; e->fuse_pool_step = (int)e->steps.size() - 1;
+  e->pool_buf = a.ptr; e->pool_img_rows = a.g.img_rows(); e->pool_wp = a.g.Wp;
+  e->pool_img_bytes = (size_t)a.g.img_rows() * 64 * sizeof(bf16);
   Act planes;        // parity planes feeding the next stage
   for (int li = 0; li < 4; ++li) {
     const int C = chans[li];
@@ -420,6 +430,7 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
       IDN_TRY(add_conv(e, L + ".0.conv1", a, w1, c3r, t, nullptr, cap));
       IDN_TRY(conv_bn(&w2, C, C, 3, false));
       IDN_TRY(add_conv(e, L + ".0.conv2+add", t, w2, c3r, o, &a, cap));
+      e->pool_last_reader = (int)e->steps.size() - 1;
     } else {
       Act d; IDN_TRY(alloc_act(e, &d, g, C, cap));
       if (last) IDN_TRY(alloc_act(e, &a, g, C, cap));
@@ -648,9 +659,12 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
   if (d_meta == nullptr) d_meta = e->d_meta;
   cudaStream_t st = e->stream;
   e->last_n = n;
+  const bool fuse = e->fuse_stem_step >= 0 && e->impl == IDN_IMPL_TC && !e->stem_simt && !e->no_pool_fusion &&
+                    e->stop_after != e->fuse_stem_step;      // a tap of conv1 itself needs the plain stem
   int step_no = 0;
   for (Step& s : e->steps) {
     if (e->stop_after >= 0 && step_no > e->stop_after) break;
+    const int step_idx = step_no;
     ++step_no;
     if (e->timing) {
       if (!s.ev0) { IDN_CUDA_TRY(cudaEventCreate(&s.ev0)); IDN_CUDA_TRY(cudaEventCreate(&s.ev1)); }
@@ -659,12 +673,18 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     switch (s.kind) {
       case STEP_PRE:
         IDN_TRY(launch_preprocess(d_imgs, d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
-                                  e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st));
+                                  e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st,
+                                  fuse ? e->pool_buf : nullptr, fuse ? e->pool_img_bytes : 0));
         break;
       case STEP_CONV:
+        if (step_idx == e->fuse_stem_step) {
+          s.cp.pool_out = fuse ? e->pool_buf : nullptr;
+          s.cp.pool_img_rows = e->pool_img_rows; s.cp.pool_wp = e->pool_wp;
+        }
         IDN_TRY(launch_conv_step(e, s, n, e->impl, st));
         break;
       case STEP_POOL:
+        if (fuse && step_idx == e->fuse_pool_step) { e->launches -= 1; break; }   // done by the stem's epilogue
         s.pp.nimg = n;
         IDN_TRY(launch_maxpool(s.pp, st));
         break;
@@ -789,6 +809,7 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   std::unique_ptr<idn_engine> e(new idn_engine());
   e->device = device; e->model = model_id; e->cap = max_batch;
   { const char* v = std::getenv("IDN_STEM_SIMT"); e->stem_simt = v && v[0] == '1'; }
+  { const char* v = std::getenv("IDN_NO_POOL_FUSION"); e->no_pool_fusion = v && v[0] == '1'; }
   int rc = IDN_OK;
   auto fail = [&](int code) { idn_engine* raw = e.release(); idn_destroy(raw); return code; };
   {

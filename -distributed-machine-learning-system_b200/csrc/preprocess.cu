@@ -144,7 +144,19 @@ template <int OUT_MODE>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ meta,
                   const int* __restrict__ tables, const uint16_t* __restrict__ lut, void* out,
-                  int left_pad, int ws, int raw_cap_words, int src_rows_cap) {
+                  int left_pad, int ws, int raw_cap_words, int src_rows_cap,
+                  uint4* __restrict__ zero_ptr, int zero_vec_per_img) {
+  // Optional side job: clear this image's slice of a buffer a later kernel accumulates into with
+  // red.max (the pooled ResNet stem output).  This kernel is bound by instruction issue, its store
+  // path is idle, so the 415 KB per image ride along for free; stream order keeps them behind the
+  // previous pass's readers.
+  if (zero_ptr != nullptr) {
+    const int per_cta = (zero_vec_per_img + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int lo = per_cta * (int)blockIdx.x;
+    const int hi = min(lo + per_cta, zero_vec_per_img);
+    uint4* zp = zero_ptr + (long long)blockIdx.y * zero_vec_per_img;
+    for (int i = lo + (int)threadIdx.x; i < hi; i += (int)blockDim.x) zp[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
   extern __shared__ uint32_t sm[];
   uint32_t* s_raw = sm;                                        // staged source bytes
   uint32_t* s_h = sm + raw_cap_words;                          // [src rows][224] RGBx after pass 1
@@ -340,7 +352,14 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
 
 int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
-                      int stem_ws, int raw_words, int src_rows, cudaStream_t st) {
+                      int stem_ws, int raw_words, int src_rows, cudaStream_t st,
+                      void* zero_ptr, size_t zero_bytes_per_img) {
+  uint4* zp = static_cast<uint4*>(zero_ptr);
+  const int zv = (int)(zero_bytes_per_img / 16);
+  if (zp != nullptr && (zero_bytes_per_img % 16 != 0 || (reinterpret_cast<uintptr_t>(zp) & 15) != 0)) {
+    set_error("preprocess: the buffer to clear must be 16-byte aligned");
+    return IDN_EINVAL;
+  }
   if (n <= 0) return IDN_OK;
   if (out_mode == PRE_OUT_STEM && stem_ws - IDN_CROP > 32) {
     set_error("preprocess: stem row pitch too wide");
@@ -354,15 +373,15 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
   if (out_mode == PRE_OUT_NCHW) {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_NCHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     preprocess_kernel<PRE_OUT_NCHW><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap);
+        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap, zp, zv);
   } else if (out_mode == PRE_OUT_STEM) {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_STEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     preprocess_kernel<PRE_OUT_STEM><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap);
+        d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap, zp, zv);
   } else {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, smem, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap);
+        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap, zp, zv);
   }
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;

@@ -228,3 +228,21 @@ def test_submit_collect_overlaps_and_matches_infer(built_library):
         im, pm, _ = eng.infer(many)
         assert np.array_equal(im, np.concatenate([ia, ib, ia, ib, ia, ib, ia]))
         assert np.array_equal(pm, np.concatenate([pa, pb, pa, pb, pa, pb, pa]))
+
+
+def test_resnet_stem_pool_fusion_is_bit_identical(built_library, monkeypatch):
+    """The product path folds ResNet18's max-pool into the stem's epilogue (partial window maxima with
+    red.max into a zeroed buffer); IDN_NO_POOL_FUSION=1 keeps the two kernels.  max is exact and order
+    independent, so logits must be identical bit for bit -- also across repeated passes (the pooled
+    buffer is re-zeroed on a side stream every pass) and for a ragged batch."""
+    sd = make_state_dict("resnet18", 0, "stress")
+    imgs = [synth_image(i, mixed=True) for i in range(21)]
+    with Engine("resnet18", sd, max_batch=16) as eng:
+        i1, p1, l1 = eng.infer(imgs, want_logits=True)          # two tensor batches: 16 + 5
+        i2, p2, l2 = eng.infer(imgs[:7], want_logits=True)
+        i3, p3, l3 = eng.infer(imgs, want_logits=True)
+    monkeypatch.setenv("IDN_NO_POOL_FUSION", "1")
+    with Engine("resnet18", sd, max_batch=16) as eng:
+        j1, q1, m1 = eng.infer(imgs, want_logits=True)
+    assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
+    assert np.array_equal(l3, l1) and np.array_equal(l2, l1[:7])

@@ -527,6 +527,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
   constexpr int B_BYTES = BLOCK_N * kBlockK * 2;
+  constexpr int G = (!BRES && TAPS > 0) ? TAPS : 1;    // streamed weights: filter taps per weight stage (== p.b_group)
   constexpr int ACC_COLS = MSUB * BLOCK_N;
   constexpr int TMEM_COLS = 2 * ACC_COLS <= 128 ? 128 : 2 * ACC_COLS <= 256 ? 256 : 512;
   static_assert(2 * ACC_COLS <= 512, "accumulators exceed TMEM");
@@ -536,7 +537,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   const int k_total = p.num_taps * p.c_blocks;
   const uint32_t a_base = base;
   const uint32_t b_base = a_base + (uint32_t)(p.a_stages * p.a_stage_bytes);
-  const uint32_t bar_base = b_base + (uint32_t)((BRES ? k_total : p.b_stages) * B_BYTES);
+  const uint32_t bar_base = b_base + (uint32_t)((BRES ? k_total : p.b_stages * G) * B_BYTES);
   auto a_full = [&](int s) { return bar_base + 8u * s; };
   auto a_empty = [&](int s) { return bar_base + 8u * (kMaxAStages + s); };
   auto b_full = [&](int s) { return bar_base + 8u * (2 * kMaxAStages + s); };
@@ -607,11 +608,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
           const int n_tile = item % p.num_n_tiles;
           for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
-            for (int tap = 0; tap < p.num_taps; ++tap) {
+            for (int tap = 0; tap < p.num_taps; tap += G) {
               if (!mbar_wait(b_empty(sb), phb ^ 1u, 4, tap, p.profile)) { alive = false; break; }
-              ptx::mbar_expect_tx(b_full(sb), B_BYTES);
-              ptx::tma_load_2d(b_base + (uint32_t)(sb * B_BYTES), &tmB, b_full(sb),
-                               (tap * p.c_blocks + cb) * kBlockK, n_tile * BLOCK_N);
+              ptx::mbar_expect_tx(b_full(sb), (uint32_t)(G * B_BYTES));
+#pragma unroll
+              for (int g = 0; g < G; ++g)
+                ptx::tma_load_2d(b_base + (uint32_t)((sb * G + g) * B_BYTES), &tmB, b_full(sb),
+                                 ((tap + g) * p.c_blocks + cb) * kBlockK, n_tile * BLOCK_N);
               if (++sb == p.b_stages) { sb = 0; phb ^= 1u; }
             }
           }
@@ -655,20 +658,24 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           }
           __syncwarp();
         } else {
-          for (int tap = 0; tap < p.num_taps; ++tap) {
-            if (!mbar_wait(b_full(sb), phb, 6, tap, p.profile)) { alive = false; break; }
+          for (int tap0 = 0; tap0 < p.num_taps; tap0 += G) {
+            if (!mbar_wait(b_full(sb), phb, 6, tap0, p.profile)) { alive = false; break; }
             ptx::tc_fence_after();
-            const uint32_t b_tile = b_base + (uint32_t)(sb * B_BYTES);
+            const uint32_t b_stage = b_base + (uint32_t)(sb * G * B_BYTES);
             if (ptx::elect_one()) {
-              const uint64_t db = make_sw128_desc(b_tile);
-              const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
 #pragma unroll
-              for (int sub = 0; sub < MSUB; ++sub) {
-                const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+              for (int g = 0; g < G; ++g) {
+                const int tap = tap0 + g;
+                const uint64_t db = make_sw128_desc(b_stage + (uint32_t)(g * B_BYTES));
+                const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
 #pragma unroll
-                for (int k = 0; k < kBlockK / 16; ++k)
-                  ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
-                                 db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+                for (int sub = 0; sub < MSUB; ++sub) {
+                  const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+#pragma unroll
+                  for (int k = 0; k < kBlockK / 16; ++k)
+                    ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
+                                   db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+                }
               }
               ptx::umma_commit(b_empty(sb));
             }
@@ -1128,7 +1135,11 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   p->halo_r1 = total_rows <= 256 ? total_rows : 256;
   p->halo_r2 = total_rows - p->halo_r1;
   p->a_stage_bytes = (total_rows * 128 + 1023) / 1024 * 1024;
-  const int b_bytes = bn * 128;
+  // Streamed weights: at N = 128 one tap is only 8 MMAs x 64 cycles, less than the MMA warp needs for a
+  // barrier round-trip, so three taps share a stage (measured: tensor pipe 53 % -> see profiles/).
+  p->b_group = (!res && bn == 128 && msub == 2 && p->num_taps % 3 == 0) ? 3 : 1;
+  if (const char* v = std::getenv("IDN_HALO_BGROUP")) { if (v[0] == '1') p->b_group = 1; }
+  const int b_bytes = bn * 128 * p->b_group;
   if (res) {
     const int left = kSmemBudget - k_total * b_bytes;
     p->a_stages = std::min(kMaxAStages, left / p->a_stage_bytes);
@@ -1139,6 +1150,10 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
     int left = kSmemBudget - p->a_stages * p->a_stage_bytes;
     if (left / b_bytes < 4) { p->a_stages = 2; left = kSmemBudget - 2 * p->a_stage_bytes; }
     p->b_stages = std::min(kMaxBStages, left / b_bytes);
+    if (p->b_stages < 3 && p->b_group > 1) {            // not enough room for grouped stages: one tap each
+      p->b_group = 1;
+      p->b_stages = std::min(kMaxBStages, left / (bn * 128));
+    }
     if (p->b_stages < 3) return false;
   }
   (void)m_rows_cap; (void)num_sms;
@@ -1153,7 +1168,7 @@ static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
   const int total = p.num_m_tiles * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   const int k_total = p.num_taps * p.c_blocks;
-  const int smem = p.a_stages * p.a_stage_bytes + (BRES ? k_total : p.b_stages) * BLOCK_N * 128 + 1024 + 1024;
+  const int smem = p.a_stages * p.a_stage_bytes + (BRES ? k_total : p.b_stages * p.b_group) * BLOCK_N * 128 + 1024 + 1024;
   static int configured_smem[64] = {0};       // per device: cudaFuncSetAttribute costs tens of microseconds
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1174,9 +1189,11 @@ int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUt
     if (p.num_taps == 9) return launch_halo_one<64, 2, true, 9>(tmA1, tmA2, tmB, p, num_sms, st);
     return launch_halo_one<64, 2, true, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   }
-  if (!b_resident && p.msub == 2 && block_n == 128)
-    return launch_halo_one<128, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
-  if (!b_resident && p.msub == 1) {
+  if (!b_resident && p.msub == 2 && block_n == 128) {
+    if (p.b_group == 3) return launch_halo_one<128, 2, false, 3>(tmA1, tmA2, tmB, p, num_sms, st);
+    if (p.b_group == 1) return launch_halo_one<128, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
+  }
+  if (!b_resident && p.msub == 1 && p.b_group == 1) {
     if (block_n == 128) return launch_halo_one<128, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
     if (block_n == 192) return launch_halo_one<192, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
     if (block_n == 256) return launch_halo_one<256, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);

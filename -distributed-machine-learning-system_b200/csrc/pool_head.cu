@@ -56,13 +56,27 @@ int launch_maxpool(const PoolParams& p, cudaStream_t st) {
 // ------------------------------------------------------------------------- softmax / top-1 tail
 // Warp-level: max + first argmax, then sum of exp(l - max); top-1 probability = 1 / sum.
 // Replaces softmax + topk(.,1) of alexnet_resnet.py:80-84; exact ties -> lowest class index.
+// The 1000 logits of an image sit in registers (8 float4 per lane, all loads issued before the first use),
+// so the row is read once and the two passes cost one memory latency instead of ~60.
 __device__ __forceinline__ void warp_softmax_top1(const float* logits, int lane, int32_t* idx_out,
-                                                  float* prob_out) {
+                                                  float* prob_out, float* copy_out) {
+  constexpr int kVec = IDN_NUM_CLASSES / 4;          // 250 float4
+  float4 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int q = lane + 32 * i;
+    v[i] = q < kVec ? __ldg(reinterpret_cast<const float4*>(logits) + q)
+                    : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+  }
   float best = -INFINITY;
   int best_i = 0x7fffffff;
-  for (int j = lane; j < IDN_NUM_CLASSES; j += 32) {
-    const float v = logits[j];
-    if (v > best) { best = v; best_i = j; }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {                        // ascending index within the lane: '>' keeps the first
+    const int j = 4 * (lane + 32 * i);
+    if (v[i].x > best) { best = v[i].x; best_i = j; }
+    if (v[i].y > best) { best = v[i].y; best_i = j + 1; }
+    if (v[i].z > best) { best = v[i].z; best_i = j + 2; }
+    if (v[i].w > best) { best = v[i].w; best_i = j + 3; }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -71,33 +85,42 @@ __device__ __forceinline__ void warp_softmax_top1(const float* logits, int lane,
     if (ob > best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
   }
   float sum = 0.0f;
-  for (int j = lane; j < IDN_NUM_CLASSES; j += 32) sum += expf(logits[j] - best);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {                        // expf(-inf) = 0 for the padding lanes
+    sum += expf(v[i].x - best); sum += expf(v[i].y - best);
+    sum += expf(v[i].z - best); sum += expf(v[i].w - best);
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (copy_out != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int q = lane + 32 * i;
+      if (q < kVec) reinterpret_cast<float4*>(copy_out)[q] = v[i];
+    }
+  }
   if (lane == 0) {
     *idx_out = best_i;
     *prob_out = 1.0f / sum;
   }
 }
 
-__global__ void __launch_bounds__(256) softmax_top1_kernel(const float* __restrict__ logits, int ld,
+__global__ void __launch_bounds__(128) softmax_top1_kernel(const float* __restrict__ logits, int ld,
                                                            int nimg, float* __restrict__ logits_out,
                                                            int32_t* __restrict__ idx,
                                                            float* __restrict__ prob) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nimg) return;
-  const float* l = logits + (long long)warp * ld;
-  if (logits_out != nullptr)
-    for (int j = lane; j < IDN_NUM_CLASSES; j += 32)
-      logits_out[(long long)warp * IDN_NUM_CLASSES + j] = l[j];
-  warp_softmax_top1(l, lane, idx + warp, prob + warp);
+  const float* l = logits + (long long)warp * ld;       // ld % 4 == 0: rows are float4-aligned
+  warp_softmax_top1(l, lane, idx + warp, prob + warp,
+                    logits_out != nullptr ? logits_out + (long long)warp * IDN_NUM_CLASSES : nullptr);
 }
 
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out, int32_t* idx,
                         float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  softmax_top1_kernel<<<(nimg + 7) / 8, 256, 0, st>>>(logits, ld, nimg, logits_out, idx, prob);
+  softmax_top1_kernel<<<(nimg + 3) / 4, 128, 0, st>>>(logits, ld, nimg, logits_out, idx, prob);
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }
@@ -143,52 +166,60 @@ avgpool_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int
 
 // grid = (ceil(n / 16), 8): a CTA stages the features of 16 images in shared memory and computes
 // 125 of the 1000 classes for them; a warp owns two classes at a time, lanes split K with 128-bit loads.
-constexpr int kHeadImgs = 16;
-constexpr int kHeadChunks = 8;
-constexpr int kHeadClassesPerChunk = IDN_NUM_CLASSES / kHeadChunks;   // 125
+// logits[n][j] = bias[j] + sum_c feats[n][c] * fc_w[j][c], fp32, c ascending (deterministic).  A
+// register-tiled SIMT GEMM: 64 images x 64 classes per CTA, 4 x 4 outputs per thread, K in slabs of 32
+// staged k-major in shared memory, so one k step costs a thread two 128-bit shared loads for 16 FMAs
+// (the earlier warp-per-class kernel issued sixteen and was bound by the shared-memory pipe).
+constexpr int kFcTile = 64, kFcK = 32;
 
 __global__ void __launch_bounds__(256)
 fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __restrict__ fc_w,
                const float* __restrict__ fc_b, float* __restrict__ logits) {
-  extern __shared__ float feat[];             // [kHeadImgs][C]
-  const int n0 = blockIdx.x * kHeadImgs;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int valid = min(kHeadImgs, nimg - n0);
-  for (int e = threadIdx.x; e < kHeadImgs * C / 4; e += blockDim.x) {
-    const int g = (e * 4) / C;
-    reinterpret_cast<float4*>(feat)[e] =
-        g < valid ? __ldg(reinterpret_cast<const float4*>(feats + (long long)n0 * C) + e)
-                  : make_float4(0.f, 0.f, 0.f, 0.f);
+  __shared__ __align__(16) float As[kFcK][kFcTile + 4];     // [k][image]
+  __shared__ __align__(16) float Bs[kFcK][kFcTile + 4];     // [k][class]
+  const int m0 = blockIdx.x * kFcTile, n0 = blockIdx.y * kFcTile;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+  for (int k0 = 0; k0 < C; k0 += kFcK) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int idx = threadIdx.x + 256 * j;
+      const int row = idx & 63, kq = (idx >> 6) * 4;
+      const int m = m0 + row, n = n0 + row;
+      const float4 a = m < nimg ? __ldg(reinterpret_cast<const float4*>(feats + (long long)m * C + k0 + kq))
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 b = n < IDN_NUM_CLASSES ? __ldg(reinterpret_cast<const float4*>(fc_w + (long long)n * C + k0 + kq))
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+      As[kq + 0][row] = a.x; As[kq + 1][row] = a.y; As[kq + 2][row] = a.z; As[kq + 3][row] = a.w;
+      Bs[kq + 0][row] = b.x; Bs[kq + 1][row] = b.y; Bs[kq + 2][row] = b.z; Bs[kq + 3][row] = b.w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kFcK; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
   }
-  __syncthreads();
-  const int j0 = blockIdx.y * kHeadClassesPerChunk;
-  for (int jj = warp; jj < kHeadClassesPerChunk; jj += 8) {
-    const int j = j0 + jj;
-    float acc[kHeadImgs];
+  const int n = n0 + tx * 4;
+  if (n < IDN_NUM_CLASSES) {                         // 1000 = 15 full tiles + 40: whole float4s either way
+    const float4 bias = __ldg(reinterpret_cast<const float4*>(fc_b + n));
 #pragma unroll
-    for (int g = 0; g < kHeadImgs; ++g) acc[g] = 0.0f;
-    const float* wr = fc_w + (long long)j * C;
-#pragma unroll 4
-    for (int c = lane * 4; c < C; c += 128) {
-      const float4 w4 = __ldg(reinterpret_cast<const float4*>(wr + c));
-#pragma unroll
-      for (int g = 0; g < kHeadImgs; ++g) {
-        const float4 f4 = *reinterpret_cast<const float4*>(feat + g * C + c);
-        acc[g] = fmaf(w4.x, f4.x, acc[g]);
-        acc[g] = fmaf(w4.y, f4.y, acc[g]);
-        acc[g] = fmaf(w4.z, f4.z, acc[g]);
-        acc[g] = fmaf(w4.w, f4.w, acc[g]);
-      }
+    for (int i = 0; i < 4; ++i) {
+      const int m = m0 + ty * 4 + i;
+      if (m < nimg)
+        *reinterpret_cast<float4*>(logits + (long long)m * IDN_NUM_CLASSES + n) =
+            make_float4(acc[i][0] + bias.x, acc[i][1] + bias.y, acc[i][2] + bias.z, acc[i][3] + bias.w);
     }
-#pragma unroll
-    for (int g = 0; g < kHeadImgs; ++g) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) acc[g] += __shfl_xor_sync(0xffffffffu, acc[g], o);
-    }
-    const float b = __ldg(fc_b + j);
-#pragma unroll
-    for (int g = 0; g < kHeadImgs; ++g)
-      if (lane == g && g < valid) logits[(long long)(n0 + g) * IDN_NUM_CLASSES + j] = acc[g] + b;
   }
 }
 
@@ -196,13 +227,12 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
                        const float* fc_w, const float* fc_b, float* feats, float* logits,
                        int32_t* idx, float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  if (C % 128 != 0 || logits == nullptr || feats == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
+  if (C % kFcK != 0 || logits == nullptr || feats == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
   const int items = nimg * (C / 2);
   avgpool_kernel<<<(items + 255) / 256, 256, 0, st>>>(act, nimg, img_rows, wp, H, W, C, feats);
   IDN_CUDA_TRY(cudaGetLastError());
-  const size_t smem = (size_t)kHeadImgs * C * sizeof(float);
-  dim3 grid((nimg + kHeadImgs - 1) / kHeadImgs, kHeadChunks);
-  fc_fp32_kernel<<<grid, 256, smem, st>>>(feats, nimg, C, fc_w, fc_b, logits);
+  dim3 grid((nimg + kFcTile - 1) / kFcTile, (IDN_NUM_CLASSES + kFcTile - 1) / kFcTile);
+  fc_fp32_kernel<<<grid, 256, 0, st>>>(feats, nimg, C, fc_w, fc_b, logits);
   IDN_CUDA_TRY(cudaGetLastError());
   return launch_softmax_top1(logits, IDN_NUM_CLASSES, nimg, nullptr, idx, prob, st);
 }

@@ -529,8 +529,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   constexpr int B_BYTES = BLOCK_N * kBlockK * 2;
   constexpr int G = (!BRES && TAPS > 0) ? TAPS : 1;    // streamed weights: filter taps per weight stage (== p.b_group)
   constexpr int ACC_COLS = MSUB * BLOCK_N;
-  constexpr int TMEM_COLS = 2 * ACC_COLS <= 128 ? 128 : 2 * ACC_COLS <= 256 ? 256 : 512;
-  static_assert(2 * ACC_COLS <= 512, "accumulators exceed TMEM");
+  // Two accumulator stages let the epilogue of one item overlap the MMAs of the next.  Two 256-column
+  // sub-tiles fill TMEM on their own: they run with ONE stage -- the epilogue is then exposed (a few
+  // thousand cycles per item) but the weights are streamed once per 256 rows instead of once per 128,
+  // and these layers are bound by that stream (L2 -> SM fabric, ~40 B/clk/SM with all SMs pulling).
+  constexpr int ACC_STAGES = 2 * ACC_COLS <= 512 ? 2 : 1;
+  constexpr int TMEM_COLS = ACC_STAGES * ACC_COLS <= 128 ? 128 : ACC_STAGES * ACC_COLS <= 256 ? 256 : 512;
+  static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw_u32 + 1023u) & ~1023u;
@@ -661,6 +666,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           for (int tap0 = 0; tap0 < p.num_taps; tap0 += G) {
             if (!mbar_wait(b_full(sb), phb, 6, tap0, p.profile)) { alive = false; break; }
             ptx::tc_fence_after();
+            const long long t_issue0 = p.profile ? clock64() : 0ll;
             const uint32_t b_stage = b_base + (uint32_t)(sb * G * B_BYTES);
             if (ptx::elect_one()) {
 #pragma unroll
@@ -677,7 +683,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
                                    db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
                 }
               }
+              if (p.profile) atomicAdd(&g_tc_wait_cycles[5], (unsigned long long)(clock64() - t_issue0));   // MMA issue
+              const long long t_c0 = p.profile ? clock64() : 0ll;
               ptx::umma_commit(b_empty(sb));
+              if (p.profile) atomicAdd(&g_tc_wait_cycles[7], (unsigned long long)(clock64() - t_c0));       // commit
             }
             __syncwarp();
             if (++sb == p.b_stages) { sb = 0; phb ^= 1u; }
@@ -690,7 +699,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         __syncwarp();
         if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
       }
-      if (++as == 2) { as = 0; aph ^= 1u; }
+      if (++as == ACC_STAGES) { as = 0; aph ^= 1u; }
     }
   } else if (warp >= 4) {
     // ================================ epilogue ====================================
@@ -715,7 +724,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
-      if (++as == 2) { as = 0; aph ^= 1u; }
+      if (++as == ACC_STAGES) { as = 0; aph ^= 1u; }
     }
   }
 
@@ -1118,7 +1127,7 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   // resident and share them between two 128-row sub-tiles.
   int msub = 1;
   if (n_total == 64) { bn = 64; msub = 2; res = (k_total * 64 * 128) <= 80 * 1024; if (!res) return false; }
-  else if (n_total % 256 == 0) bn = 256;
+  else if (n_total % 256 == 0) bn = 256;   // (two sub-tiles with one accumulator stage: measured 25 % slower)
   else if (n_total % 192 == 0) bn = 192;
   else if (n_total % 128 == 0) { bn = 128; msub = 2; }   // measured: sharing B between two sub-tiles wins at N = 128
   else return false;
@@ -1126,8 +1135,8 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
     const int f = std::atoi(v);
     if (n_total != 64 && (f == 128 || f == 192 || f == 256) && n_total % f == 0) { bn = f; msub = 1; }
   }
-  if (const char* v = std::getenv("IDN_HALO_MSUB")) {          // experiments: two sub-tiles share B
-    if (v[0] == '2' && bn == 128) msub = 2;
+  if (const char* v = std::getenv("IDN_HALO_MSUB")) {          // experiments: one / two sub-tiles share B
+    if (v[0] == '2' && (bn == 128 || bn == 256)) msub = 2;
   }
   const int total_rows = kBlockM * msub + span;
   p->msub = msub;
@@ -1193,6 +1202,8 @@ int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUt
     if (p.b_group == 3) return launch_halo_one<128, 2, false, 3>(tmA1, tmA2, tmB, p, num_sms, st);
     if (p.b_group == 1) return launch_halo_one<128, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   }
+  if (!b_resident && p.msub == 2 && block_n == 256 && p.b_group == 1)
+    return launch_halo_one<256, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   if (!b_resident && p.msub == 1 && p.b_group == 1) {
     if (block_n == 128) return launch_halo_one<128, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
     if (block_n == 192) return launch_halo_one<192, 1, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);

@@ -381,7 +381,7 @@ def main():
                        "parallelism": f"range-sharded dp{world}, NCCL gather of (idx, prob)" if world > 1 else "1 GPU"},
             "roofline": r["roofline"], "e2e": r["e2e"], "clocks": r["clocks"],
             "gpu_launches": r["gpu_launches"], "whole_net": r["whole_net"], "preprocess": r["preprocess"],
-            "kernel_ms": r["kernel_ms"]}
+            "kernel_ms": r["kernel_ms"], "wait_cycles": r["wait_cycles"]}
     if "cpu_baseline" in r:
         line["cpu_baseline"] = r["cpu_baseline"]
     for other in results:

@@ -133,6 +133,7 @@ struct ConvParams {
   int msub;                   // 128-row sub-tiles per work item (1 or 2)
   FastDiv fd_img_rows, fd_wp, fd_per_img, fd_tiles_w;   // row decode without integer division
   int profile;                // 1: book pipeline-wait cycles per role (bench.py timing mode)
+  int pair;                   // 1: conv_pair_kernel (CTA pairs, cta_group::2); weight boxes are N/2 rows
   int b_group;                // halo kernel, streamed weights: filter taps per weight stage (1 or 3).  One
                               // barrier round-trip of the MMA warp costs ~500 cycles whatever it covers
   // stem only: 3x3 stride-2 pad-1 max-pool fused into the epilogue (ResNet18 conv1 -> maxpool).  The

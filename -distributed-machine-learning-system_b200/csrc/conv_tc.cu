@@ -165,6 +165,73 @@ __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// ---- CTA pairs (cta_group::2): two CTAs of a cluster on the two SMs of a TPC share one 256-row MMA ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok;
+}
+// TMA load whose completion is booked on a barrier of EITHER CTA of the pair (cluster_bar)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* tm, uint32_t cluster_bar,
+                                                 int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(cluster_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_dst) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "n"(COLS)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
+}
+// D[tmem of both CTAs, 256 rows] (+)= A[128 rows in each CTA] * B[N/2 rows in each CTA]; leader CTA only
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrives on the barrier at this shared-memory offset in BOTH CTAs once the MMAs issued so far are done
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3)
+      : "memory");
+}
+
 }  // namespace ptx
 
 // Diagnostics of a pipeline stall: [0] = 1 when a wait timed out, [1] = role (0 producer, 1 MMA
@@ -737,6 +804,206 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 }
 
 // =============================================================================================
+// conv_pair_kernel: conv_halo_kernel's streamed-weight variant on CTA pairs (tcgen05 cta_group::2).
+//
+// Measured (profiles/README.md): with one CTA per tile the N = 256 layers stop at 75-82 % tensor-pipe
+// activity because every MMA re-reads its 4 KB activation slice AND its 8 KB weight slice through the
+// ~128 B/clk shared-memory port that the TMA fill also uses.  A CTA pair computes a 256-row x 256-column
+// tile with ONE instruction stream: each CTA stages its own 128 rows (+ halo) of activations and only HALF
+// of the weight rows; the tensor cores of both SMs read both halves.  Per MMA a CTA now reads 4 + 4 KB
+// and fills 16 KB per tap instead of 32.
+//   both CTAs : warp 0 = A producer, warp 3 = B producer (TMA completion is booked on the LEADER's
+//               barriers), warp 2 = TMEM allocator, warps 4.. = epilogue of the CTA's own 128 rows
+//   leader    : warp 1 = MMA issuer; tcgen05.commit multicasts "stage free" / "accumulator ready" to the
+//               barriers at the same offset in both CTAs; the peer's epilogue warps arrive remotely on
+//               the leader's "accumulator drained" barrier.
+// =============================================================================================
+__device__ __forceinline__ bool mbar_wait_cluster(uint32_t bar, uint32_t parity, int role, int where) {
+  if (ptx::mbar_try_wait_cluster(bar, parity)) return true;
+  const unsigned long long t0 = ptx::globaltimer();
+  unsigned int spins = 0;
+  while (!ptx::mbar_try_wait_cluster(bar, parity)) {
+    if ((++spins & 0x3ffu) == 0) {
+      if (*reinterpret_cast<volatile unsigned int*>(&g_tc_watchdog[0]) != 0) return false;
+      if (ptx::globaltimer() - t0 > 2000000000ull) {
+        if (atomicCAS(&g_tc_watchdog[0], 0u, 1u) == 0u) {
+          g_tc_watchdog[1] = (unsigned)role; g_tc_watchdog[2] = blockIdx.x; g_tc_watchdog[3] = (unsigned)where;
+        }
+        __threadfence();
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+template <int BLOCK_N, int G>      // G = filter taps per weight stage (one barrier round-trip each)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
+  constexpr int HALF_N = BLOCK_N / 2;
+  constexpr int B_BYTES = HALF_N * kBlockK * 2;            // this CTA's half of one tap's weight tile
+  constexpr int TMEM_COLS = 2 * BLOCK_N <= 256 ? 256 : 512;
+  static_assert(2 * BLOCK_N <= 512, "accumulators exceed TMEM");
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+  const uint32_t a_base = base;
+  const uint32_t b_base = a_base + (uint32_t)(p.a_stages * p.a_stage_bytes);
+  const uint32_t bar_base = b_base + (uint32_t)(p.b_stages * G * B_BYTES);
+  auto a_full = [&](int s) { return bar_base + 8u * s; };
+  auto a_empty = [&](int s) { return bar_base + 8u * (kMaxAStages + s); };
+  auto b_full = [&](int s) { return bar_base + 8u * (2 * kMaxAStages + s); };
+  auto b_empty = [&](int s) { return bar_base + 8u * (2 * kMaxAStages + kMaxBStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 5);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = (int)(blockIdx.x >> 1), num_pairs = (int)(gridDim.x >> 1);
+  const int m_pairs = (p.num_m_tiles + 1) >> 1;                  // num_m_tiles counts 128-row tiles
+  const int total_items = m_pairs * p.num_n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA1);
+    ptx::prefetch_tmap(&tmA2);
+    ptx::prefetch_tmap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kMaxAStages; ++s) { ptx::mbar_init(a_full(s), 1); ptx::mbar_init(a_empty(s), 1); }
+    for (int s = 0; s < kMaxBStages; ++s) { ptx::mbar_init(b_full(s), 1); ptx::mbar_init(b_empty(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 2 * kEpiWarps); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_pair<TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();                  // both CTAs' barriers and TMEM exist before anything crosses over
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ================================ A producer (own 128 rows + halo) ===============
+    if (lane == 0) {
+      int sa = 0;
+      uint32_t pha = 0;
+      bool alive = true;
+      const uint32_t a_bytes = (uint32_t)(p.halo_r1 + p.halo_r2) * 128u;
+      for (int item = pair; item < total_items && alive; item += num_pairs) {
+        const int m_tile = 2 * (item / p.num_n_tiles) + (int)rank;
+        const int row0 = m_tile * kBlockM + p.halo_lo;
+        for (int cb = 0; cb < p.c_blocks; ++cb) {
+          if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb, p.profile)) { alive = false; break; }
+          const uint32_t dst = a_base + (uint32_t)(sa * p.a_stage_bytes);
+          const uint32_t lead_bar = ptx::mapa(a_full(sa), 0);
+          if (leader) ptx::mbar_expect_tx(a_full(sa), 2u * a_bytes);
+          ptx::tma_load_2d_pair(dst, &tmA1, lead_bar, cb * kBlockK, row0);
+          if (p.halo_r2 > 0)
+            ptx::tma_load_2d_pair(dst + (uint32_t)p.halo_r1 * 128u, &tmA2, lead_bar, cb * kBlockK, row0 + p.halo_r1);
+          if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 3) {
+    // ================================ B producer (own half of the weight rows) =======
+    if (lane == 0) {
+      int sb = 0;
+      uint32_t phb = 0;
+      bool alive = true;
+      for (int item = pair; item < total_items && alive; item += num_pairs) {
+        const int n_tile = item % p.num_n_tiles;
+        for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
+          for (int tap = 0; tap < p.num_taps; tap += G) {
+            if (!mbar_wait(b_empty(sb), phb ^ 1u, 4, tap, p.profile)) { alive = false; break; }
+            const uint32_t lead_bar = ptx::mapa(b_full(sb), 0);
+            if (leader) ptx::mbar_expect_tx(b_full(sb), 2u * (uint32_t)(G * B_BYTES));
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+              ptx::tma_load_2d_pair(b_base + (uint32_t)((sb * G + g) * B_BYTES), &tmB, lead_bar,
+                                    ((tap + g) * p.c_blocks + cb) * kBlockK, n_tile * BLOCK_N + (int)rank * HALF_N);
+            if (++sb == p.b_stages) { sb = 0; phb ^= 1u; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1 && leader) {
+    // ================================ MMA issuer (leader CTA) =========================
+    constexpr uint32_t idesc = make_idesc(2 * kBlockM, BLOCK_N);
+    int sa = 0, sb = 0, as = 0;
+    uint32_t pha = 0, phb = 0, aph = 0;
+    bool alive = true;
+    for (int item = pair; item < total_items && alive; item += num_pairs) {
+      if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) break;      // both CTAs' epilogues drained
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
+      for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
+        if (!mbar_wait(a_full(sa), pha, 2, cb, p.profile)) { alive = false; break; }
+        ptx::tc_fence_after();
+        const uint32_t a_tile = a_base + (uint32_t)(sa * p.a_stage_bytes);
+        for (int tap0 = 0; tap0 < p.num_taps; tap0 += G) {
+          if (!mbar_wait(b_full(sb), phb, 6, tap0, p.profile)) { alive = false; break; }
+          ptx::tc_fence_after();
+          if (ptx::elect_one()) {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+              const int tap = tap0 + g;
+              const uint64_t db = make_sw128_desc(b_base + (uint32_t)((sb * G + g) * B_BYTES));
+              const uint64_t da = make_sw128_desc(a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u);
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k)
+                ptx::umma_bf16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc,
+                                    (cb | tap | k) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit_pair(b_empty(sb));
+          }
+          __syncwarp();
+          if (++sb == p.b_stages) { sb = 0; phb ^= 1u; }
+        }
+        if (alive && ptx::elect_one()) {
+          ptx::umma_commit_pair(a_empty(sa));
+          if (cb == p.c_blocks - 1) ptx::umma_commit_pair(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
+      }
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue (own 128 rows) =========================
+    const int ew = (warp - 4) & 3;
+    const int chunk0 = (warp - 4) >> 2;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int item = pair; item < total_items; item += num_pairs) {
+      const int m_pair = item / p.num_n_tiles;
+      const int n_tile = item - m_pair * p.num_n_tiles;
+      const RowInfo ri = decode_row(p, 2 * m_pair + (int)rank, ew * 32 + lane);
+      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
+      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0, nullptr);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();                  // nobody leaves while the partner may still touch its memory
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+  }
+}
+
+// =============================================================================================
 // stem_kernel: ResNet18 conv1 (7x7, stride 2, pad 3, C = 3 -> 64) + BN + ReLU.
 //
 // The preprocess kernel writes the image as 4-channel NHWC bf16 with 3 zero pixels of left padding,
@@ -1138,6 +1405,26 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   if (const char* v = std::getenv("IDN_HALO_MSUB")) {          // experiments: one / two sub-tiles share B
     if (v[0] == '2' && (bn == 128 || bn == 256)) msub = 2;
   }
+  // CTA pairs (conv_pair_kernel): two SMs share one 256-row MMA and each stages half of the weight rows.
+  // Taps are grouped per weight stage so that one barrier round-trip of the MMA warp covers >= ~1500
+  // cycles of tensor work.
+  // (measured: at N = 128 the single-CTA kernel with two sub-tiles per item is as fast -- there a CTA's MMA
+  // already reads as many activation as weight bytes -- so pairs are used from N = 192 up)
+  p->pair = (!res && (bn == 256 || bn == 192) && num_sms % 2 == 0) ? 1 : 0;
+  if (const char* v = std::getenv("IDN_PAIR_128")) { if (v[0] == '1' && !res && bn == 128 && num_sms % 2 == 0) p->pair = 1; }
+  if (const char* v = std::getenv("IDN_NO_PAIR")) { if (v[0] == '1') p->pair = 0; }
+  if (const char* v = std::getenv("IDN_PAIR_MIN_N")) { if (bn < std::atoi(v)) p->pair = 0; }   // experiments
+  int pair_g = 1;
+  if (p->pair) {
+    msub = 1;
+    if (bn == 128 && p->num_taps % 9 == 0) pair_g = 9;
+    else if (bn == 192 && p->num_taps % 5 == 0) pair_g = 5;
+    else if (p->num_taps % 3 == 0) pair_g = 3;
+    if (const char* v = std::getenv("IDN_PAIR_G")) {            // experiments
+      const int f = std::atoi(v);
+      if ((f == 1 || f == 3 || f == 5 || f == 9) && p->num_taps % f == 0) pair_g = f;
+    }
+  }
   const int total_rows = kBlockM * msub + span;
   p->msub = msub;
   p->halo_lo = lo;
@@ -1148,7 +1435,8 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   // barrier round-trip, so three taps share a stage (measured: tensor pipe 53 % -> see profiles/).
   p->b_group = (!res && bn == 128 && msub == 2 && p->num_taps % 3 == 0) ? 3 : 1;
   if (const char* v = std::getenv("IDN_HALO_BGROUP")) { if (v[0] == '1') p->b_group = 1; }
-  const int b_bytes = bn * 128 * p->b_group;
+  if (p->pair) p->b_group = pair_g;
+  const int b_bytes = (p->pair ? bn / 2 : bn) * 128 * p->b_group;
   if (res) {
     const int left = kSmemBudget - k_total * b_bytes;
     p->a_stages = std::min(kMaxAStages, left / p->a_stage_bytes);
@@ -1159,13 +1447,14 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
     int left = kSmemBudget - p->a_stages * p->a_stage_bytes;
     if (left / b_bytes < 4) { p->a_stages = 2; left = kSmemBudget - 2 * p->a_stage_bytes; }
     p->b_stages = std::min(kMaxBStages, left / b_bytes);
-    if (p->b_stages < 3 && p->b_group > 1) {            // not enough room for grouped stages: one tap each
+    const int min_stages = p->b_group >= 3 ? 2 : 3;      // a grouped stage is long enough for two to overlap
+    if (p->b_stages < min_stages && p->b_group > 1) {    // not enough room for grouped stages: one tap each
       p->b_group = 1;
-      p->b_stages = std::min(kMaxBStages, left / (bn * 128));
+      p->b_stages = std::min(kMaxBStages, left / ((p->pair ? bn / 2 : bn) * 128));
     }
-    if (p->b_stages < 3) return false;
+    if (p->b_stages < (p->b_group >= 3 ? 2 : 3)) return false;
   }
-  (void)m_rows_cap; (void)num_sms;
+  (void)m_rows_cap;
   *block_n = bn;
   *b_resident = res;
   return true;
@@ -1192,6 +1481,25 @@ static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
   return IDN_OK;
 }
 
+template <int BLOCK_N, int G>
+static int launch_pair_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                           const ConvParams& p, int num_sms, cudaStream_t st) {
+  const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles;           // 256-row pair items
+  if (total <= 0) return IDN_OK;
+  const int smem = p.a_stages * p.a_stage_bytes + p.b_stages * G * (BLOCK_N / 2) * 128 + 1024 + 1024;
+  static int configured_smem[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_smem[dev & 63] < smem) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(conv_pair_kernel<BLOCK_N, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured_smem[dev & 63] = smem;
+  }
+  const int pairs = std::min(total, num_sms / 2);
+  conv_pair_kernel<BLOCK_N, G><<<2 * pairs, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);   // __cluster_dims__(2,1,1)
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
 int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                      const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st) {
   if (block_n == 64 && b_resident && p.msub == 2) {
@@ -1201,6 +1509,18 @@ int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUt
   if (!b_resident && p.msub == 2 && block_n == 128) {
     if (p.b_group == 3) return launch_halo_one<128, 2, false, 3>(tmA1, tmA2, tmB, p, num_sms, st);
     if (p.b_group == 1) return launch_halo_one<128, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);
+  }
+  if (p.pair) {
+    if (!b_resident && p.msub == 1) {
+#define IDN_PAIR_CASE(N, GG) \
+      if (block_n == N && p.b_group == GG) return launch_pair_one<N, GG>(tmA1, tmA2, tmB, p, num_sms, st);
+      IDN_PAIR_CASE(256, 1) IDN_PAIR_CASE(256, 3)
+      IDN_PAIR_CASE(192, 1) IDN_PAIR_CASE(192, 3) IDN_PAIR_CASE(192, 5)
+      IDN_PAIR_CASE(128, 1) IDN_PAIR_CASE(128, 3) IDN_PAIR_CASE(128, 9)
+#undef IDN_PAIR_CASE
+    }
+    set_error("launch_conv_halo: unsupported pair configuration");
+    return IDN_EINVAL;
   }
   if (!b_resident && p.msub == 2 && block_n == 256 && p.b_group == 1)
     return launch_halo_one<256, 2, false, 0>(tmA1, tmA2, tmB, p, num_sms, st);

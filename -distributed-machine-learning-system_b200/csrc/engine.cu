@@ -299,7 +299,7 @@ static int add_conv(idn_engine* e, const std::string& name, const Act& src, cons
     IDN_TRY(make_tmap_2d(&st.tmA2, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
                          (uint64_t)src.C * 2, kBlockK, (uint32_t)(cp.halo_r2 > 0 ? cp.halo_r2 : 8)));
     IDN_TRY(make_tmap_2d(&st.tmB, cw.wt, (uint64_t)cw.ktot, (uint64_t)cw.n_total,
-                         (uint64_t)cw.ktot * 2, kBlockK, (uint32_t)st.block_n));
+                         (uint64_t)cw.ktot * 2, kBlockK, (uint32_t)(cp.pair ? st.block_n / 2 : st.block_n)));
     e->steps.push_back(st);
     return IDN_OK;
   }

@@ -1003,6 +1003,159 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   }
 }
 
+// conv_pair_res_kernel: the 64 -> 64 channel layers (weights resident in shared memory) on CTA pairs.
+// A single CTA's 128 x 64 x 16 MMA reads 4 KB of activations + 2 KB of weights for 32 cycles of math and
+// runs at the 48 cycles the shared-memory port needs; in a pair each CTA keeps only 32 of the 64 weight
+// rows (4 + 1 KB per MMA).  Each CTA owns MSUB 128-row sub-tiles of a work item (2 * MSUB * 128 rows per
+// pair), all taps of a channel block are issued in one elected burst as in conv_halo_kernel.
+template <int MSUB, int TAPS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_pair_res_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+                     const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
+  constexpr int BLOCK_N = 64, HALF_N = 32;
+  constexpr int B_BYTES = HALF_N * kBlockK * 2;            // 4 KB: this CTA's half of one tap x channel block
+  constexpr int ACC_COLS = MSUB * BLOCK_N;
+  constexpr int TMEM_COLS = 2 * ACC_COLS <= 128 ? 128 : 2 * ACC_COLS <= 256 ? 256 : 512;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+  const int k_total = p.num_taps * p.c_blocks;
+  const uint32_t a_base = base;
+  const uint32_t b_base = a_base + (uint32_t)(p.a_stages * p.a_stage_bytes);
+  const uint32_t bar_base = b_base + (uint32_t)(k_total * B_BYTES);
+  auto a_full = [&](int s) { return bar_base + 8u * s; };
+  auto a_empty = [&](int s) { return bar_base + 8u * (kMaxAStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxAStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxAStages + 2 + a); };
+  const uint32_t bres_bar = bar_base + 8u * (2 * kMaxAStages + 4);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxAStages + 5);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = (int)(blockIdx.x >> 1), num_pairs = (int)(gridDim.x >> 1);
+  // p.num_m_tiles counts per-CTA items of 128 * MSUB rows; a pair item is two of them
+  const int total_items = (p.num_m_tiles + 1) >> 1;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA1);
+    ptx::prefetch_tmap(&tmA2);
+    ptx::prefetch_tmap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kMaxAStages; ++s) { ptx::mbar_init(a_full(s), 1); ptx::mbar_init(a_empty(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 2 * kEpiWarps); }
+    ptx::mbar_init(bres_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_pair<TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ================================ A producer (own MSUB * 128 rows + halo) ========
+    if (lane == 0) {
+      int sa = 0;
+      uint32_t pha = 0;
+      bool alive = true;
+      const uint32_t a_bytes = (uint32_t)(p.halo_r1 + p.halo_r2) * 128u;
+      for (int item = pair; item < total_items && alive; item += num_pairs) {
+        const int row0 = (2 * item + (int)rank) * (kBlockM * MSUB) + p.halo_lo;
+        for (int cb = 0; cb < p.c_blocks; ++cb) {
+          if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb, p.profile)) { alive = false; break; }
+          const uint32_t dst = a_base + (uint32_t)(sa * p.a_stage_bytes);
+          const uint32_t lead_bar = ptx::mapa(a_full(sa), 0);
+          if (leader) ptx::mbar_expect_tx(a_full(sa), 2u * a_bytes);
+          ptx::tma_load_2d_pair(dst, &tmA1, lead_bar, cb * kBlockK, row0);
+          if (p.halo_r2 > 0)
+            ptx::tma_load_2d_pair(dst + (uint32_t)p.halo_r1 * 128u, &tmA2, lead_bar, cb * kBlockK, row0 + p.halo_r1);
+          if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 3) {
+    // ================================ resident weights: this CTA's 32 rows of every tap =====
+    if (lane == 0) {
+      const uint32_t lead_bar = ptx::mapa(bres_bar, 0);
+      if (leader) ptx::mbar_expect_tx(bres_bar, 2u * (uint32_t)(k_total * B_BYTES));
+      for (int kb = 0; kb < k_total; ++kb)
+        ptx::tma_load_2d_pair(b_base + (uint32_t)(kb * B_BYTES), &tmB, lead_bar, kb * kBlockK, (int)rank * HALF_N);
+    }
+    __syncwarp();
+  } else if (warp == 1 && leader) {
+    // ================================ MMA issuer (leader CTA) =========================
+    constexpr uint32_t idesc = make_idesc(2 * kBlockM, BLOCK_N);
+    int sa = 0, as = 0;
+    uint32_t pha = 0, aph = 0;
+    bool alive = mbar_wait(bres_bar, 0u, 5, 0, p.profile);
+    for (int item = pair; item < total_items && alive; item += num_pairs) {
+      if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) break;
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * ACC_COLS);
+      for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
+        if (!mbar_wait(a_full(sa), pha, 2, cb, p.profile)) { alive = false; break; }
+        ptx::tc_fence_after();
+        const uint32_t a_tile = a_base + (uint32_t)(sa * p.a_stage_bytes);
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int tap = 0; tap < (TAPS > 0 ? TAPS : p.num_taps); ++tap) {
+            const uint64_t db = make_sw128_desc(b_base + (uint32_t)((tap * p.c_blocks + cb) * B_BYTES));
+            const uint32_t a_tap = a_tile + (uint32_t)(p.tap_off[tap] - p.halo_lo) * 128u;
+#pragma unroll
+            for (int sub = 0; sub < MSUB; ++sub) {
+              const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k)
+                ptx::umma_bf16_pair(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
+                                    db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+            }
+          }
+          ptx::umma_commit_pair(a_empty(sa));
+          if (cb == p.c_blocks - 1) ptx::umma_commit_pair(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++sa == p.a_stages) { sa = 0; pha ^= 1u; }
+      }
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue (own sub-tiles) =========================
+    const int ew = (warp - 4) & 3;
+    const int chunk0 = (warp - 4) >> 2;
+    ChunkAffine aff;
+    aff.load(p, chunk0 * 16);
+    int as = 0;
+    uint32_t aph = 0;
+    for (int item = pair; item < total_items; item += num_pairs) {
+      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int sub = 0; sub < MSUB; ++sub) {
+        const RowInfo ri = decode_row(p, (2 * item + (int)rank) * MSUB + sub, ew * 32 + lane);
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
+        epilogue_tile<BLOCK_N>(p, ri, taddr, 0, chunk0, &aff);
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair<TMEM_COLS>(tmem_base);
+  }
+}
+
 // =============================================================================================
 // stem_kernel: ResNet18 conv1 (7x7, stride 2, pad 3, C = 3 -> 64) + BN + ReLU.
 //
@@ -1411,11 +1564,17 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   // (measured: at N = 128 the single-CTA kernel with two sub-tiles per item is as fast -- there a CTA's MMA
   // already reads as many activation as weight bytes -- so pairs are used from N = 192 up)
   p->pair = (!res && (bn == 256 || bn == 192) && num_sms % 2 == 0) ? 1 : 0;
+  // 64-channel layers with resident weights (conv_pair_res_kernel): correct but measured 4 % SLOWER than
+  // the single-CTA kernel on ResNet18's layer1 (those layers move 320-480 MB each and sit nearer the HBM
+  // roofline than the tensor one), so it stays an experiment behind IDN_PAIR_64=1.
+  if (const char* v = std::getenv("IDN_PAIR_64")) {
+    if (v[0] == '1' && res && bn == 64 && msub == 2 && num_sms % 2 == 0) p->pair = 1;
+  }
   if (const char* v = std::getenv("IDN_PAIR_128")) { if (v[0] == '1' && !res && bn == 128 && num_sms % 2 == 0) p->pair = 1; }
   if (const char* v = std::getenv("IDN_NO_PAIR")) { if (v[0] == '1') p->pair = 0; }
   if (const char* v = std::getenv("IDN_PAIR_MIN_N")) { if (bn < std::atoi(v)) p->pair = 0; }   // experiments
   int pair_g = 1;
-  if (p->pair) {
+  if (p->pair && !res) {
     msub = 1;
     if (bn == 128 && p->num_taps % 9 == 0) pair_g = 9;
     else if (bn == 192 && p->num_taps % 5 == 0) pair_g = 5;
@@ -1500,8 +1659,32 @@ static int launch_pair_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
   return IDN_OK;
 }
 
+template <int MSUB, int TAPS>
+static int launch_pair_res_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                               const ConvParams& p, int num_sms, cudaStream_t st) {
+  const int total = (p.num_m_tiles + 1) / 2;                              // pair items of 2 * MSUB * 128 rows
+  if (total <= 0) return IDN_OK;
+  const int k_total = p.num_taps * p.c_blocks;
+  const int smem = p.a_stages * p.a_stage_bytes + k_total * 32 * 128 + 1024 + 1024;
+  static int configured_smem[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_smem[dev & 63] < smem) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(conv_pair_res_kernel<MSUB, TAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured_smem[dev & 63] = smem;
+  }
+  const int pairs = std::min(total, num_sms / 2);
+  conv_pair_res_kernel<MSUB, TAPS><<<2 * pairs, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
+  IDN_CUDA_TRY(cudaGetLastError());
+  return IDN_OK;
+}
+
 int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                      const ConvParams& p, int block_n, bool b_resident, int num_sms, cudaStream_t st) {
+  if (p.pair && b_resident && block_n == 64 && p.msub == 2) {
+    if (p.num_taps == 9) return launch_pair_res_one<2, 9>(tmA1, tmA2, tmB, p, num_sms, st);
+    return launch_pair_res_one<2, 0>(tmA1, tmA2, tmB, p, num_sms, st);
+  }
   if (block_n == 64 && b_resident && p.msub == 2) {
     if (p.num_taps == 9) return launch_halo_one<64, 2, true, 9>(tmA1, tmA2, tmB, p, num_sms, st);
     return launch_halo_one<64, 2, true, 0>(tmA1, tmA2, tmB, p, num_sms, st);

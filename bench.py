@@ -55,10 +55,10 @@ WORKLOAD = {"alexnet": "AlexNet batch 400 over range 0-3999 (uint8 224x224 HWC -
 # dram__bytes_read+write per launch of the dominant kernel from the committed `ncu --set full`
 # capture (profiles/), keyed by (model, step); None until a capture exists for that kernel.
 NCU_TRAFFIC_BYTES: dict = {
-    # profiles/r01b_alexnet_conv2_ncu.txt: conv_halo_kernel<192,1,0,0>, 43.80 MB read + 58.78 MB written
-    ("alexnet", "features.3+relu"): 102577408,
-    # profiles/r01b_resnet18_convs_ncu_full.csv: stem_kernel, 166.53 MB read + 589.15 MB written
-    ("resnet18", "conv1+bn1+relu"): 755691776,
+    # profiles/r01f_alexnet_pair_ncu_full.csv: conv_pair_kernel<192,5>, 43.77 MB read + 59.92 MB written
+    ("alexnet", "features.3+relu"): 103693568,
+    # profiles/r01c_stem_pool2 (stem_kernel with the max-pool folded in): 326.9 MB read + 113.8 MB written
+    ("resnet18", "conv1+bn1+relu"): 440713728,
 }
 
 
@@ -247,7 +247,9 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
     roofline = {"bound": "tensor", "kernel": f"tcgen05 implicit-GEMM conv [{dom}]", "achieved": round(achieved, 2),
                 "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
                 "traffic": NCU_TRAFFIC_BYTES.get((model, dom)),
-                "peak_source": f"MEASURED_PEAKS.json bf16 sustained ({peaks['source']})",
+                "peak_source": f"MEASURED_PEAKS.json bf16 sustained ({peaks['source']}); the kernel is timed inside a "
+                               "full step, so the sustained figure is the denominator (a short kernel can exceed it)",
+                "frac_of_burst": round(achieved / peaks["tf_burst"], 4) if peaks.get("tf_burst") else None,
                 "kernel_ms": round(tc_steps[dom], 4), "step_share": round(tc_steps[dom] / sum(acc.values()), 4)}
     whole = value / world * FLOP_PER_IMG[model] / 1e12
     pre_ms = acc.get("preprocess")

@@ -35,7 +35,7 @@ from .dist import merge_idempotent
 
 HEARTBEAT_S = 0.25
 LOSS_TIMEOUT_S = 2.0          # the reference's ping timeout (mp4_machinelearning.py:847)
-POLL_S = 0.005
+POLL_S = 0.001
 STOP = "STOP"
 
 
@@ -347,6 +347,8 @@ def gpu_worker_main(host: str, port: int, rank: int, max_batch: int, die_after_b
                     preload=("resnet18",), device: int | None = None):
     """Entry point of one GPU worker process (CUDA device index = rank unless ``device`` says otherwise:
     the single-GPU test runs two ranks on one device)."""
+    from .engine import bind_host_thread_to_gpu
+    bind_host_thread_to_gpu(rank if device is None else device)     # staging memory on the GPU's NUMA node
     classify = gpu_classifier(rank if device is None else device, max_batch)
     for m in preload:                      # weights resident before the first heartbeat is sent
         classify.engine(m)

@@ -232,3 +232,26 @@ class PinnedBuffer:
             self.close()
         except Exception:
             pass
+
+
+def bind_host_thread_to_gpu(device: int) -> list[int]:
+    """Pins the calling process to the CPU cores next to ``device`` (NVML's affinity mask for the GPU,
+    intersected with what the process may use), so that page-locked staging buffers allocated afterwards
+    are first-touched on the GPU's own NUMA node.  With one process per GPU on a two-socket host, image
+    batches otherwise cross the socket interconnect on their way to half of the GPUs.  Returns the cores
+    chosen ([] = left alone: no NVML, or the mask does not intersect the allowed set)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+    except Exception:
+        return []
+    near = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+    allowed = os.sched_getaffinity(0)
+    pick = sorted(near & allowed)
+    if not pick or len(pick) == len(allowed):
+        return []
+    os.sched_setaffinity(0, pick)
+    return pick

@@ -357,6 +357,10 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
     torch.cuda.set_device(local)
+    numa_cores = []
+    if world > 1 and os.environ.get("IDN_NO_NUMA_BIND") != "1":
+        from idunno_b200 import bind_host_thread_to_gpu
+        numa_cores = bind_host_thread_to_gpu(local)      # before any page-locked buffer is allocated
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
@@ -380,7 +384,9 @@ def main():
                        "images_per_step": BATCH * world, "weights": "random-init seed 0 (torchvision init)",
                        "l2": "inputs cycle through 4 distinct 60.2 MB uint8 batches per rank (241 MB > 126 MB L2); "
                              "weights + activations per step also exceed L2",
-                       "parallelism": f"range-sharded dp{world}, NCCL gather of (idx, prob)" if world > 1 else "1 GPU"},
+                       "parallelism": f"range-sharded dp{world}, NCCL gather of (idx, prob)" if world > 1 else "1 GPU",
+                       "host_binding": (f"each rank pinned to the {len(numa_cores)} cores NVML reports next to its GPU"
+                                        if numa_cores else "none")},
             "roofline": r["roofline"], "e2e": r["e2e"], "clocks": r["clocks"],
             "gpu_launches": r["gpu_launches"], "whole_net": r["whole_net"], "preprocess": r["preprocess"],
             "kernel_ms": r["kernel_ms"], "wait_cycles": r["wait_cycles"]}

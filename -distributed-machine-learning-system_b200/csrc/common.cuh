@@ -35,6 +35,32 @@ const char* last_error_cstr();
     if (_r != IDN_OK) return _r;      \
   } while (0)
 
+// ---- programmatic dependent launch -------------------------------------------------------------
+// Every kernel of a plan is launched with cudaLaunchAttributeProgrammaticStreamSerialization: its CTAs may
+// become resident while the previous kernel of the stream is still draining (one CTA per SM at a time for
+// the large-shared-memory kernels), run their prologue -- barrier init, TMEM allocation, tensor-map
+// prefetch, resident weights -- and then block in pdl_wait() until the previous kernel has completed and
+// its writes are visible.  Rules kept by every kernel: (1) pdl_wait() before the first access to anything
+// another kernel wrote or reads, (2) pdl_launch_dependents() only AFTER pdl_wait(), so that at most one
+// kernel runs ahead and completion stays transitive along the stream.
+#if defined(__CUDACC__)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+bool pdl_enabled();         // IDN_NO_PDL=1 switches the launch attribute off (engine.cu)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 inline uint16_t f32_to_bf16_bits(float f) {  // round to nearest even, as torch .to(bfloat16)
   uint32_t u;
   std::memcpy(&u, &f, 4);

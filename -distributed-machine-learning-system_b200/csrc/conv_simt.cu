@@ -64,6 +64,8 @@ __device__ __forceinline__ SimtRow simt_decode(const ConvParams& p, int m_tile, 
 
 // block: 256 threads -> 128 rows x 64 cols; thread (ty, tx): rows ty*8..+7, cols tx*4..+3
 __global__ void __launch_bounds__(256) conv_simt_kernel(const ConvParams p) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ float As[16][kBlockM + 1];
   __shared__ float Bs[16][64 + 1];
   const int m_tile = blockIdx.x;
@@ -122,7 +124,7 @@ int launch_conv_simt(const ConvParams& p, cudaStream_t st) {
   if (p.n_total % 64 != 0) { set_error("launch_conv_simt: n_total % 64 != 0"); return IDN_EINVAL; }
   if (p.num_m_tiles <= 0) return IDN_OK;
   dim3 grid(p.num_m_tiles, p.n_total / 64);
-  conv_simt_kernel<<<grid, 256, 0, st>>>(p);
+  IDN_CUDA_TRY(launch_pdl(conv_simt_kernel, dim3(grid), dim3(256), 0, st, p));
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;
 }

@@ -483,6 +483,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();                 // prologue above overlapped the previous kernel's tail; its data from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -642,6 +644,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();                 // prologue above overlapped the previous kernel's tail; its data from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ================================ A producer =================================
@@ -884,6 +888,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   ptx::cluster_sync();                  // both CTAs' barriers and TMEM exist before anything crosses over
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();                 // prologue above overlapped the previous kernel's tail; its data from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ================================ A producer (own 128 rows + halo) ===============
@@ -1055,6 +1061,8 @@ conv_pair_res_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_cons
   ptx::cluster_sync();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();                 // prologue above overlapped the previous kernel's tail; its data from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ================================ A producer (own MSUB * 128 rows + halo) ========
@@ -1294,6 +1302,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();                 // prologue above overlapped the previous kernel's tail; its data from here on
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -1421,8 +1431,7 @@ static int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const Conv
   const int total = p.num_m_tiles * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   const int grid = total < num_sms ? total : num_sms;
-  conv_tc_kernel<BLOCK_N><<<grid, kThreads, TcCfg<BLOCK_N>::SMEM_BYTES, st>>>(tmA, tmB, p);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(conv_tc_kernel<BLOCK_N>, dim3(grid), dim3(kThreads), (size_t)TcCfg<BLOCK_N>::SMEM_BYTES, st, tmA, tmB, p));
   return IDN_OK;
 }
 
@@ -1521,8 +1530,7 @@ int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cud
     configured[dev & 63] = true;
   }
   const int grid = total < num_sms ? total : num_sms;
-  stem_kernel<<<grid, kThreads, kStemSmemBytes, st>>>(tmA, p);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(stem_kernel, dim3(grid), dim3(kThreads), (size_t)kStemSmemBytes, st, tmA, p));
   return IDN_OK;
 }
 
@@ -1635,8 +1643,8 @@ static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
     configured_smem[dev & 63] = smem;
   }
   const int grid = total < num_sms ? total : num_sms;
-  conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS><<<grid, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(conv_halo_kernel<BLOCK_N, MSUB, BRES, TAPS>, dim3(grid), dim3(kThreads), (size_t)smem, st,
+                          tmA1, tmA2, tmB, p));
   return IDN_OK;
 }
 
@@ -1654,8 +1662,8 @@ static int launch_pair_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
     configured_smem[dev & 63] = smem;
   }
   const int pairs = std::min(total, num_sms / 2);
-  conv_pair_kernel<BLOCK_N, G><<<2 * pairs, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);   // __cluster_dims__(2,1,1)
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(conv_pair_kernel<BLOCK_N, G>, dim3(2 * pairs), dim3(kThreads), (size_t)smem, st,
+                          tmA1, tmA2, tmB, p));                       // __cluster_dims__(2,1,1)
   return IDN_OK;
 }
 
@@ -1674,8 +1682,8 @@ static int launch_pair_res_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2,
     configured_smem[dev & 63] = smem;
   }
   const int pairs = std::min(total, num_sms / 2);
-  conv_pair_res_kernel<MSUB, TAPS><<<2 * pairs, kThreads, smem, st>>>(tmA1, tmA2, tmB, p);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(conv_pair_res_kernel<MSUB, TAPS>, dim3(2 * pairs), dim3(kThreads), (size_t)smem, st,
+                          tmA1, tmA2, tmB, p));
   return IDN_OK;
 }
 

@@ -14,6 +14,10 @@ namespace idn {
 // ------------------------------------------------------------------------------ error plumbing
 static thread_local std::string g_last_error;
 void set_error(const std::string& msg) { g_last_error = msg; }
+bool pdl_enabled() {
+  static const bool on = [] { const char* v = std::getenv("IDN_NO_PDL"); return !(v && v[0] == '1'); }();
+  return on;
+}
 const char* last_error_cstr() { return g_last_error.c_str(); }
 
 // ------------------------------------------------------------------------------------ geometry

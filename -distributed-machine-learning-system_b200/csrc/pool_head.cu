@@ -16,6 +16,8 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
 
 // grid = (ceil(OH*OW*C/8 / 256), n); 32-bit index math, packed bf16x2 max (inputs are finite)
 __global__ void __launch_bounds__(256) maxpool3x3s2_kernel(const PoolParams p) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int cvec = p.C >> 3;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= p.OH * p.OW * cvec) return;
@@ -48,8 +50,7 @@ int launch_maxpool(const PoolParams& p, cudaStream_t st) {
   const int per_img = p.OH * p.OW * (p.C / 8);
   if (per_img <= 0 || p.nimg <= 0) return IDN_OK;
   dim3 grid((per_img + 255) / 256, p.nimg);
-  maxpool3x3s2_kernel<<<grid, 256, 0, st>>>(p);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(maxpool3x3s2_kernel, grid, dim3(256), 0, st, p));
   return IDN_OK;
 }
 
@@ -109,6 +110,8 @@ __global__ void __launch_bounds__(128) softmax_top1_kernel(const float* __restri
                                                            int nimg, float* __restrict__ logits_out,
                                                            int32_t* __restrict__ idx,
                                                            float* __restrict__ prob) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= nimg) return;
@@ -120,13 +123,14 @@ __global__ void __launch_bounds__(128) softmax_top1_kernel(const float* __restri
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out, int32_t* idx,
                         float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  softmax_top1_kernel<<<(nimg + 3) / 4, 128, 0, st>>>(logits, ld, nimg, logits_out, idx, prob);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(softmax_top1_kernel, dim3((nimg + 3) / 4), dim3(128), 0, st, logits, ld, nimg, logits_out, idx, prob));
   return IDN_OK;
 }
 
 __global__ void __launch_bounds__(256)
 copy_words_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, size_t n) {
+  pdl_wait();
+  pdl_launch_dependents();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dst[i] = src[i];
 }
@@ -134,8 +138,8 @@ copy_words_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, 
 int launch_copy_words(void* dst, const void* src, size_t n_words, cudaStream_t st) {
   if (n_words == 0) return IDN_OK;
   const unsigned blocks = (unsigned)std::min<size_t>((n_words + 255) / 256, 64);
-  copy_words_kernel<<<blocks, 256, 0, st>>>(static_cast<uint32_t*>(dst), static_cast<const uint32_t*>(src), n_words);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(copy_words_kernel, dim3(blocks), dim3(256), 0, st, static_cast<uint32_t*>(dst),
+                          static_cast<const uint32_t*>(src), n_words));
   return IDN_OK;
 }
 
@@ -146,6 +150,8 @@ int launch_copy_words(void* dst, const void* src, size_t n_words, cudaStream_t s
 __global__ void __launch_bounds__(256)
 avgpool_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W, int C,
                float* __restrict__ feats) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int cpairs = C >> 1;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= nimg * cpairs) return;
@@ -175,6 +181,8 @@ constexpr int kFcTile = 64, kFcK = 32;
 __global__ void __launch_bounds__(256)
 fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __restrict__ fc_w,
                const float* __restrict__ fc_b, float* __restrict__ logits) {
+  pdl_wait();
+  pdl_launch_dependents();
   __shared__ __align__(16) float As[kFcK][kFcTile + 4];     // [k][image]
   __shared__ __align__(16) float Bs[kFcK][kFcTile + 4];     // [k][class]
   const int m0 = blockIdx.x * kFcTile, n0 = blockIdx.y * kFcTile;
@@ -229,11 +237,9 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
   if (nimg <= 0) return IDN_OK;
   if (C % kFcK != 0 || logits == nullptr || feats == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
   const int items = nimg * (C / 2);
-  avgpool_kernel<<<(items + 255) / 256, 256, 0, st>>>(act, nimg, img_rows, wp, H, W, C, feats);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(avgpool_kernel, dim3((items + 255) / 256), dim3(256), 0, st, act, nimg, img_rows, wp, H, W, C, feats));
   dim3 grid((nimg + kFcTile - 1) / kFcTile, (IDN_NUM_CLASSES + kFcTile - 1) / kFcTile);
-  fc_fp32_kernel<<<grid, 256, 0, st>>>(feats, nimg, C, fc_w, fc_b, logits);
-  IDN_CUDA_TRY(cudaGetLastError());
+  IDN_CUDA_TRY(launch_pdl(fc_fp32_kernel, grid, dim3(256), 0, st, feats, nimg, C, fc_w, fc_b, logits));
   return launch_softmax_top1(logits, IDN_NUM_CLASSES, nimg, nullptr, idx, prob, st);
 }
 

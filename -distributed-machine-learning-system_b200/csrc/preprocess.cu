@@ -146,6 +146,8 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
                   const int* __restrict__ tables, const uint16_t* __restrict__ lut, void* out,
                   int left_pad, int ws, int raw_cap_words, int src_rows_cap,
                   uint4* __restrict__ zero_ptr, int zero_vec_per_img) {
+  pdl_wait();
+  pdl_launch_dependents();
   // Optional side job: clear this image's slice of a buffer a later kernel accumulates into with
   // red.max (the pooled ResNet stem output).  This kernel is bound by instruction issue, its store
   // path is idle, so the 415 KB per image ride along for free; stream order keeps them behind the
@@ -372,16 +374,16 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
   const int smem = (raw_cap + rows_cap * IDN_CROP) * 4 + 768 * 2;
   if (out_mode == PRE_OUT_NCHW) {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_NCHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    preprocess_kernel<PRE_OUT_NCHW><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap, zp, zv);
+    IDN_CUDA_TRY(launch_pdl(preprocess_kernel<PRE_OUT_NCHW>, dim3(IDN_CROP / kPreRows, n), dim3(256), (size_t)smem, st,
+                            d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap, zp, zv));
   } else if (out_mode == PRE_OUT_STEM) {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_STEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    preprocess_kernel<PRE_OUT_STEM><<<dim3(IDN_CROP / kPreRows, n), 256, smem, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap, zp, zv);
+    IDN_CUDA_TRY(launch_pdl(preprocess_kernel<PRE_OUT_STEM>, dim3(IDN_CROP / kPreRows, n), dim3(256), (size_t)smem, st,
+                            d_imgs, d_meta, d_tables, d_lut, out, stem_left_pad, stem_ws, raw_cap, rows_cap, zp, zv));
   } else {
     if (smem > 48 * 1024) IDN_CUDA_TRY(cudaFuncSetAttribute(preprocess_kernel<PRE_OUT_S2D4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    preprocess_kernel<PRE_OUT_S2D4><<<dim3(29, n), 256, smem, st>>>(
-        d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap, zp, zv);
+    IDN_CUDA_TRY(launch_pdl(preprocess_kernel<PRE_OUT_S2D4>, dim3(29, n), dim3(256), (size_t)smem, st,
+                            d_imgs, d_meta, d_tables, d_lut, out, 0, 0, raw_cap, rows_cap, zp, zv));
   }
   IDN_CUDA_TRY(cudaGetLastError());
   return IDN_OK;

@@ -1539,7 +1539,16 @@ constexpr int kSmemBudget = 232448 - 1024 - 1024;     // max dynamic smem minus 
 
 bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sms, int* block_n,
                     bool* b_resident) {
-  if (p->mode != MODE_FLAT || p->num_taps < 2) return false;
+  if (p->mode != MODE_FLAT) return false;
+  // Single-tap layers (FC layers, 1x1 downsamples) stay on conv_tc_kernel.  Running them on the CTA-pair
+  // kernel (IDN_FC_PAIR=1) was measured 8 % slower for AlexNet as a whole: 400 rows are two pair items per
+  // N tile, so only 32 of the 74 pairs have work at N = 256.
+  if (p->num_taps < 2) {
+    const char* v = std::getenv("IDN_FC_PAIR");
+    const bool fc_pair = p->num_taps == 1 && n_total % 256 == 0 && num_sms % 2 == 0 && v && v[0] == '1' &&
+                         p->tap_off[0] == 0;
+    if (!fc_pair) return false;
+  }
   if (const char* v = std::getenv("IDN_NO_HALO")) { if (v[0] == '1') return false; }
   int lo = p->tap_off[0], hi = p->tap_off[0];
   for (int t = 1; t < p->num_taps; ++t) { lo = std::min(lo, p->tap_off[t]); hi = std::max(hi, p->tap_off[t]); }

@@ -250,8 +250,8 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       }
     }
     __syncthreads();
-    // Upscales and mild downscales (every 224x224 .. ~450-pixel source) have 2-tap kernels; the table
-    // format pads to 4.  The branch is uniform per image, the arithmetic is the same sum with the zero
+    // Upscales (every source whose short side is < 256, e.g. the 224 x 224 benchmark set) have 3-tap
+    // kernels in Pillow's tables, mild downscales 3-4; the table format allows up to 4.  The branch is uniform per image, the arithmetic is the same sum with the zero
     // terms left out.
     auto passes = [&](auto taps_c) {
       constexpr int NT = decltype(taps_c)::value;
@@ -261,7 +261,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
         const int x0 = ht[1 + x], xn = ht[1 + IDN_CROP + x];
         const int* hk = ht + 1 + 2 * IDN_CROP + x * hks;
         const int k0 = __ldg(hk), k1 = xn > 1 ? __ldg(hk + 1) : 0;
-        const int k2 = (NT > 2 && xn > 2) ? __ldg(hk + 2) : 0, k3 = (NT > 2 && xn > 3) ? __ldg(hk + 3) : 0;
+        const int k2 = (NT > 2 && xn > 2) ? __ldg(hk + 2) : 0, k3 = (NT > 3 && xn > 3) ? __ldg(hk + 3) : 0;
         const int boff = (x0 - c0) * 3;
         int shift = (int)(reinterpret_cast<uintptr_t>(g_first) & 3);
         const uint32_t* rowp = s_raw;
@@ -277,9 +277,10 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
           h0 += bsel(p0, 0) * k0; h1 += bsel(p0, 1) * k0; h2 += bsel(p0, 2) * k0;
           h0 += bsel(p0, 3) * k1; h1 += bsel(p1, 0) * k1; h2 += bsel(p1, 1) * k1;
           if (NT > 2) {
-            const uint32_t p2 = __funnelshift_r(c, wp[3], sh);             // 12 bytes = 4 RGB pixels
+            // 9 bytes (3 pixels) end inside word c whatever the shift; the 4th pixel needs word d
+            const uint32_t p2 = __funnelshift_r(c, NT > 3 ? wp[3] : 0u, sh);
             h0 += bsel(p1, 2) * k2; h1 += bsel(p1, 3) * k2; h2 += bsel(p2, 0) * k2;
-            h0 += bsel(p2, 1) * k3; h1 += bsel(p2, 2) * k3; h2 += bsel(p2, 3) * k3;
+            if (NT > 3) { h0 += bsel(p2, 1) * k3; h1 += bsel(p2, 2) * k3; h2 += bsel(p2, 3) * k3; }
           }
           // coefficients are >= 0 and sum to 2^22 (+- rounding), so the result is already in [0, 255]
           *hp = (uint32_t)(h0 >> 22) | ((uint32_t)(h1 >> 22) << 8) | ((uint32_t)(h2 >> 22) << 16);
@@ -299,7 +300,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
         v.r0 = y0 * IDN_CROP; v.r1 = min(y0 + 1, last) * IDN_CROP;
         v.r2 = min(y0 + 2, last) * IDN_CROP; v.r3 = min(y0 + 3, last) * IDN_CROP;
         v.k0 = __ldg(vk); v.k1 = yn > 1 ? __ldg(vk + 1) : 0;
-        v.k2 = (NT > 2 && yn > 2) ? __ldg(vk + 2) : 0; v.k3 = (NT > 2 && yn > 3) ? __ldg(vk + 3) : 0;
+        v.k2 = (NT > 2 && yn > 2) ? __ldg(vk + 2) : 0; v.k3 = (NT > 3 && yn > 3) ? __ldg(vk + 3) : 0;
         return v;
       };
       auto vpix = [&](const VRow& v, int x) -> uint32_t {
@@ -308,8 +309,11 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
         a0 += bsel(q0, 0) * v.k0; a1 += bsel(q0, 1) * v.k0; a2 += bsel(q0, 2) * v.k0;
         a0 += bsel(q1, 0) * v.k1; a1 += bsel(q1, 1) * v.k1; a2 += bsel(q1, 2) * v.k1;
         if (NT > 2) {
-          const uint32_t q2 = s_h[v.r2 + x], q3 = s_h[v.r3 + x];
+          const uint32_t q2 = s_h[v.r2 + x];
           a0 += bsel(q2, 0) * v.k2; a1 += bsel(q2, 1) * v.k2; a2 += bsel(q2, 2) * v.k2;
+        }
+        if (NT > 3) {
+          const uint32_t q3 = s_h[v.r3 + x];
           a0 += bsel(q3, 0) * v.k3; a1 += bsel(q3, 1) * v.k3; a2 += bsel(q3, 2) * v.k3;
         }
         return (uint32_t)(a0 >> 22) | ((uint32_t)(a1 >> 22) << 8) | ((uint32_t)(a2 >> 22) << 16);
@@ -325,6 +329,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
       }
     };
     if (hks <= 2 && vks <= 2) passes(std::integral_constant<int, 2>{});
+    else if (hks <= 3 && vks <= 3) passes(std::integral_constant<int, 3>{});   // every upscale: Pillow's ksize is 3
     else passes(std::integral_constant<int, 4>{});
   } else {
     __syncthreads();                              // s_lut

@@ -192,20 +192,32 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
-  for (int k0 = 0; k0 < C; k0 += kFcK) {
+  // The next K slab is fetched into registers while the current one is multiplied: the global-load
+  // latency of a slab would otherwise be exposed sixteen times.
+  float4 ra[2], rb[2];
+  auto fetch = [&](int k0) {
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       const int idx = threadIdx.x + 256 * j;
       const int row = idx & 63, kq = (idx >> 6) * 4;
       const int m = m0 + row, n = n0 + row;
-      const float4 a = m < nimg ? __ldg(reinterpret_cast<const float4*>(feats + (long long)m * C + k0 + kq))
-                                : make_float4(0.f, 0.f, 0.f, 0.f);
-      const float4 b = n < IDN_NUM_CLASSES ? __ldg(reinterpret_cast<const float4*>(fc_w + (long long)n * C + k0 + kq))
-                                           : make_float4(0.f, 0.f, 0.f, 0.f);
-      As[kq + 0][row] = a.x; As[kq + 1][row] = a.y; As[kq + 2][row] = a.z; As[kq + 3][row] = a.w;
-      Bs[kq + 0][row] = b.x; Bs[kq + 1][row] = b.y; Bs[kq + 2][row] = b.z; Bs[kq + 3][row] = b.w;
+      ra[j] = m < nimg ? __ldg(reinterpret_cast<const float4*>(feats + (long long)m * C + k0 + kq))
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+      rb[j] = n < IDN_NUM_CLASSES ? __ldg(reinterpret_cast<const float4*>(fc_w + (long long)n * C + k0 + kq))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  fetch(0);
+  for (int k0 = 0; k0 < C; k0 += kFcK) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int idx = threadIdx.x + 256 * j;
+      const int row = idx & 63, kq = (idx >> 6) * 4;
+      As[kq + 0][row] = ra[j].x; As[kq + 1][row] = ra[j].y; As[kq + 2][row] = ra[j].z; As[kq + 3][row] = ra[j].w;
+      Bs[kq + 0][row] = rb[j].x; Bs[kq + 1][row] = rb[j].y; Bs[kq + 2][row] = rb[j].z; Bs[kq + 3][row] = rb[j].w;
     }
     __syncthreads();
+    if (k0 + kFcK < C) fetch(k0 + kFcK);
 #pragma unroll
     for (int k = 0; k < kFcK; ++k) {
       const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);

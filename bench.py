@@ -205,7 +205,7 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
             eng.collect(pending.pop(0))
     run_e2e(3)
     host_submit[0] = 0.0
-    e2e_steps = max(steps, 40)      # long enough that filling and draining the 3-deep pipeline is < 5 %
+    e2e_steps = max(steps, 100)     # ~0.1-0.2 s: filling/draining the 3-deep pipeline is < 2 %, host jitter averages out
     barrier()
     t0 = time.perf_counter()
     run_e2e(e2e_steps)

@@ -14,7 +14,14 @@
 //   residual add -> optional ReLU -> bf16 (or fp32 logits) with 128-bit stores, written either in
 //   the tile's own geometry or scattered to the parity planes a following stride-2 layer reads.
 //
-// ResNet18's stem (7x7 s2 p3, C = 3) has its own kernel, stem_toeplitz_kernel, below.
+// Kernels in this file, all sharing the epilogue and the barrier/watchdog helpers:
+//   conv_tc_kernel        one TMA box per (tap, 64-channel block): FC layers, stride-2 and 1x1 layers
+//   conv_halo_kernel      stride-1 multi-tap layers: one staged activation tile per channel block, taps
+//                         are descriptor offsets into it; weights resident (64-wide) or streamed
+//   conv_pair_kernel      the same on CTA pairs (tcgen05 cta_group::2): 192- and 256-wide layers
+//   conv_pair_res_kernel  64-wide layers on CTA pairs (experiment, off by default)
+//   stem_kernel           ResNet18's 7x7 s2 p3 stem (C = 3) with the following max-pool in its epilogue
+// Every kernel is launched with programmatic dependent launch (common.cuh: pdl_wait after the prologue).
 #include <algorithm>
 #include <cstdlib>
 
@@ -71,14 +78,6 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm,
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
-                                            int c0, int c1, int c2, int c3, int c4) {
-  asm volatile(
-      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {

@@ -91,13 +91,9 @@ struct idn_engine {
   uint16_t* d_lut = nullptr;
   void* xs = nullptr;                 // stem input image
   int stem_left = 0, stem_ws = 232;
-  // io staging
-  uint8_t* d_imgs = nullptr; size_t d_imgs_cap = 0;
-  // host-buffer entry point: the H2D copy of sub-batch k+1 (copy stream, second staging buffer)
-  // overlaps the kernels of sub-batch k
-  // Two submission slots: each has its own staging buffer, pinned metadata, device and pinned
-  // result buffers and events, so that the H2D copy of one tensor batch runs (on the copy stream)
-  // while the kernels of the previous batch run (on the handle's stream).
+  // Submission slots of the host-buffer path: each has its own staging buffer, page-locked and device
+  // records, page-locked result buffers and events, so that the H2D copies of the next tensor batches
+  // run (on the copy stream) while the kernels of the current one run (on the handle's stream).
   struct Slot {
     uint8_t* d_stage = nullptr; size_t d_stage_cap = 0;
     PreMeta* h_meta = nullptr; PreMeta* d_meta = nullptr;
@@ -108,7 +104,7 @@ struct idn_engine {
   } slot[kSlots];
   cudaStream_t copy_stream = nullptr;
   int next_slot = 0;
-  int32_t* d_idx = nullptr; float* d_prob = nullptr; float* d_logits = nullptr;
+  float* d_logits = nullptr;                           // ResNet logits when the caller passes none
   // head
   const bf16* head_act = nullptr; Geom head_g; int head_C = 0;
   float* fc_w = nullptr; float* fc_b = nullptr;        // ResNet fp32 FC
@@ -775,7 +771,6 @@ int idn_destroy(idn_handle h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   for (void* p : h->dev_allocs) cudaFree(p);
   if (h->d_tables) cudaFree(h->d_tables);
-  if (h->d_imgs) cudaFree(h->d_imgs);
   for (int b = 0; b < kSlots; ++b) {
     idn_engine::Slot& sl = h->slot[b];
     if (sl.d_stage) cudaFree(sl.d_stage);
@@ -836,8 +831,6 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   if (cudaMemcpy(e->d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice) != cudaSuccess) {
     set_error("lut upload failed"); return fail(IDN_ECUDA);
   }
-  if ((rc = dev_alloc(e.get(), &e->d_idx, (size_t)max_batch)) != IDN_OK) return fail(rc);
-  if ((rc = dev_alloc(e.get(), &e->d_prob, (size_t)max_batch)) != IDN_OK) return fail(rc);
   if ((rc = dev_alloc(e.get(), &e->d_logits, (size_t)max_batch * IDN_NUM_CLASSES)) != IDN_OK) return fail(rc);
   const float* blob = reinterpret_cast<const float*>(weights_blob);
   rc = model_id == IDN_MODEL_ALEXNET ? build_alexnet(e.get(), blob, n_bytes / 4)

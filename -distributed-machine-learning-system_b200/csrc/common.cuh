@@ -159,6 +159,7 @@ struct ConvParams {
   int msub;                   // 128-row sub-tiles per work item (1 or 2)
   FastDiv fd_img_rows, fd_wp, fd_per_img, fd_tiles_w;   // row decode without integer division
   int profile;                // 1: book pipeline-wait cycles per role (bench.py timing mode)
+  int tc_pair;                // 1: conv_tc_pair_kernel (per-k-block ring on CTA pairs); weight boxes are N/2 rows
   int pair;                   // 1: conv_pair_kernel (CTA pairs, cta_group::2); weight boxes are N/2 rows
   int b_group;                // halo kernel, streamed weights: filter taps per weight stage (1 or 3).  One
                               // barrier round-trip of the MMA warp costs ~500 cycles whatever it covers
@@ -174,6 +175,7 @@ int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvPar
 int launch_conv_simt(const ConvParams& p, cudaStream_t st);
 // Chooses the halo-kernel configuration for a stride-1 multi-tap convolution; returns false when
 // the layer should stay on conv_tc_kernel.  Fills p.halo_* / stages / msub, *block_n, *b_resident.
+bool plan_tc_pair(int num_taps, int n_total, long long m_tiles_cap, int num_sms, int* block_n);   // conv_tc_pair_kernel
 bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sms, int* block_n,
                     bool* b_resident);
 int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,

@@ -278,6 +278,26 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity, int rol
   return true;
 }
 
+// mbar_wait with cluster-scope acquire: for barriers that the partner CTA arrives on remotely
+__device__ __forceinline__ bool mbar_wait_cluster(uint32_t bar, uint32_t parity, int role, int where) {
+  if (ptx::mbar_try_wait_cluster(bar, parity)) return true;
+  const unsigned long long t0 = ptx::globaltimer();
+  unsigned int spins = 0;
+  while (!ptx::mbar_try_wait_cluster(bar, parity)) {
+    if ((++spins & 0x3ffu) == 0) {
+      if (*reinterpret_cast<volatile unsigned int*>(&g_tc_watchdog[0]) != 0) return false;
+      if (ptx::globaltimer() - t0 > 2000000000ull) {
+        if (atomicCAS(&g_tc_watchdog[0], 0u, 1u) == 0u) {
+          g_tc_watchdog[1] = (unsigned)role; g_tc_watchdog[2] = blockIdx.x; g_tc_watchdog[3] = (unsigned)where;
+        }
+        __threadfence();
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
 // Shared-memory matrix descriptor of a K-major, 128B-swizzled tile (rows of 128 bytes; 8-row
 // groups 1024 bytes apart): start>>4 | LBO(unused for swizzled K-major)=1 | SBO=1024>>4 |
 // version=1 (sm_100) | layout_type=2 (SWIZZLE_128B).
@@ -572,6 +592,152 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 }
 
 // =============================================================================================
+// conv_tc_pair_kernel: conv_tc_kernel's ring (one k-block per stage) on CTA pairs.
+//
+// The layers that run on conv_tc_kernel -- FC layers, stride-2 3x3 and 1x1 layers -- use every staged byte
+// exactly once, so a k-block of a 128 x N tile moves (16 + N/8) KB into shared memory and the same amount
+// out again through a ~128 B/clk port: 512 cycles for 256 cycles of math at N = 128, 768 for 512 at
+// N = 256 (measured 700 / ~770; neither cutting the L2 reads with multicast nor fewer barrier round-trips
+// changed that).  As a pair each CTA stages its own 128 rows of A and only N/2 rows of B per k-block.
+// =============================================================================================
+template <int BLOCK_N>
+struct TcPairCfg {
+  static constexpr int HALF_N = BLOCK_N / 2;
+  static constexpr int A_BYTES = kBlockM * kBlockK * 2;
+  static constexpr int B_BYTES = HALF_N * kBlockK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int kStages = (220 * 1024 / STAGE_BYTES) < 8 ? (220 * 1024 / STAGE_BYTES) : 8;
+  static constexpr int TMEM_COLS = 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 256 + 1024;
+};
+
+template <int BLOCK_N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ ConvParams p) {
+  using Cfg = TcPairCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+  const uint32_t bar_base = base + kStages * Cfg::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const int pair = (int)(blockIdx.x >> 1), num_pairs = (int)(gridDim.x >> 1);
+  const int m_pairs = (p.num_m_tiles + 1) >> 1;
+  const int total_items = m_pairs * p.num_n_tiles;
+  const int k_blocks = p.num_taps * p.c_blocks;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 2 * kEpiWarps); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_pair<Cfg::TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ================================ TMA producer (both CTAs) ====================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool alive = true;
+      for (int item = pair; item < total_items && alive; item += num_pairs) {
+        const int m_pair = item / p.num_n_tiles;
+        const int n_tile = item - m_pair * p.num_n_tiles;
+        const int m_tile = 2 * m_pair + (int)rank;
+        int tap = 0, cb = 0;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
+          const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
+          const uint32_t lead_bar = ptx::mapa(full_bar(s), 0);
+          if (leader) ptx::mbar_expect_tx(full_bar(s), 2u * (uint32_t)Cfg::STAGE_BYTES);
+          ptx::tma_load_2d_pair(a_dst, &tmA, lead_bar, cb * kBlockK, m_tile * kBlockM + p.tap_off[tap]);
+          ptx::tma_load_2d_pair(a_dst + Cfg::A_BYTES, &tmB, lead_bar, kb * kBlockK,
+                                n_tile * BLOCK_N + (int)rank * Cfg::HALF_N);
+          if (++cb == p.c_blocks) { cb = 0; ++tap; }
+          if (++s == kStages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1 && leader) {
+    // ================================ MMA issuer (leader CTA) =====================
+    constexpr uint32_t idesc = make_idesc(2 * kBlockM, BLOCK_N);
+    int s = 0, as = 0;
+    uint32_t ph = 0, aph = 0;
+    bool alive = true;
+    for (int item = pair; item < total_items && alive; item += num_pairs) {
+      if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) break;
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
+      for (int kb = 0; kb < k_blocks; ++kb) {
+        if (!mbar_wait(full_bar(s), ph, 2, kb, p.profile)) { alive = false; break; }
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint32_t a_addr = base + s * Cfg::STAGE_BYTES;
+          const uint64_t da = make_sw128_desc(a_addr);
+          const uint64_t db = make_sw128_desc(a_addr + Cfg::A_BYTES);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k)
+            ptx::umma_bf16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+          ptx::umma_commit_pair(empty_bar(s));
+          if (kb == k_blocks - 1) ptx::umma_commit_pair(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++s == kStages) { s = 0; ph ^= 1u; }
+      }
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue (own 128 rows) =====================
+    const int ew = (warp - 4) & 3;
+    const int chunk0 = (warp - 4) >> 2;
+    int as = 0;
+    uint32_t aph = 0;
+    for (int item = pair; item < total_items; item += num_pairs) {
+      const int m_pair = item / p.num_n_tiles;
+      const int n_tile = item - m_pair * p.num_n_tiles;
+      const RowInfo ri = decode_row(p, 2 * m_pair + (int)rank, ew * 32 + lane);
+      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
+      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+      if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair<Cfg::TMEM_COLS>(tmem_base);
+  }
+}
+
+// =============================================================================================
 // conv_halo_kernel: stride-1 multi-tap convolutions with operand reuse.
 //
 // conv_tc_kernel re-fetches a 128 x 64 A box for every filter tap and streams the whole weight
@@ -821,25 +987,6 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 //               barriers at the same offset in both CTAs; the peer's epilogue warps arrive remotely on
 //               the leader's "accumulator drained" barrier.
 // =============================================================================================
-__device__ __forceinline__ bool mbar_wait_cluster(uint32_t bar, uint32_t parity, int role, int where) {
-  if (ptx::mbar_try_wait_cluster(bar, parity)) return true;
-  const unsigned long long t0 = ptx::globaltimer();
-  unsigned int spins = 0;
-  while (!ptx::mbar_try_wait_cluster(bar, parity)) {
-    if ((++spins & 0x3ffu) == 0) {
-      if (*reinterpret_cast<volatile unsigned int*>(&g_tc_watchdog[0]) != 0) return false;
-      if (ptx::globaltimer() - t0 > 2000000000ull) {
-        if (atomicCAS(&g_tc_watchdog[0], 0u, 1u) == 0u) {
-          g_tc_watchdog[1] = (unsigned)role; g_tc_watchdog[2] = blockIdx.x; g_tc_watchdog[3] = (unsigned)where;
-        }
-        __threadfence();
-        return false;
-      }
-    }
-  }
-  return true;
-}
-
 template <int BLOCK_N, int G>      // G = filter taps per weight stage (one barrier round-trip each)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
@@ -1434,8 +1581,54 @@ static int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const Conv
   return IDN_OK;
 }
 
+// Where conv_tc_pair_kernel pays (measured, ResNet18 / AlexNet at batch 400): the stride-2 3x3 layers with a
+// 256-wide tile (-8 %) and the FC layers (few rows: 128-wide pair tiles so that most pairs have an item, FC6
+// -8 %).  It loses on the 128-wide stride-2 layer (+19 %) and on the 1x1 downsamples (+15..40 %: K is 1-4
+// k-blocks, the pair's start-up dominates), which stay on conv_tc_kernel.
+bool plan_tc_pair(int num_taps, int n_total, long long m_tiles_cap, int num_sms, int* block_n) {
+  if (const char* v = std::getenv("IDN_NO_TC_PAIR")) { if (v[0] == '1') return false; }
+  if (num_sms % 2 != 0 || n_total % 128 != 0) return false;
+  const long long m_pairs = (m_tiles_cap + 1) / 2;
+  int bn = 0;
+  if (num_taps > 1 && n_total % 256 == 0 && m_pairs * (n_total / 256) >= num_sms / 2) bn = 256;
+  else if (num_taps == 1 && m_tiles_cap <= 4 && m_tiles_cap >= 2) bn = 128;
+  if (const char* v = std::getenv("IDN_TC_PAIR_BN")) {            // experiments: force it everywhere
+    const int f = std::atoi(v);
+    if ((f == 128 || f == 256) && n_total % f == 0) bn = f;
+  }
+  if (bn == 0) return false;
+  *block_n = bn;
+  return true;
+}
+
+template <int BLOCK_N>
+static int launch_tc_pair_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int num_sms,
+                              cudaStream_t st) {
+  const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles;
+  if (total <= 0) return IDN_OK;
+  static int configured[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(conv_tc_pair_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      TcPairCfg<BLOCK_N>::SMEM_BYTES));
+    configured[dev & 63] = 1;
+  }
+  const int pairs = std::min(total, num_sms / 2);
+  IDN_CUDA_TRY(launch_pdl(conv_tc_pair_kernel<BLOCK_N>, dim3(2 * pairs), dim3(kThreads),
+                          (size_t)TcPairCfg<BLOCK_N>::SMEM_BYTES, st, tmA, tmB, p));
+  return IDN_OK;
+}
+
 int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int block_n,
                    int num_sms, cudaStream_t st) {
+  if (p.tc_pair) {
+    if (p.mode != MODE_FLAT || p.num_n_tiles * block_n != p.n_total) { set_error("launch_conv_tc: bad pair shape"); return IDN_EINVAL; }
+    if (block_n == 128) return launch_tc_pair_one<128>(tmA, tmB, p, num_sms, st);
+    if (block_n == 256) return launch_tc_pair_one<256>(tmA, tmB, p, num_sms, st);
+    set_error("launch_conv_tc: unsupported pair tile");
+    return IDN_EINVAL;
+  }
   if (p.n_total % block_n != 0 || p.num_n_tiles * block_n != p.n_total) {
     set_error("launch_conv_tc: n_total is not a multiple of the N tile");
     return IDN_EINVAL;

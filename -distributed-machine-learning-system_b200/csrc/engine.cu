@@ -304,11 +304,12 @@ static int add_conv(idn_engine* e, const std::string& name, const Act& src, cons
     return IDN_OK;
   }
   st.block_n = pick_block_n(cw.n_total, m_tiles_cap, e->num_sms);
+  cp.tc_pair = plan_tc_pair(cp.num_taps, cw.n_total, m_tiles_cap, e->num_sms, &st.block_n) ? 1 : 0;
   cp.num_n_tiles = cw.n_total / st.block_n;
   IDN_TRY(make_tmap_2d(&st.tmA, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
                        (uint64_t)src.C * 2, kBlockK, kBlockM));
   IDN_TRY(make_tmap_2d(&st.tmB, cw.wt, (uint64_t)cw.ktot, (uint64_t)cw.n_total,
-                       (uint64_t)cw.ktot * 2, kBlockK, (uint32_t)st.block_n));
+                       (uint64_t)cw.ktot * 2, kBlockK, (uint32_t)(cp.tc_pair ? st.block_n / 2 : st.block_n)));
   e->steps.push_back(st);
   return IDN_OK;
 }

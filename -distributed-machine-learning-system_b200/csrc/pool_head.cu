@@ -170,39 +170,43 @@ avgpool_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int
   reinterpret_cast<float2*>(feats)[t] = make_float2(s0 * inv, s1 * inv);
 }
 
-// grid = (ceil(n / 16), 8): a CTA stages the features of 16 images in shared memory and computes
-// 125 of the 1000 classes for them; a warp owns two classes at a time, lanes split K with 128-bit loads.
 // logits[n][j] = bias[j] + sum_c feats[n][c] * fc_w[j][c], fp32, c ascending (deterministic).  A
-// register-tiled SIMT GEMM: 64 images x 64 classes per CTA, 4 x 4 outputs per thread, K in slabs of 32
-// staged k-major in shared memory, so one k step costs a thread two 128-bit shared loads for 16 FMAs
-// (the earlier warp-per-class kernel issued sixteen and was bound by the shared-memory pipe).
-constexpr int kFcTile = 64, kFcK = 32;
+// register-tiled SIMT GEMM: 32 images x 64 classes per CTA (13 x 16 = 208 CTAs at batch 400, two per SM:
+// the kernel is latency-bound, so more and smaller CTAs beat fewer big ones), 4 x 4 outputs per thread, K in
+// slabs of 32 staged k-major in shared memory: one k step costs a thread two 128-bit shared loads for
+// 16 FMAs.  The next slab is fetched into registers while the current one is multiplied.
+constexpr int kFcTileM = 32, kFcTileN = 64, kFcK = 32, kFcThreads = (kFcTileM / 4) * (kFcTileN / 4);
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kFcThreads)
 fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __restrict__ fc_w,
                const float* __restrict__ fc_b, float* __restrict__ logits) {
   pdl_wait();
   pdl_launch_dependents();
-  __shared__ __align__(16) float As[kFcK][kFcTile + 4];     // [k][image]
-  __shared__ __align__(16) float Bs[kFcK][kFcTile + 4];     // [k][class]
-  const int m0 = blockIdx.x * kFcTile, n0 = blockIdx.y * kFcTile;
+  __shared__ __align__(16) float As[kFcK][kFcTileM + 4];     // [k][image]
+  __shared__ __align__(16) float Bs[kFcK][kFcTileN + 4];     // [k][class]
+  const int m0 = blockIdx.x * kFcTileM, n0 = blockIdx.y * kFcTileN;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  constexpr int kLoadsA = kFcTileM * (kFcK / 4) / kFcThreads, kLoadsB = kFcTileN * (kFcK / 4) / kFcThreads;
   float acc[4][4];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
-  // The next K slab is fetched into registers while the current one is multiplied: the global-load
-  // latency of a slab would otherwise be exposed sixteen times.
-  float4 ra[2], rb[2];
+  float4 ra[kLoadsA], rb[kLoadsB];
   auto fetch = [&](int k0) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int idx = threadIdx.x + 256 * j;
-      const int row = idx & 63, kq = (idx >> 6) * 4;
-      const int m = m0 + row, n = n0 + row;
+    for (int j = 0; j < kLoadsA; ++j) {
+      const int idx = threadIdx.x + kFcThreads * j;
+      const int row = idx % kFcTileM, kq = (idx / kFcTileM) * 4;
+      const int m = m0 + row;
       ra[j] = m < nimg ? __ldg(reinterpret_cast<const float4*>(feats + (long long)m * C + k0 + kq))
                        : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int j = 0; j < kLoadsB; ++j) {
+      const int idx = threadIdx.x + kFcThreads * j;
+      const int row = idx % kFcTileN, kq = (idx / kFcTileN) * 4;
+      const int n = n0 + row;
       rb[j] = n < IDN_NUM_CLASSES ? __ldg(reinterpret_cast<const float4*>(fc_w + (long long)n * C + k0 + kq))
                                   : make_float4(0.f, 0.f, 0.f, 0.f);
     }
@@ -210,10 +214,15 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
   fetch(0);
   for (int k0 = 0; k0 < C; k0 += kFcK) {
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int idx = threadIdx.x + 256 * j;
-      const int row = idx & 63, kq = (idx >> 6) * 4;
+    for (int j = 0; j < kLoadsA; ++j) {
+      const int idx = threadIdx.x + kFcThreads * j;
+      const int row = idx % kFcTileM, kq = (idx / kFcTileM) * 4;
       As[kq + 0][row] = ra[j].x; As[kq + 1][row] = ra[j].y; As[kq + 2][row] = ra[j].z; As[kq + 3][row] = ra[j].w;
+    }
+#pragma unroll
+    for (int j = 0; j < kLoadsB; ++j) {
+      const int idx = threadIdx.x + kFcThreads * j;
+      const int row = idx % kFcTileN, kq = (idx / kFcTileN) * 4;
       Bs[kq + 0][row] = rb[j].x; Bs[kq + 1][row] = rb[j].y; Bs[kq + 2][row] = rb[j].z; Bs[kq + 3][row] = rb[j].w;
     }
     __syncthreads();
@@ -250,8 +259,8 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
   if (C % kFcK != 0 || logits == nullptr || feats == nullptr) { set_error("resnet_head: bad arguments"); return IDN_EINVAL; }
   const int items = nimg * (C / 2);
   IDN_CUDA_TRY(launch_pdl(avgpool_kernel, dim3((items + 255) / 256), dim3(256), 0, st, act, nimg, img_rows, wp, H, W, C, feats));
-  dim3 grid((nimg + kFcTile - 1) / kFcTile, (IDN_NUM_CLASSES + kFcTile - 1) / kFcTile);
-  IDN_CUDA_TRY(launch_pdl(fc_fp32_kernel, grid, dim3(256), 0, st, feats, nimg, C, fc_w, fc_b, logits));
+  dim3 grid((nimg + kFcTileM - 1) / kFcTileM, (IDN_NUM_CLASSES + kFcTileN - 1) / kFcTileN);
+  IDN_CUDA_TRY(launch_pdl(fc_fp32_kernel, grid, dim3(kFcThreads), 0, st, feats, nimg, C, fc_w, fc_b, logits));
   return launch_softmax_top1(logits, IDN_NUM_CLASSES, nimg, nullptr, idx, prob, st);
 }
 

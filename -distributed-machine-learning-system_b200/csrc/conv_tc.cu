@@ -883,6 +883,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           // the channel block in a single straight-line burst (TAPS > 0: fully unrolled, descriptor
           // arithmetic hoisted ahead of the back-pressured MMA issue)
           if (ptx::elect_one()) {
+            const long long t_burst0 = p.profile ? clock64() : 0ll;
 #pragma unroll
             for (int tap = 0; tap < (TAPS > 0 ? TAPS : p.num_taps); ++tap) {
               const uint64_t db = make_sw128_desc(b_base + (uint32_t)((tap * p.c_blocks + cb) * B_BYTES));
@@ -896,6 +897,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
                                  db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
               }
             }
+            if (p.profile) atomicAdd(&g_tc_wait_cycles[7], (unsigned long long)(clock64() - t_burst0));   // burst issue
           }
           __syncwarp();
         } else {

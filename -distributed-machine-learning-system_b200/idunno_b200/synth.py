@@ -76,6 +76,8 @@ def make_state_dict(model: str, seed: int = 0, variant: str = "default"):
     sd = {k: v.detach().clone() for k, v in net.state_dict().items()}
     if variant == "default":
         return sd
+    if variant == "diverse":
+        return _apply_diverse(name, sd, diverse_calibration(name, seed))
     if variant != "stress":
         raise ValueError(f"unknown weight variant {variant!r}")
     g = torch.Generator().manual_seed(seed + 12345)
@@ -117,4 +119,193 @@ def make_state_dict(model: str, seed: int = 0, variant: str = "default"):
     scale = 2.5 / float(centred.std() + 1e-12)
     sd[head_w] = w * scale
     sd[head_b] = -(sd[head_w] @ fbar) + torch.empty(w.shape[0]).normal_(0.0, 0.3, generator=g)
+    return sd
+
+
+# ---------------------------------------------------------------------------------------------
+# "diverse" weights: a seeded stand-in for a TRAINED network.
+#
+# Random-init networks are dominated by a common mode: every image lands on the same few classes
+# ("default"), and a classifier centred on that common mode amplifies rounding noise ("stress").  A
+# random linear classifier over 1000 classes also has Gaussian logits whose top-1/top-2 gap (about a
+# quarter of their spread) is no larger than what bf16 arithmetic through 8-20 layers costs (measured:
+# 2 % of the feature signal), so on such weights NO reduced-precision implementation can be held to a
+# top-1 bar.  Trained networks do not look like that: their BatchNorm statistics match the data, every
+# layer's output is centred and image dependent, and the classifier is confident about pictures it has
+# learnt.  This variant reproduces those properties with a seeded recipe:
+#   trunk : random BatchNorm gamma/beta with running statistics CALIBRATED on a fixed batch of 32
+#           synthetic images and then perturbed (so mean, var, gamma and beta all matter to the fold);
+#           AlexNet has no BatchNorm, so the same per-channel scale/shift goes into its convolution /
+#           linear weights and biases;
+#   head  : a nearest-prototype classifier that has "learnt" the pictures synth_image(i, mixed=True),
+#           i in 0..999: features are projected on their top-k principal directions (whitened),
+#           class perm[i] has picture i as its prototype p, logit = s * (p.u - |p|^2 / 2).
+# On the BASELINE query (images 0..399) the oracle then predicts 400 distinct classes -- image i is
+# class perm[i], a known answer -- with a median top-1/top-2 margin of 6 logit units, 12-16x the error
+# of the CPU bf16 contract, and top-1 probabilities around 0.97 (not saturated).
+#
+# The calibration is a CPU forward pass whose last bits depend on the machine; the calibrated numbers
+# are therefore committed (idunno_b200/synth_calib/<model>_diverse_seed0.npz, written by
+# tools/make_diverse_calibration.py) and applied with element-wise fp32 arithmetic and float64 sums
+# rounded to fp32, so the weights are the same on every machine (the golden fixtures carry their
+# SHA-256).
+# ---------------------------------------------------------------------------------------------
+CALIB_IMAGES = 32
+PROTOTYPES = 1000
+HEAD_DIMS = {"resnet18": 64, "alexnet": 32}
+MEDIAN_MARGIN = 6.0
+_ALEX_LAYERS = ["features.0", "features.3", "features.6", "features.8", "features.10",
+                "classifier.1", "classifier.4"]
+
+
+def _calib_path(name: str, seed: int) -> str:
+    import os
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "synth_calib", f"{name}_diverse_seed{seed}.npz")
+
+
+def _library_preprocess(indices):
+    """Images through the reference's own preprocess (Pillow / torchvision, alexnet_resnet.py:57-62)."""
+    import torch
+    from PIL import Image
+    from torchvision import transforms
+    tf = transforms.Compose([transforms.Resize(256), transforms.CenterCrop(224), transforms.ToTensor(),
+                             transforms.Normalize(mean=[0.485, 0.456, 0.406], std=[0.229, 0.224, 0.225])])
+    return torch.stack([tf(Image.fromarray(synth_image(j, mixed=True))) for j in indices])
+
+
+def compute_diverse_calibration(name: str, seed: int = 0) -> dict:
+    """Runs the calibration (CPU, about a minute) -> {key: array}."""
+    import torch
+    import torch.nn.functional as F
+    import torchvision
+
+    torch.manual_seed(seed)
+    net = getattr(torchvision.models, name)(weights=None)
+    g = torch.Generator().manual_seed(seed + 777)
+    x = _library_preprocess(range(900000, 900000 + CALIB_IMAGES))
+    out = {}
+    with torch.no_grad():
+        # ---- trunk
+        if name == "resnet18":
+            bns = [(k, m) for k, m in net.named_modules() if isinstance(m, torch.nn.BatchNorm2d)]
+            for k, m in bns:
+                n = m.num_features
+                m.weight.copy_(torch.empty(n).uniform_(0.6, 1.4, generator=g))
+                m.bias.copy_(torch.empty(n).normal_(0.0, 0.25, generator=g))
+                m.momentum = 1.0                      # running statistics := statistics of this batch
+            net.train()
+            net(x)
+            net.eval()
+            for k, m in bns:
+                n = m.num_features
+                sd_ = torch.sqrt(m.running_var)
+                m.running_mean.add_(torch.empty(n).normal_(0.0, 0.1, generator=g) * sd_)
+                m.running_var.mul_(torch.empty(n).uniform_(0.8, 1.25, generator=g))
+                for part in ("weight", "bias", "running_mean", "running_var"):
+                    out[f"{k}.{part}"] = getattr(m, part).detach().numpy().astype(np.float32).copy()
+            head = net.fc
+        else:
+            sd = net.state_dict()
+            h = x
+            for k in _ALEX_LAYERS:
+                w = sd[k + ".weight"]
+                if k == "classifier.1":
+                    h = torch.flatten(h, 1)
+                z = F.conv2d(h, w, None, stride=4, padding=2) if k == "features.0" else \
+                    F.conv2d(h, w, None, padding=w.shape[-1] // 2) if w.dim() == 4 else F.linear(h, w)
+                dims = (0, 2, 3) if z.dim() == 4 else (0,)
+                mean, std = z.mean(dim=dims), z.std(dim=dims) + 1e-6
+                n = w.shape[0]
+                gamma = torch.empty(n).uniform_(0.6, 1.4, generator=g)
+                beta = torch.empty(n).normal_(0.0, 0.25, generator=g)
+                mult = gamma / std
+                bias = beta - mean * mult
+                out[k + ".mult"] = mult.numpy().astype(np.float32)
+                out[k + ".bias"] = bias.numpy().astype(np.float32)
+                shape = (1, -1, 1, 1) if z.dim() == 4 else (1, -1)
+                h = F.relu(z * mult.view(shape) + bias.view(shape))
+                if k in ("features.0", "features.3", "features.10"):
+                    h = F.max_pool2d(h, 3, 2)
+            net.load_state_dict(_apply_diverse(name, {k: v.clone() for k, v in sd.items()}, out))
+            net.eval()
+            head = net.classifier[6]
+        # ---- head: features of the 1000 pictures the classifier "has learnt"
+        feats = []
+        hook = head.register_forward_hook(lambda mod, i, o: feats.append(i[0].detach().clone()))
+        for i0 in range(0, PROTOTYPES, 50):
+            net(_library_preprocess(range(i0, i0 + 50)))
+        hook.remove()
+        f = torch.cat(feats).double()
+        k = HEAD_DIMS[name]
+        fbar = f.mean(dim=0)
+        _, s, vt = torch.linalg.svd(f - fbar, full_matrices=False)
+        a = (vt[:k] / (s[:k] / np.sqrt(len(f))).unsqueeze(1)).t().contiguous()      # D x k, whitening projection
+        a = a.float().double()                                                      # as it is stored
+        p = ((f - fbar) @ a).float().double()                                       # prototypes, 1000 x k
+        u = (f - fbar) @ a
+        logits = u @ p.t() - 0.5 * (p * p).sum(1)
+        top2 = logits.topk(2, dim=1).values
+        scale = MEDIAN_MARGIN / float((top2[:, 0] - top2[:, 1]).median())
+        out["head.A"] = a.numpy().astype(np.float32)
+        out["head.P"] = p.numpy().astype(np.float32)
+        out["head.fbar"] = fbar.numpy().astype(np.float32)
+        out["head.scale"] = np.asarray([scale], dtype=np.float32)
+        out["head.perm"] = torch.randperm(PROTOTYPES, generator=g).numpy().astype(np.int64)
+    return out
+
+
+def diverse_calibration(name: str, seed: int = 0) -> dict:
+    import os
+    path = _calib_path(name, seed)
+    if os.path.exists(path):
+        with np.load(path) as z:
+            return {k: z[k] for k in z.files}
+    return compute_diverse_calibration(name, seed)
+
+
+def diverse_class_of(name: str, i: int, seed: int = 0) -> int:
+    """The class the "diverse" classifier has learnt for picture synth_image(i, mixed=True), 0 <= i < 1000."""
+    return int(diverse_calibration(name, seed)["head.perm"][i])
+
+
+def _apply_diverse(name: str, sd: dict, calib: dict) -> dict:
+    import torch
+    head = "fc" if name == "resnet18" else "classifier.6"
+    for k, v in calib.items():
+        if k.startswith("head."):
+            continue
+        t = torch.from_numpy(np.asarray(v, dtype=np.float32))
+        if k.endswith(".mult"):
+            base = k[: -len(".mult")]
+            w = sd[base + ".weight"]
+            sd[base + ".weight"] = w * t.view(-1, *([1] * (w.dim() - 1)))
+        else:
+            sd[k] = t.clone()
+    if "head.A" in calib:
+        # logit_c(f) = s * (p_c . u - |p_c|^2 / 2),  u = (f - fbar) A   ->   W = s P A^T,  b = -s |p|^2 / 2 - W fbar
+        # Plain IEEE multiply-adds in a fixed order (no BLAS, no SIMD-dependent reductions), float64 rounded to
+        # fp32 at the end: the same bits on every machine.
+        a = calib["head.A"].astype(np.float64)                 # D x k
+        p = calib["head.P"].astype(np.float64)                 # 1000 x k
+        fbar = calib["head.fbar"].astype(np.float64)
+        s = float(calib["head.scale"][0])
+        perm = calib["head.perm"]
+        w = np.zeros((p.shape[0], a.shape[0]), dtype=np.float64)
+        pp = np.zeros(p.shape[0], dtype=np.float64)
+        pc = np.zeros(p.shape[0], dtype=np.float64)
+        c = np.zeros(a.shape[1], dtype=np.float64)
+        for d in range(a.shape[0]):
+            c += a[d] * fbar[d]                                # A^T fbar
+        for j in range(a.shape[1]):
+            w += p[:, j:j + 1] * a[None, :, j]
+            pp += p[:, j] * p[:, j]
+            pc += p[:, j] * c[j]
+        w *= s
+        b = -0.5 * s * pp - s * pc
+        wt = np.zeros_like(w)
+        bt = np.zeros_like(b)
+        wt[perm] = w
+        bt[perm] = b
+        sd[head + ".weight"] = torch.from_numpy(wt.astype(np.float32))
+        sd[head + ".bias"] = torch.from_numpy(bt.astype(np.float32))
     return sd

@@ -167,6 +167,38 @@ def test_full_query_of_400_is_consistent_with_small_batches(built_library, model
     _compare(f"{model}/batch400-tail", i1[380:], p1[380:], l1[380:], want)
 
 
+@pytest.mark.parametrize("model", ["alexnet", "resnet18"])
+def test_baseline_query_top1_against_reference(built_library, golden_dir, model):
+    """BASELINE.json configs[0] at full size: images 0-399 in ONE 400-image tensor batch against the
+    logits / classes / probabilities the UNMODIFIED reference produced for them (oracle/make_golden.py,
+    "diverse" weights: 400 distinct known classes, median margin > 10x the bf16-contract error).
+    This is the top-1 bar of the north star in a form that can fail: the set on which top-1 is provable
+    (margin > 2 x measured error) must hold at least 360 of the 400 images, and on it -- and here on all
+    400 -- the class must be the reference's."""
+    from idunno_b200.synth import diverse_class_of
+    g = np.load(os.path.join(golden_dir, f"{model}_diverse400.npz"))
+    n = int(g["last"]) - int(g["first"]) + 1
+    imgs = [synth_image(i, mixed=True) for i in range(int(g["first"]), int(g["last"]) + 1)]
+    sd = make_state_dict(model, 0, "diverse")
+    with Engine(model, sd, max_batch=400) as eng:
+        idx, prob, logits = eng.infer(imgs, want_logits=True)
+    x = torch.from_numpy(np.stack([pil_resize.preprocess(im) for im in imgs]))
+    contract = torch.cat([ref_path.forward_bf16_contract(model, sd, x[i:i + 50]) for i in range(0, n, 50)]).numpy()
+    want = dict(logits=g["logits"], idx=g["idx"], prob=g["prob"].astype(np.float32), contract=contract)
+    err, tau = _compare(f"{model}/diverse400", idx, prob, logits, want)
+    srt = np.sort(want["logits"], axis=1)
+    margin = srt[:, -1] - srt[:, -2]
+    safe = margin > 2 * err
+    agree = idx == want["idx"]
+    a, b, c = int(agree.sum()), int((agree & safe).sum()), int(safe.sum())
+    print(f"[{model}/diverse400] top-1 agree {a}/{n}, margin>2err {b}/{c}; median margin / err = {np.median(margin) / err:.1f}; "
+          f"error {err / float(np.abs(want['logits']).max()):.3%} of the logit range")
+    assert c > 0.5 * n, "the provable set must not be vacuous"
+    assert c >= 360 and b == c
+    assert a == n, f"{n - a} top-1 flips against the reference"
+    assert np.array_equal(idx, np.asarray([diverse_class_of(model, i) for i in range(n)]))     # the known answer
+
+
 def test_deeplearning_dropin_matches_oracle(built_library, tmp_path, monkeypatch):
     """The reference-facing call: same signature, same result format (alexnet_resnet.py:12,85-92)."""
     from PIL import Image

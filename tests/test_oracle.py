@@ -9,7 +9,8 @@ import torch
 from idunno_b200.synth import MIXED_SIZES, make_state_dict, synth_image
 from oracle import pil_resize, ref_path
 
-CASES = ["alexnet_default", "alexnet_stress", "resnet18_default", "resnet18_stress"]
+CASES = ["alexnet_default", "alexnet_stress", "resnet18_default", "resnet18_stress",
+         "alexnet_diverse400", "resnet18_diverse400"]
 
 
 def test_resize_matches_pillow_bit_exact():
@@ -62,6 +63,8 @@ def test_restatement_matches_reference_fixture(case, golden_dir):
     idxs = [i for i in range(first, last + 1) if i not in skipped]
     imgs = [synth_image(i, mixed=mixed) for i in idxs]
     r = ref_path.infer_arrays(model, sd, imgs)
+    if variant == "diverse":
+        _check_diverse_properties(model, sd, idxs, r, g)
     assert [f"test_{i}.JPEG" for i in idxs] == [str(n) for n in g["names"]]
     for k, p in enumerate(r["pre"]):
         assert hashlib.sha256(p.tobytes()).hexdigest() == str(g["pre_sha256"][k])
@@ -70,6 +73,27 @@ def test_restatement_matches_reference_fixture(case, golden_dir):
     np.testing.assert_allclose(r["prob"], g["prob"], rtol=1e-4)
     cats = ref_path.imagenet_categories()
     assert [cats[i] for i in r["idx"]] == [str(c) for c in g["categories"]]
+
+
+def _check_diverse_properties(model, sd, idxs, r, g):
+    """What makes the BASELINE-size fixture a parity set that can fail: the
+    unmodified reference predicts the KNOWN class of every picture (400 distinct classes), and the margins
+    are far above what bf16 arithmetic costs on these weights."""
+    from idunno_b200.synth import diverse_class_of
+    want_cls = np.asarray([diverse_class_of(model, i) for i in idxs])
+    assert np.array_equal(g["idx"], want_cls), "the reference does not predict the classes the head has learnt"
+    assert len(set(g["idx"].tolist())) >= 50
+    srt = np.sort(g["logits"], axis=1)
+    margin = srt[:, -1] - srt[:, -2]
+    x = torch.from_numpy(r["pre"])
+    contract = torch.cat([ref_path.forward_bf16_contract(model, sd, x[i:i + 50]) for i in range(0, len(x), 50)]).numpy()
+    err = float(np.abs(contract - g["logits"]).max())
+    print(f"\n[{model}/diverse400] median margin {np.median(margin):.3f}, bf16-contract error {err:.4f} "
+          f"({err / float(np.abs(g['logits']).max()):.3%} of the logit range), ratio {np.median(margin) / err:.1f}, "
+          f"margin > 2 err on {int((margin > 2 * err).sum())}/{len(margin)}")
+    assert np.median(margin) >= 10 * err
+    assert int((margin > 2 * err).sum()) >= 0.9 * len(margin)
+    assert np.array_equal(contract.argmax(axis=1), g["idx"])
 
 
 def test_deeplearning_restatement_file_loop(tmp_path, monkeypatch):

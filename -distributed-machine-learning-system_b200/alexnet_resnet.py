@@ -8,9 +8,11 @@ batches instead of one ``model(input_batch)`` per image; the model is built once
 kept resident instead of ``torch.hub.load`` per call.
 
 Weights: the reference downloads torchvision's pretrained checkpoints (``pretrained=True``,
-:18,21).  This module loads ``<modelname>.pth`` (a torchvision state_dict) from the path in
-``IDUNNO_WEIGHTS_DIR`` (default: CWD) when present; offline it falls back to the seed-fixed random
-initialisation used by the tests and says so once on stderr.
+:18,21).  This module loads ``<modelname>.pth`` (a torchvision state_dict) from the directory in
+``IDUNNO_WEIGHTS_DIR`` (default: CWD).  A missing checkpoint is an ERROR, as a failed download is in
+the reference: a worker with a wrong weights directory must not answer with well-formed but
+meaningless tuples.  Only with ``IDUNNO_ALLOW_RANDOM_WEIGHTS=1`` (tests, benchmarks, offline demos)
+does it fall back to the seed-fixed synthetic weights of ``idunno_b200.synth`` and say so on stderr.
 """
 from __future__ import annotations
 
@@ -34,9 +36,16 @@ def _state_dict(name: str):
     if os.path.exists(path):
         import torch
         return torch.load(path, map_location="cpu")
-    sys.stderr.write(f"[alexnet_resnet] {path} not found: using seed-0 random-init {name} weights\n")
-    return synth.make_state_dict(name, int(os.environ.get("IDUNNO_WEIGHTS_SEED", "0")),
-                                 os.environ.get("IDUNNO_WEIGHTS_VARIANT", "default"))
+    if os.environ.get("IDUNNO_ALLOW_RANDOM_WEIGHTS") != "1":
+        raise FileNotFoundError(
+            f"{path} not found: put the torchvision state_dict of {name} there (IDUNNO_WEIGHTS_DIR selects the "
+            "directory) or install weights with alexnet_resnet.set_weights(); set IDUNNO_ALLOW_RANDOM_WEIGHTS=1 "
+            "to classify with seeded synthetic weights instead")
+    seed = int(os.environ.get("IDUNNO_WEIGHTS_SEED", "0"))
+    variant = os.environ.get("IDUNNO_WEIGHTS_VARIANT", "default")
+    sys.stderr.write(f"[alexnet_resnet] {path} not found and IDUNNO_ALLOW_RANDOM_WEIGHTS=1: "
+                     f"using seed-{seed} synthetic '{variant}' {name} weights\n")
+    return synth.make_state_dict(name, seed, variant)
 
 
 def set_weights(modelname: str, state_dict, device: int | None = None):

@@ -84,9 +84,9 @@ struct idn_engine {
   cudaEvent_t meta_ev[4] = {nullptr, nullptr, nullptr, nullptr};   // "ring entry has been read"
   int meta_ring = 1, meta_next = 0;
   int* d_tables = nullptr;
+  int* h_tables = nullptr;                  // page-locked mirror of the pool (upload source, tile sizing)
   size_t tables_cap = 0, tables_used = 0;   // int32 units
   std::map<std::tuple<int, int, int>, int> table_index;
-  std::map<int, std::vector<int>> table_host;   // offset -> host copy (tile sizing)
   int pre_raw_words = 0, pre_src_rows = 0;     // staged-tile need of the current batch
   uint16_t* d_lut = nullptr;
   void* xs = nullptr;                 // stem input image
@@ -563,7 +563,18 @@ static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
 }
 
 // ------------------------------------------------------------------------------- preprocess io
-static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int* off) {
+// Resample tables live in one device pool with a page-locked mirror on the host.  A table that a batch
+// needs for the first time is written into the mirror and copied to the pool by copy_words_kernel on the
+// stream that carries the batch's records (`copy_on`), so a previously unseen image size costs one small
+// kernel and NO synchronisation: earlier batches keep running (a cudaMemcpyAsync from pageable memory
+// would first drain the stream, once per new size -- on a folder of mixed-size JPEGs that used to collapse
+// the submit/collect overlap until the cache was warm).  Every reader of the pool runs on the handle's
+// stream, which is either `copy_on` itself or waits for an event recorded on it after the upload.
+// The pool holds ~180 distinct (source size, resized size, crop) axes before it has to grow; growing is the
+// one slow path (device-wide synchronise, reallocate, copy).
+constexpr size_t kTablePoolInts = 1u << 20;
+
+static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int* off, cudaStream_t copy_on) {
   auto key = std::make_tuple(in_size, out_size, crop);
   auto it = e->table_index.find(key);
   if (it != e->table_index.end()) { *off = it->second; return IDN_OK; }
@@ -571,23 +582,25 @@ static int ensure_table(idn_engine* e, int in_size, int out_size, int crop, int*
   build_axis_table(in_size, out_size, crop, &bytes);
   const size_t n = bytes.size() / 4;
   if (e->tables_used + n > e->tables_cap) {
-    const size_t ncap = std::max(e->tables_cap * 2, e->tables_used + n + (1u << 16));
+    const size_t ncap = std::max({e->tables_cap * 2, e->tables_used + n + (1u << 16), kTablePoolInts});
     int* nt = nullptr;
+    int* nh = nullptr;
     IDN_CUDA_TRY(cudaMalloc(&nt, ncap * 4));
+    if (cudaMallocHost(&nh, ncap * 4) != cudaSuccess) { cudaFree(nt); set_error("table pool: cudaMallocHost failed"); return IDN_ENOMEM; }
     if (e->d_tables) {
-      IDN_CUDA_TRY(cudaStreamSynchronize(e->stream));
+      IDN_CUDA_TRY(cudaDeviceSynchronize());            // kernels in flight may be reading the old pool
       IDN_CUDA_TRY(cudaMemcpy(nt, e->d_tables, e->tables_used * 4, cudaMemcpyDeviceToDevice));
+      std::memcpy(nh, e->h_tables, e->tables_used * 4);
       cudaFree(e->d_tables);
+      cudaFreeHost(e->h_tables);
     }
-    e->d_tables = nt; e->tables_cap = ncap;
+    e->d_tables = nt; e->h_tables = nh; e->tables_cap = ncap;
   }
-  IDN_CUDA_TRY(cudaMemcpyAsync(e->d_tables + e->tables_used, bytes.data(), bytes.size(),
-                               cudaMemcpyHostToDevice, e->stream));
-  IDN_CUDA_TRY(cudaStreamSynchronize(e->stream));   // `bytes` is a temporary
+  std::memcpy(e->h_tables + e->tables_used, bytes.data(), bytes.size());
+  IDN_TRY(launch_copy_words(e->d_tables + e->tables_used, e->h_tables + e->tables_used, n, copy_on));
+  e->launches++;
   *off = (int)e->tables_used;
   e->table_index[key] = *off;
-  e->table_host[*off].assign(reinterpret_cast<const int*>(bytes.data()),
-                             reinterpret_cast<const int*>(bytes.data()) + n);
   e->tables_used += n;
   return IDN_OK;
 }
@@ -613,11 +626,11 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
     resized_size(H, W, &nh, &nw);
     PreMeta& m = hm[i];
     m.offset = offsets[i] - base; m.H = H; m.W = W;
-    IDN_TRY(ensure_table(e, W, nw, crop_offset(nw), &m.htab));
-    IDN_TRY(ensure_table(e, H, nh, crop_offset(nh), &m.vtab));
+    IDN_TRY(ensure_table(e, W, nw, crop_offset(nw), &m.htab, copy_on));
+    IDN_TRY(ensure_table(e, H, nh, crop_offset(nh), &m.vtab, copy_on));
     if (m.htab != last_h || m.vtab != last_v) {
       int rw = 0, sr = 0;
-      preprocess_tile_need(e->table_host[m.htab].data(), e->table_host[m.vtab].data(), &rw, &sr);
+      preprocess_tile_need(e->h_tables + m.htab, e->h_tables + m.vtab, &rw, &sr);
       e->pre_raw_words = std::max(e->pre_raw_words, rw);
       e->pre_src_rows = std::max(e->pre_src_rows, sr);
       last_h = m.htab; last_v = m.vtab;
@@ -772,6 +785,7 @@ int idn_destroy(idn_handle h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   for (void* p : h->dev_allocs) cudaFree(p);
   if (h->d_tables) cudaFree(h->d_tables);
+  if (h->h_tables) cudaFreeHost(h->h_tables);
   for (int b = 0; b < kSlots; ++b) {
     idn_engine::Slot& sl = h->slot[b];
     if (sl.d_stage) cudaFree(sl.d_stage);
@@ -858,6 +872,20 @@ int idn_sync(idn_handle h) {
   if (!h) return IDN_EINVAL;
   IDN_CUDA_TRY(cudaSetDevice(h->device));
   IDN_CUDA_TRY(cudaStreamSynchronize(h->stream));
+  return read_tc_watchdog();
+}
+
+int idn_abort(idn_handle h) {
+  if (!h) return IDN_EINVAL;
+  IDN_CUDA_TRY(cudaSetDevice(h->device));
+  cudaError_t e1 = h->copy_stream ? cudaStreamSynchronize(h->copy_stream) : cudaSuccess;
+  cudaError_t e2 = cudaStreamSynchronize(h->stream);
+  for (int b = 0; b < kSlots; ++b) h->slot[b].busy = false;
+  h->next_slot = 0;
+  if (e1 != cudaSuccess || e2 != cudaSuccess) {
+    set_error(std::string("idn_abort: ") + cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    return IDN_ECUDA;
+  }
   return read_tc_watchdog();
 }
 
@@ -992,6 +1020,7 @@ int idn_preprocess_u8hwc(int device, const uint8_t* imgs, const int64_t* offsets
   auto cleanup = [&]() {
     for (void* p : tmp.dev_allocs) cudaFree(p);
     if (tmp.d_tables) cudaFree(tmp.d_tables);
+    if (tmp.h_tables) cudaFreeHost(tmp.h_tables);
     if (tmp.h_meta) cudaFreeHost(tmp.h_meta);
     for (cudaEvent_t& ev : tmp.meta_ev) if (ev) { cudaEventDestroy(ev); ev = nullptr; }
     if (d_in) cudaFree(d_in);

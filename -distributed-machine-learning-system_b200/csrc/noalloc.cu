@@ -34,19 +34,21 @@ constexpr size_t kTablesOff = 4096;                             // int32 resampl
 constexpr int kTableIntsCap = (int)((IDN_NOALLOC_SCRATCH_BYTES - kTablesOff) / sizeof(int));
 static_assert(sizeof(PreMeta) * IDN_NOALLOC_MAX_IMAGES <= kTablesOff - kMetaOff, "meta region");
 
-constexpr int kMaxDevices = 64;
+constexpr int kMaxDevices = 16;
+struct TableKey { int in_size, out_size, crop, off; };
+// Everything a call touches on the host is per device and static (this entry point does not use the heap
+// either): its own lock, its own staging arrays.  Calls on different GPUs therefore never wait for each
+// other; calls on the same GPU are serialised on the host for as long as it takes to fill and hand over
+// the staging arrays (they share the device array anyway).  Untouched entries are untouched zero pages.
 struct DeviceState {
+  std::mutex mu;
   bool ready = false;
   unsigned char* scratch = nullptr;     // device address of g_noalloc_scratch on this device
+  int host_tables[kTableIntsCap];
+  PreMeta host_meta[IDN_NOALLOC_MAX_IMAGES];
+  TableKey keys[2 * IDN_NOALLOC_MAX_IMAGES];
 };
 DeviceState g_dev[kMaxDevices];
-std::mutex g_mu;                        // the host staging arrays below are shared by all callers
-
-// host staging (static: this entry point does not touch the heap either)
-int g_host_tables[kTableIntsCap];
-PreMeta g_host_meta[IDN_NOALLOC_MAX_IMAGES];
-struct TableKey { int in_size, out_size, crop, off; };
-TableKey g_keys[2 * IDN_NOALLOC_MAX_IMAGES];
 
 // Pillow's fixed-point BILINEAR coefficients for the 224 cropped outputs of one axis, written
 // straight into `dst` ([ksize][xmin[224]][xcnt[224]][k[224][ksize]]).  Same arithmetic as
@@ -119,7 +121,11 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
               std::to_string(IDN_NOALLOC_MAX_IMAGES) + " (IDN_NOALLOC_MAX_IMAGES); split the batch");
     return IDN_EINVAL;
   }
-  if (device < 0 || device >= kMaxDevices) { set_error("idn_preprocess_u8hwc_noalloc: device index"); return IDN_EINVAL; }
+  if (device < 0 || device >= kMaxDevices) {
+    set_error("idn_preprocess_u8hwc_noalloc: device index out of range (static state exists for devices 0.." +
+              std::to_string(kMaxDevices - 1) + ")");
+    return IDN_EINVAL;
+  }
   if (n == 0) return IDN_OK;
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || device >= count) {
@@ -128,10 +134,13 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
   }
   IDN_CUDA_TRY(cudaSetDevice(device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(cuda_stream);
-  std::lock_guard<std::mutex> lock(g_mu);
+  DeviceState& ds = g_dev[device];
+  std::lock_guard<std::mutex> lock(ds.mu);
+  int* const g_host_tables = ds.host_tables;
+  PreMeta* const g_host_meta = ds.host_meta;
+  TableKey* const g_keys = ds.keys;
 
   // ---- set-up, once per device, with that device current
-  DeviceState& ds = g_dev[device];
   if (!ds.ready) {
     unsigned char* ptr = nullptr;
     cudaError_t err = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_scratch);
@@ -180,8 +189,9 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
     if (rw > raw_words) raw_words = rw;
     if (sr > src_rows) src_rows = sr;
   }
-  // pageable -> device copies return once the source has been staged, so the static host arrays
-  // may be reused by the next caller as soon as the lock is released
+  // The sources are ordinary (pageable) static arrays: each of these copies makes the HOST wait until the
+  // work already queued on `st` has finished and the bytes have been staged, and returns only then -- so
+  // the arrays may be refilled by the next call on this device as soon as the lock is released.
   IDN_CUDA_TRY(cudaMemcpyAsync(ds.scratch + kMetaOff, g_host_meta, sizeof(PreMeta) * n, cudaMemcpyHostToDevice, st));
   IDN_CUDA_TRY(cudaMemcpyAsync(ds.scratch + kTablesOff, g_host_tables, sizeof(int) * used, cudaMemcpyHostToDevice, st));
   return launch_preprocess(d_imgs_packed, reinterpret_cast<const PreMeta*>(ds.scratch + kMetaOff),

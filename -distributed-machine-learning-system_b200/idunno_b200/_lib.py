@@ -31,6 +31,7 @@ SIGNATURES = {
     "idn_infer_u8hwc_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                          C.c_void_p, C.c_void_p, C.c_void_p]),
     "idn_sync": (C.c_int, [C.c_void_p]),
+    "idn_abort": (C.c_int, [C.c_void_p]),
     "idn_preprocess_u8hwc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "idn_preprocess_u8hwc_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                                C.c_void_p, C.c_void_p]),

@@ -43,6 +43,7 @@ class Engine:
         self._lib = _lib.load_library()
         self.modelname = "alexnet" if modelname == "alexnet" else "resnet18"
         self.max_batch = int(max_batch)
+        self.device = int(device)
         blob = pack_state_dict(state_dict)
         want = self._lib.idn_weight_count(model_id(modelname))
         if blob.size != want:
@@ -135,6 +136,11 @@ class Engine:
 
     def sync(self):
         _lib.check(self._lib.idn_sync(self._h), "idn_sync")
+
+    def abort(self):
+        """Waits for everything in flight and frees every submission slot without reading results
+        (error recovery: tickets whose results nobody will collect)."""
+        _lib.check(self._lib.idn_abort(self._h), "idn_abort")
 
     # -- diagnostics ---------------------------------------------------------------------------
     def steps(self):

@@ -101,11 +101,14 @@ def stage_chunk(files, buf_for, pool):
     return c
 
 
-def classify_range(eng, filename: str, start_image, end_image, threads: int = 8, device: int = 0):
+def classify_range(eng, filename: str, start_image, end_image, threads: int = 8, device: int | None = None):
     """Folder range -> (indices, top1_idx, top1_prob), tensor batches of ``eng.max_batch`` files.
     While the GPU works on batch k (and the DMA engine copies it), the host threads decode batch
     k+1 into the next pinned buffer; four buffers rotate (three submissions in flight + one being
-    filled, kept on the engine between calls).  Missing files are skipped exactly like the reference does."""
+    filled, kept on the engine between calls).  Missing files are skipped exactly like the reference does.
+    The page-locked ring is allocated in the context of the engine's own GPU.  If staging or a collect
+    raises (a corrupt file, a file deleted between discovery and open), the submissions already in flight
+    are drained before the exception leaves, so the engine stays usable for the next shard."""
     from concurrent.futures import ThreadPoolExecutor
     from .engine import MAX_IN_FLIGHT, PinnedBuffer
     files = discover(filename, start_image, end_image)
@@ -115,6 +118,8 @@ def classify_range(eng, filename: str, start_image, end_image, threads: int = 8,
     prob = np.zeros(n, dtype=np.float32)
     if n == 0:
         return indices, idx, prob
+    if device is None:
+        device = getattr(eng, "device", 0)
     if not hasattr(eng, "_stage_ring"):               # page-locked memory is slow to allocate: keep it
         eng._stage_ring = [None] * (MAX_IN_FLIGHT + 1)
     ring = eng._stage_ring
@@ -131,17 +136,26 @@ def classify_range(eng, filename: str, start_image, end_image, threads: int = 8,
     B = eng.max_batch
     chunks = [files[i:i + B] for i in range(0, n, B)]
     pending = []                                      # (ticket, first position, chunk)
-    with ThreadPoolExecutor(max_workers=threads) as pool:
-        for k, chunk_files in enumerate(chunks):
-            # this buffer last held chunk k-4, which was collected before chunk k-1 was submitted
-            c = stage_chunk(chunk_files, buf_for(k % (MAX_IN_FLIGHT + 1)), pool)
-            if len(pending) == MAX_IN_FLIGHT:
+    try:
+        with ThreadPoolExecutor(max_workers=threads) as pool:
+            for k, chunk_files in enumerate(chunks):
+                # this buffer last held chunk k-4, which was collected before chunk k-1 was submitted
+                c = stage_chunk(chunk_files, buf_for(k % (MAX_IN_FLIGHT + 1)), pool)
+                if len(pending) == MAX_IN_FLIGHT:
+                    t, at, _c = pending.pop(0)
+                    i, p, _ = eng.collect(t)
+                    idx[at:at + len(i)], prob[at:at + len(i)] = i, p
+                pending.append((eng.submit_packed(c.offsets, c.hw, c.buf.ptr), k * B, c))
+            while pending:
                 t, at, _c = pending.pop(0)
                 i, p, _ = eng.collect(t)
                 idx[at:at + len(i)], prob[at:at + len(i)] = i, p
-            pending.append((eng.submit_packed(c.offsets, c.hw, c.buf.ptr), k * B, c))
-        while pending:
-            t, at, _c = pending.pop(0)
-            i, p, _ = eng.collect(t)
-            idx[at:at + len(i)], prob[at:at + len(i)] = i, p
+    except BaseException:
+        # tickets nobody will collect would keep their slots busy for ever ("three submissions are already
+        # in flight" on every later call); wait for the GPU and free them, then let the error out
+        try:
+            eng.abort()
+        except Exception:
+            pass
+        raise
     return indices, idx, prob

@@ -109,6 +109,14 @@ int idn_infer_u8hwc_device(idn_handle h, const uint8_t* d_imgs_packed, const int
 /* Blocks until everything enqueued on the handle's stream has finished. */
 int idn_sync(idn_handle h);
 
+/* Error recovery for the submit/collect pair (no reference counterpart: the reference's worker loop has
+ * nothing in flight, alexnet_resnet.py:48-90; its caller drops a failed shard, mp4_machinelearning.py:615).
+ * Waits for the copy stream and the handle's stream, then frees every submission slot without returning
+ * results: tickets issued before the call are void.  A host that hits an exception between idn_submit_u8hwc
+ * and idn_collect (a file that fails to decode for the next batch) calls this so that the handle is usable
+ * for the next shard. */
+int idn_abort(idn_handle h);
+
 /* Replaces the preprocess Compose at alexnet_resnet.py:57-66 alone (parity tests, staging):
  * host uint8 HWC images -> host bf16 (raw uint16 bit patterns) NCHW [n][3][224][224]. */
 int idn_preprocess_u8hwc(int device, const uint8_t* imgs_packed, const int64_t* offsets,
@@ -161,6 +169,11 @@ int idn_conv2d_nchw(int device, int impl, const float* x, int n, int cin, int h,
  * host heap allocation on its success path.  It is asynchronous: work is enqueued on cuda_stream
  * (NULL = the legacy default stream) and d_out_nchw_bf16 is complete once that stream has been
  * synchronised.  offsets/hw are host arrays as elsewhere.
+ * Host-side cost: the per-image records and the resample tables are copied from static (pageable)
+ * host arrays with two cudaMemcpyAsync calls; such copies make the calling thread wait until the
+ * work already queued on cuda_stream has finished and the bytes have been staged.  The call never
+ * waits for the allocator, but it is not free of host stalls: keep cuda_stream short, or give this
+ * call a stream of its own.  Host state (lock, staging arrays) is per device, devices 0..15.
  * The first call on a device looks up the array's device address and uploads the normalisation
  * table (an extra copy on cuda_stream); make that first call before starting any stream capture.
  * Every call on a device shares the one array: it is rewritten by each call (nothing from an

@@ -256,6 +256,13 @@ def test_submit_collect_overlaps_and_matches_infer(built_library):
         assert np.array_equal(gc[0], ia) and np.array_equal(gc[1], pa)
         assert np.array_equal(ga[0], ia) and np.array_equal(ga[1], pa) and np.array_equal(ga[2], la)
         assert np.array_equal(gb[0], ib) and np.array_equal(gb[1], pb) and gb[2] is None
+        # idn_abort: tickets nobody collects are voided, all three slots are free again
+        eng.submit_packed(off_a, hw_a, pk_a.ctypes.data)
+        eng.submit_packed(off_b, hw_b, pk_b.ctypes.data)
+        eng.abort()
+        ts = [eng.submit_packed(off_a, hw_a, pk_a.ctypes.data) for _ in range(3)]
+        for t in ts:
+            assert np.array_equal(eng.collect(t)[0], ia)
         many = a + b + a + b + a + b + a             # 51 images through a 12-image engine: 5 batches
         im, pm, _ = eng.infer(many)
         assert np.array_equal(im, np.concatenate([ia, ib, ia, ib, ia, ib, ia]))

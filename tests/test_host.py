@@ -143,3 +143,70 @@ def test_stage_chunk_layout_and_reference_file_semantics(tmp_path, monkeypatch):
         assert np.array_equal(c.buf[o:o + h * w * 3].reshape(h, w, 3), want[int(i)])
     assert Image.open("alexnet/test_6.JPEG").mode == "RGB"                    # rewritten like the reference
     assert staging.discover("alexnet", 100, 105) == [] and staging.discover("nosuchfolder", 0, 5) == []
+
+
+def test_missing_checkpoint_is_an_error_unless_opted_in(tmp_path, monkeypatch):
+    """The reference loads pretrained checkpoints (alexnet_resnet.py:18,21) and fails when it cannot; the
+    drop-in must not classify with synthetic weights just because <model>.pth is missing."""
+    import alexnet_resnet as shim
+    monkeypatch.chdir(tmp_path)
+    monkeypatch.setenv("IDUNNO_WEIGHTS_DIR", str(tmp_path))
+    monkeypatch.delenv("IDUNNO_ALLOW_RANDOM_WEIGHTS", raising=False)
+    with pytest.raises(FileNotFoundError, match="IDUNNO_ALLOW_RANDOM_WEIGHTS"):
+        shim._state_dict("resnet18")
+    monkeypatch.setenv("IDUNNO_ALLOW_RANDOM_WEIGHTS", "1")
+    sd = shim._state_dict("resnet18")
+    assert "fc.weight" in sd
+    import torch
+    torch.save(make_state_dict("alexnet", 3), tmp_path / "alexnet.pth")
+    monkeypatch.delenv("IDUNNO_ALLOW_RANDOM_WEIGHTS")
+    assert torch.equal(shim._state_dict("alexnet")["classifier.6.bias"], make_state_dict("alexnet", 3)["classifier.6.bias"])
+
+
+def test_classify_range_drains_tickets_when_staging_fails(tmp_path, monkeypatch):
+    """A file that cannot be decoded for batch k+1 while batch k is in flight: the exception must leave
+    classify_range, and the engine's submission slots must have been released (Engine.abort)."""
+    from PIL import Image
+    from idunno_b200 import staging
+    monkeypatch.chdir(tmp_path)
+    os.makedirs("alexnet")
+    for i in range(5):
+        Image.fromarray(synth_image(i, (32, 40))).save(f"alexnet/test_{i}.JPEG", format="PNG")
+    with open("alexnet/test_5.JPEG", "wb") as f:
+        f.write(b"this is not an image")
+
+    class FakeEngine:
+        max_batch, device = 2, 0
+
+        def __init__(self):
+            self.in_flight, self.aborted, self._stage_ring = 0, 0, [None] * 4
+
+        def submit_packed(self, offsets, hw, ptr):
+            assert self.in_flight < 3
+            self.in_flight += 1
+            return (self.in_flight, len(offsets), False)
+
+        def collect(self, ticket):
+            self.in_flight -= 1
+            return np.zeros(ticket[1], np.int32), np.ones(ticket[1], np.float32), None
+
+        def abort(self):
+            self.aborted += 1
+            self.in_flight = 0
+
+    class HostBuf:                                      # stands in for the page-locked buffer (no GPU here)
+        def __init__(self, n, device=0):
+            self.nbytes, self.array, self.ptr = n, np.zeros(n, np.uint8), 1
+
+        def close(self):
+            pass
+
+    import idunno_b200.engine as engine_mod
+    monkeypatch.setattr(engine_mod, "PinnedBuffer", HostBuf)
+    eng = FakeEngine()
+    with pytest.raises(Exception):
+        staging.classify_range(eng, "alexnet", 0, 5, threads=2)
+    assert eng.aborted == 1 and eng.in_flight == 0
+    os.remove("alexnet/test_5.JPEG")
+    indices, idx, prob = staging.classify_range(eng, "alexnet", 0, 5, threads=2)
+    assert list(indices) == [0, 1, 2, 3, 4] and eng.in_flight == 0 and eng.aborted == 1

@@ -32,15 +32,51 @@ def _noalloc(lib, images, stream):
 
 
 def test_noalloc_matches_allocating_entry_point_twice(built_library):
+    """Two calls in a row, different images, sizes and counts; the second on ANOTHER stream than the one
+    the first call did its one-time set-up on (the set-up copy has completed by then: _noalloc
+    synchronises the stream it used)."""
     lib = built_library
-    stream = torch.cuda.Stream()
     first = [synth_image(i, mixed=True) for i in range(10)]     # ten different source sizes
     second = [synth_image(200 + i) for i in range(3)] + [synth_image(7, size=(300, 224))]
-    for images in (first, second):
+    for images, stream in ((first, torch.cuda.Stream()), (second, torch.cuda.Stream())):
         got = _noalloc(lib, images, stream)
         want = preprocess(images)                               # idn_preprocess_u8hwc
         assert got.dtype == want.dtype and got.shape == want.shape
         assert np.array_equal(got, want), f"{int((got != want).sum())} bf16 values differ"
+
+
+def test_noalloc_allocates_nothing_and_runs_with_the_device_full(built_library):
+    """What the entry point is for: the caller's pool owns the GPU.  A filler tensor takes all free device
+    memory but a small reserve (what the driver itself needs to launch a kernel), then the call must still
+    succeed, give the right answer, and leave cudaMemGetInfo exactly where it was."""
+    lib = built_library
+    images = [synth_image(300 + i, mixed=True) for i in range(6)]
+    want = preprocess(images)
+    stream = torch.cuda.Stream()
+    _noalloc(lib, images[:1], stream)                            # one-time set-up outside the measured window
+    packed, offsets, hw = pack_images(images)
+    d_in = torch.from_numpy(packed).cuda()
+    d_out = torch.zeros(len(images) * 3 * 224 * 224, dtype=torch.int16, device="cuda")
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    reserve = 192 << 20
+    free0, _total = torch.cuda.mem_get_info()
+    filler = torch.empty(max(free0 - reserve, 1 << 20), dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 <= reserve + (64 << 20), "the filler did not take the device's memory"
+    for _ in range(2):
+        rc = lib.idn_preprocess_u8hwc_noalloc(0, C.c_void_p(d_in.data_ptr()), offsets.ctypes.data,
+                                              hw.ctypes.data, len(images), C.c_void_p(d_out.data_ptr()),
+                                              C.c_void_p(stream.cuda_stream))
+        _lib.check(rc, "idn_preprocess_u8hwc_noalloc")
+        stream.synchronize()
+        free2, _ = torch.cuda.mem_get_info()
+        assert free2 == free1, f"device memory in use changed by {free1 - free2} bytes across the call"
+    del filler
+    torch.cuda.empty_cache()
+    got = d_out.cpu().numpy().view(np.uint16).reshape(len(images), 3, 224, 224)
+    assert np.array_equal(got, want)
 
 
 def test_noalloc_rejects_what_does_not_fit(built_library):

@@ -163,8 +163,8 @@ struct ConvParams {
   int pair;                   // 1: conv_pair_kernel (CTA pairs, cta_group::2); weight boxes are N/2 rows
   int b_group;                // halo kernel, streamed weights: filter taps per weight stage (1 or 3).  One
                               // barrier round-trip of the MMA warp costs ~500 cycles whatever it covers
-  // stem only: 3x3 stride-2 pad-1 max-pool fused into the epilogue (ResNet18 conv1 -> maxpool).  The
-  // conv output is not stored; partial window maxima go to pool_out (zeroed beforehand) with red.max.
+  // stem only: 3x3 stride-2 pad-1 max-pool fused into the epilogue (ResNet18 conv1 -> maxpool): the conv
+  // output is not stored, stem_pool_kernel writes the pooled pixels to pool_out with plain stores.
   bf16* pool_out;             // nullptr: plain stem
   int pool_img_rows, pool_wp, pool_oh, pool_ow;
 };
@@ -188,7 +188,8 @@ int conv_tc_configure();   // cudaFuncSetAttribute for every instantiation; once
 int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner_elems, uint64_t rows,
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
 int make_tmap_stem(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
-int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st);
+int make_tmap_stem_row(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
+int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const ConvParams& p, int num_sms, cudaStream_t st);
 
 // other kernels (pool_head.cu)
 struct PoolParams {

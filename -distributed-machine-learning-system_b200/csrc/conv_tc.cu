@@ -20,7 +20,8 @@
 //                         are descriptor offsets into it; weights resident (64-wide) or streamed
 //   conv_pair_kernel      the same on CTA pairs (tcgen05 cta_group::2): 192- and 256-wide layers
 //   conv_pair_res_kernel  64-wide layers on CTA pairs (experiment, off by default)
-//   stem_kernel           ResNet18's 7x7 s2 p3 stem (C = 3) with the following max-pool in its epilogue
+//   stem_kernel           ResNet18's 7x7 s2 p3 stem (C = 3), conv1 + bn1 + relu (tests, activation taps)
+//   stem_pool_kernel      the product path: the same plus the following max-pool, pooled pixels stored directly
 // Every kernel is launched with programmatic dependent launch (common.cuh: pdl_wait after the prologue).
 #include <algorithm>
 #include <cstdlib>
@@ -78,6 +79,14 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm,
       "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4, %5, %6}], [%2];"
       ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                            int c0, int c1, int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
@@ -1345,74 +1354,9 @@ __device__ __forceinline__ uint64_t make_nosw_desc(uint32_t smem_addr, uint32_t 
   return d;                                                     // layout type 0 = no swizzle
 }
 
-// Epilogue of the stem with the following 3x3 / stride-2 / pad-1 max-pool fused in (tv:models/resnet.py
-// :200, the layer right after conv1+bn1+relu).  Pooled pixel (P, Q) is the maximum over conv pixels
-// (2P-1..2P+1, 2Q-1..2Q+1); after ReLU every value is >= 0, so out-of-image taps can count as 0 and the
-// pooled buffer can start from 0.  A warp holds 4 rows x 8 columns of the conv tile (lane = 8 r + c,
-// 16 channels = 8 packed registers per lane).  Window centres are the even (y, x); the warp reduces what
-// it holds of each window with shuffles and sends one partial maximum per touched window to memory
-// with red.global.max (15 windows: centres inside at r in {0,2} x c in {0,2,4,6}, plus the row below
-// (r = 3) and the column to the right (c = 7) whose centres belong to the next warp / tile).  Partial
-// maxima of one window from different warps and CTAs combine in L2; the order does not matter for max,
-// so the result is deterministic.  Measured on B200: red.v4.bf16x2.max runs at 185 G ops/s (16 B each).
 __device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
   __nv_bfloat162 x = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
   return *reinterpret_cast<uint32_t*>(&x);
-}
-
-__device__ __forceinline__ void red_max_bf16x2_v4(bf16* addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("red.global.v4.bf16x2.max.noftz [%0], {%1, %2, %3, %4};"
-               :: "l"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-
-__device__ __forceinline__ void epilogue_stem_pool(const ConvParams& p, int n, int y0, int x0, int lane,
-                                                   uint32_t taddr, int chunk0, const ChunkAffine& aff) {
-  uint32_t v[16];
-  ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(chunk0 * 16), v);
-  const int r = lane >> 3, c = lane & 7;
-  const int y = y0 + r, x = x0 + c;
-  const bool inside = y < p.H && x < p.W;
-  ptx::tmem_ld_wait();
-  uint32_t w[8];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float a0 = fmaf(__uint_as_float(v[4 * j + 0]), aff.s4[j].x, aff.b4[j].x);
-    const float a1 = fmaf(__uint_as_float(v[4 * j + 1]), aff.s4[j].y, aff.b4[j].y);
-    const float a2 = fmaf(__uint_as_float(v[4 * j + 2]), aff.s4[j].z, aff.b4[j].z);
-    const float a3 = fmaf(__uint_as_float(v[4 * j + 3]), aff.s4[j].w, aff.b4[j].w);
-    w[2 * j + 0] = inside ? relu_bf16x2(pack_bf16x2(a0, a1)) : 0u;      // same rounding as the plain stem
-    w[2 * j + 1] = inside ? relu_bf16x2(pack_bf16x2(a2, a3)) : 0u;
-  }
-  // A lane whose neighbour does not take part shuffles from ITSELF (max(x, x) = x): no masks, no
-  // branches -- two shuffles and one three-input packed max per register and direction.
-  // horizontal: even columns take their two neighbours (column 0 has no left neighbour in this warp)
-  const bool c_even = (c & 1) == 0;
-  const int src_right = c_even ? lane + 1 : lane;
-  const int src_left = (c_even && c > 0) ? lane - 1 : lane;
-#pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    const uint32_t left = __shfl_sync(0xffffffffu, w[e], src_left);
-    const uint32_t right = __shfl_sync(0xffffffffu, w[e], src_right);
-    w[e] = max_bf16x2(max_bf16x2(w[e], right), left);
-  }
-  // vertical: rows 0 and 2 are centres (row 0 has no upper neighbour in this warp), row 3 goes to the
-  // centre below on its own
-  const int src_down = (r == 0 || r == 2) ? lane + 8 : lane;
-  const int src_up = r == 2 ? lane - 8 : lane;
-#pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    const uint32_t up = __shfl_sync(0xffffffffu, w[e], src_up);
-    const uint32_t down = __shfl_sync(0xffffffffu, w[e], src_down);
-    w[e] = max_bf16x2(max_bf16x2(w[e], down), up);
-  }
-  const int yc = r == 3 ? y + 1 : y, xc = c == 7 ? x + 1 : x;        // the window centre this lane reports to
-  const bool reports = (r != 1) && (c_even || c == 7) && yc < p.H && xc < p.W && n < p.nimg;
-  if (reports) {
-    bf16* dst = p.pool_out + ((long long)n * p.pool_img_rows + (long long)(yc >> 1) * p.pool_wp + (xc >> 1)) * 64 +
-                chunk0 * 16;
-    red_max_bf16x2_v4(dst, w[0], w[1], w[2], w[3]);
-    red_max_bf16x2_v4(dst + 8, w[4], w[5], w[6], w[7]);
-  }
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -1507,14 +1451,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
     uint32_t aph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64);
-      if (p.pool_out != nullptr) {
-        const int n = (int)fastdiv((unsigned int)tile, p.fd_per_img);
-        const int t = tile - n * per_img;
-        const int th = (int)fastdiv((unsigned int)t, p.fd_tiles_w), tw = t - th * p.tiles_w;
-        if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) break;
-        ptx::tc_fence_after();
-        epilogue_stem_pool(p, n, th * kStemTH + ew * 4, tw * kStemTW, lane, taddr, chunk0, aff);
-      } else {
+      {
         const RowInfo ri = decode_row(p, tile, ew * 32 + lane);
         if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) break;
         ptx::tc_fence_after();
@@ -1524,6 +1461,270 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
       if (++as == 2) { as = 0; aph ^= 1u; }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<128>(tmem_base);
+  }
+}
+
+// =============================================================================================
+// stem_pool_kernel: ResNet18 conv1 + bn1 + relu + maxpool(3, 2, 1) as ONE kernel with plain stores.
+//
+// Same TMA boxes, descriptors and MMA stream as stem_kernel (16 x 8 conv pixels per tile, 14 MMAs).  What
+// differs is who owns which tiles and what the epilogue does.  A CTA walks a contiguous range of "tile
+// rows" (16 conv rows x 112 columns = 14 tiles) in raster order, so every 3 x 3 pooling window it meets
+// has its upper and left neighbours in tiles the SAME CTA finished a moment ago.  The epilogue keeps just
+// those borders in shared memory:
+//   E[3]  : the current tile after BN + ReLU as bf16, 17 x 9 pixels x 64 channels -- interior 16 x 8, row 0 =
+//           the last conv row above the tile, column 0 = the last conv column left of it (written there by
+//           the previous tile's epilogue);
+//   PR[2] : the last conv row of the previous / of this tile row, 112 pixels.
+// Stage a (all 16 epilogue warps): tcgen05.ld -> scale/shift -> bf16 -> ReLU -> st.shared (16-byte chunks
+// XOR-swizzled by pixel index: conflict free both ways); stage c: each thread takes 4 channels of one of the
+// tile's 32 pooled pixels, reads its nine taps from E and writes 8 bytes -- a warp writes 2 x 128 contiguous
+// bytes.  One named barrier per tile separates a from c; E rotates over three buffers and PR over two so
+// that no second barrier is needed.  Out-of-image taps count as 0, which equals PyTorch's -inf padding
+// because every value is >= 0 after ReLU and every window holds at least its centre.
+// Only the first tile row of a CTA's range can lack its upper neighbour (when the range starts inside an
+// image): that ONE conv row (112 pixels) is recomputed as an extra 1 x 128-pixel tile through a second
+// tensor map whose 16 strips are the 14 column blocks of a single row (+ 2 zero-filled).
+// No red.max, no zero-fill pass, no shuffles; the pooled buffer's padding stays zero from allocation.
+// =============================================================================================
+constexpr int kSpStages = 4;
+constexpr int kSpEPix = 17 * 9;
+constexpr int kSpEBytes = kSpEPix * 128;                    // 19584
+constexpr int kSpPRBytes = 112 * 128;                       // 14336
+constexpr int kSpTilesW = 14, kSpTilesH = 7;
+constexpr int kSpSmemBytes = kSpStages * kStemStageBytes + kStemWBytes + 3 * kSpEBytes + 2 * kSpPRBytes + 512 + 1024;
+
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void epi_bar_sync() {            // the 16 epilogue warps only
+  asm volatile("bar.sync 1, %0;" :: "n"(32 * kEpiWarps) : "memory");
+}
+// address of 16-byte chunk `c16` (0..7) of pixel `pix` in a [pixels][128 B] buffer, chunks swizzled by pixel
+__device__ __forceinline__ uint32_t sp_chunk(uint32_t buf, int pix, int c16) {
+  return buf + (uint32_t)pix * 128u + (uint32_t)((c16 ^ (pix & 7)) << 4);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmRow,
+                 const __grid_constant__ ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
+  const uint32_t base = (raw_u32 + 1023u) & ~1023u;
+  const uint32_t w_base = base + kSpStages * kStemStageBytes;
+  const uint32_t e_base = w_base + kStemWBytes;
+  const uint32_t pr_base = e_base + 3 * kSpEBytes;
+  const uint32_t bar_base = pr_base + 2 * kSpPRBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kSpStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kSpStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kSpStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kSpStages + 4);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
+  volatile uint32_t* dead = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot + 8u - raw_u32));   // "a wait timed out"
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // this CTA's tile rows: [tr0, tr1) of nimg * 7, image-major
+  const int total_tr = p.nimg * kSpTilesH;
+  const int per_cta = (total_tr + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int tr0 = (int)blockIdx.x * per_cta;
+  const int tr1 = min(tr0 + per_cta, total_tr);
+
+  if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmA); ptx::prefetch_tmap(&tmRow); }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kSpStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
+    ptx::fence_barrier_init();
+    *dead = 0u;
+  }
+  if (warp == 2) ptx::tmem_alloc<128>(tmem_slot);
+  {   // resident weights (already in shared-memory order); borders start as zeros
+    const uint4* src = reinterpret_cast<const uint4*>(p.stem_w);
+    uint4* dst = reinterpret_cast<uint4*>(smem_raw + (w_base - raw_u32));
+    for (int i = threadIdx.x; i < kStemWBytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
+    uint4* z = reinterpret_cast<uint4*>(smem_raw + (e_base - raw_u32));
+    for (int i = threadIdx.x; i < (3 * kSpEBytes + 2 * kSpPRBytes) / 16; i += blockDim.x) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool alive = true;
+      for (int tr = tr0; tr < tr1 && alive; ++tr) {
+        const int n = tr / kSpTilesH, ty = tr - n * kSpTilesH;
+        for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
+          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, tr, p.profile)) { alive = false; break; }
+          ptx::mbar_expect_tx(full_bar(s), 7 * kStemABytes);
+          const uint32_t dst = base + s * kStemStageBytes;
+          if (tx >= 0) {
+#pragma unroll
+            for (int r = 0; r < 7; ++r)
+              ptx::tma_load_4d(dst + r * kStemABoxPitch, &tmA, full_bar(s), tx * kStemTW * 8, p.tap_par[r],
+                               ty * kStemTH + p.tap_off[r], n);
+          } else {            // the conv row above this CTA's first tile row: 14 column blocks of one row
+#pragma unroll
+            for (int r = 0; r < 7; ++r)
+              ptx::tma_load_5d(dst + r * kStemABoxPitch, &tmRow, full_bar(s), 0, 0, p.tap_par[r],
+                               ty * kStemTH - 1 + p.tap_off[r], n);
+          }
+          if (++s == kSpStages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    constexpr uint32_t idesc = make_idesc(kBlockM, 64);
+    int s = 0, as = 0;
+    uint32_t ph = 0, aph = 0;
+    bool alive = true;
+    for (int tr = tr0; tr < tr1 && alive; ++tr) {
+      const int ty = tr % kSpTilesH;
+      for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
+        if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tr, p.profile)) { alive = false; break; }
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * 64);
+        if (!mbar_wait(full_bar(s), ph, 2, tr, p.profile)) { alive = false; break; }
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, kStemStripBytes);
+          const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
+#pragma unroll
+          for (int r = 0; r < 7; ++r) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k)
+              ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * kStemABoxPitch + 32 * k) >> 4),
+                             db0 + (uint64_t)((r * 4096 + 2048 * k) >> 4), idesc, (r | k) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(empty_bar(s));
+          ptx::umma_commit(tfull_bar(as));
+        }
+        __syncwarp();
+        if (++s == kSpStages) { s = 0; ph ^= 1u; }
+        if (++as == 2) { as = 0; aph ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue: BN + ReLU -> shared memory -> 3x3/s2 max -> global ========
+    const int ew = (warp - 4) & 3;           // TMEM lane quarter
+    const int chunk0 = (warp - 4) >> 2;      // 16-channel chunk of this warp
+    const int eidx = (warp - 4) * 32 + lane; // 0..511
+    const int m = ew * 32 + lane;            // accumulator row = 8 g + i
+    const int g = m >> 3, i = m & 7;
+    ChunkAffine aff;
+    aff.load(p, chunk0 * 16);
+    int as = 0, e3 = 0;
+    uint32_t aph = 0;
+    bool alive = true;
+    for (int tr = tr0; tr < tr1 && alive; ++tr) {
+      const int n = tr / kSpTilesH, ty = tr - n * kSpTilesH;
+      const uint32_t pr_cur = pr_base + (uint32_t)(((tr - tr0) & 1) * kSpPRBytes);        // row above this tile row
+      const uint32_t pr_next = pr_base + (uint32_t)((((tr - tr0) & 1) ^ 1) * kSpPRBytes); // this tile row's last row
+      for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64 + chunk0 * 16);
+        const uint32_t e_cur = e_base + (uint32_t)(e3 * kSpEBytes);
+        const uint32_t e_nxt = e_base + (uint32_t)((e3 == 2 ? 0 : e3 + 1) * kSpEBytes);
+        // ---- stage a
+        if (tx >= 0 && eidx < 72) {            // row 0 of E: the conv row above the tile, columns x0-1 .. x0+7
+          const int j = eidx >> 3, c = eidx & 7;
+          const int col = tx * 8 - 1 + j;
+          uint4 v = make_uint4(0u, 0u, 0u, 0u);
+          if (ty > 0 && col >= 0) v = lds128(sp_chunk(pr_cur, col, c));
+          sts128(sp_chunk(e_cur, j, c), v.x, v.y, v.z, v.w);
+        }
+        const bool ok = mbar_wait(tfull_bar(as), aph, 3, tr, p.profile);
+        if (ok) {
+          ptx::tc_fence_after();
+          uint32_t v[16];
+          ptx::tmem_ld_32x32b_x16(taddr, v);
+          ptx::tmem_ld_wait();
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(tempty_bar(as));      // accumulator is in registers: the MMA may reuse it
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float a0 = fmaf(__uint_as_float(v[4 * j + 0]), aff.s4[j].x, aff.b4[j].x);
+            const float a1 = fmaf(__uint_as_float(v[4 * j + 1]), aff.s4[j].y, aff.b4[j].y);
+            const float a2 = fmaf(__uint_as_float(v[4 * j + 2]), aff.s4[j].z, aff.b4[j].z);
+            const float a3 = fmaf(__uint_as_float(v[4 * j + 3]), aff.s4[j].w, aff.b4[j].w);
+            w[2 * j + 0] = relu_bf16x2(pack_bf16x2(a0, a1));      // same rounding as the plain stem
+            w[2 * j + 1] = relu_bf16x2(pack_bf16x2(a2, a3));
+          }
+          if (tx >= 0) {
+            const int e = (g + 1) * 9 + (i + 1);
+            sts128(sp_chunk(e_cur, e, 2 * chunk0), w[0], w[1], w[2], w[3]);
+            sts128(sp_chunk(e_cur, e, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
+            if (i == 7) {                       // column 0 of the next tile's E (zeros at the start of a tile row)
+              const int e0 = (g + 1) * 9;
+              const uint32_t keep = tx == kSpTilesW - 1 ? 0u : 0xffffffffu;
+              sts128(sp_chunk(e_nxt, e0, 2 * chunk0), w[0] & keep, w[1] & keep, w[2] & keep, w[3] & keep);
+              sts128(sp_chunk(e_nxt, e0, 2 * chunk0 + 1), w[4] & keep, w[5] & keep, w[6] & keep, w[7] & keep);
+            }
+            if (g == 15) {                      // last conv row of this tile row
+              const int col = tx * 8 + i;
+              sts128(sp_chunk(pr_next, col, 2 * chunk0), w[0], w[1], w[2], w[3]);
+              sts128(sp_chunk(pr_next, col, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
+            }
+          } else if (g < kSpTilesW) {           // the recomputed row: accumulator row 8 g + i is column 8 g + i
+            const int col = g * 8 + i;
+            sts128(sp_chunk(pr_cur, col, 2 * chunk0), w[0], w[1], w[2], w[3]);
+            sts128(sp_chunk(pr_cur, col, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
+          }
+        } else {
+          *dead = 1u;
+        }
+        epi_bar_sync();
+        if (*dead != 0u) { alive = false; break; }
+        if (++as == 2) { as = 0; aph ^= 1u; }
+        if (tx < 0) continue;
+        // ---- stage c: pooled pixel (py, px) of the tile, 4 channels per thread
+        {
+          const int pp = eidx >> 4, q = eidx & 15;
+          const int py = pp >> 2, px = pp & 3;
+          uint2 mx = make_uint2(0u, 0u);
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy) {
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) {
+              const int e = (2 * py + dy) * 9 + 2 * px + dx;
+              const uint2 t = lds64(sp_chunk(e_cur, e, q >> 1) + (uint32_t)((q & 1) << 3));
+              mx.x = max_bf16x2(mx.x, t.x);
+              mx.y = max_bf16x2(mx.y, t.y);
+            }
+          }
+          const int P = ty * 8 + py, Q = tx * 4 + px;
+          uint2* dst = reinterpret_cast<uint2*>(p.pool_out + ((long long)n * p.pool_img_rows + (long long)P * p.pool_wp + Q) * 64) + q;
+          *dst = mx;
+        }
+        e3 = e3 == 2 ? 0 : e3 + 1;
+      }
     }
   }
   ptx::tc_fence_before();
@@ -1712,10 +1913,46 @@ int make_tmap_stem(CUtensorMap* tm, const void* base_ptr, int ws_px, int img_h, 
   return IDN_OK;
 }
 
-int launch_stem_tc(const CUtensorMap& tmA, const ConvParams& p, int num_sms, cudaStream_t st) {
+// 5-D map over the same image for the ONE-ROW tile of stem_pool_kernel: (element within a 176-byte strip,
+// column block of 8 output columns = 128 bytes further along the row [overlapping strides], row phase,
+// row group, image); one box = the 14 column blocks of a single conv row (+ 2 out-of-range blocks that
+// read as zeros), in the same 16-strips-of-176-bytes shared-memory shape as the regular 16 x 8 tile.
+int make_tmap_stem_row(CUtensorMap* tm, const void* base_ptr, int ws_px, int img_h, int nimg_cap) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return IDN_ECUDA;
+  const uint64_t row = (uint64_t)ws_px * 8;
+  cuuint64_t gdim[5] = {(cuuint64_t)ws_px * 4, (cuuint64_t)kSpTilesW, 2, (cuuint64_t)(img_h / 2), (cuuint64_t)nimg_cap};
+  cuuint64_t gstr[4] = {128, row, 2 * row, (cuuint64_t)img_h * row};
+  cuuint32_t box[5] = {88, 16, 1, 1, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base_ptr), gdim, gstr,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(stem row 5d, overlapping strides) failed with CUresult " + std::to_string((int)r));
+    return IDN_ECUDA;
+  }
+  return IDN_OK;
+}
+
+int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const ConvParams& p, int num_sms, cudaStream_t st) {
   const int total = p.num_m_tiles;
   if (total <= 0) return IDN_OK;
   if (p.mode != MODE_STEM || p.num_taps != 7 || p.stem_w == nullptr) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
+  if (p.pool_out != nullptr) {              // conv1 + bn1 + relu + maxpool in one kernel
+    if (p.tiles_w != kSpTilesW || p.tiles_h != kSpTilesH || p.H != 112 || p.W != 112) { set_error("launch_stem_tc: pool fusion needs the 112 x 112 stem"); return IDN_EINVAL; }
+    static bool configured_sp[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured_sp[dev & 63]) {
+      IDN_CUDA_TRY(cudaFuncSetAttribute(stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSpSmemBytes));
+      configured_sp[dev & 63] = true;
+    }
+    const int total_tr = p.nimg * kSpTilesH;
+    const int grid = total_tr < num_sms ? total_tr : num_sms;
+    IDN_CUDA_TRY(launch_pdl(stem_pool_kernel, dim3(grid), dim3(kThreads), (size_t)kSpSmemBytes, st, tmA, tmRow, p));
+    return IDN_OK;
+  }
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);

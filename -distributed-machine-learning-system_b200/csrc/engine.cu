@@ -117,9 +117,8 @@ struct idn_engine {
   bool timing = false;
   bool wait_profile = false;  // timing mode 2: also book per-role pipeline waits (slower kernels)
   int stop_after = -1;      // diagnostic: run the plan up to and including this step
-  // ResNet18: conv1 and the max-pool behind it run as ONE kernel on the product path (the pool is folded
-  // into the stem's epilogue with red.max into a buffer that the preprocess kernel of the same pass has
-  // cleared on the side).
+  // ResNet18: conv1 and the max-pool behind it run as ONE kernel on the product path (stem_pool_kernel:
+  // pooling windows are resolved in shared memory, pooled pixels leave with plain stores).
   int fuse_stem_step = -1, fuse_pool_step = -1, pool_last_reader = -1;
   bf16* pool_buf = nullptr; size_t pool_img_bytes = 0;
   int pool_img_rows = 0, pool_wp = 0;
@@ -343,7 +342,10 @@ static int add_stem(idn_engine* e, const std::string& name, const void* xs, int 
   cp.st_stride = stride; cp.st_ws = ws; cp.st_h = IDN_CROP; cp.st_ow = OW;
   cp.st_nrow = IDN_CROP / stride;
   st.block_n = 64;
-  if (!e->stem_simt) IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
+  if (!e->stem_simt) {
+    IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
+    IDN_TRY(make_tmap_stem_row(&st.tmA2, xs, ws, IDN_CROP, cap));
+  }
   e->steps.push_back(st);
   return IDN_OK;
 }
@@ -659,7 +661,7 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
   else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
   if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
-  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, cp, e->num_sms, st);
+  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, s.tmA2, cp, e->num_sms, st);
   if (s.use_halo) {
     const int item_rows = kBlockM * cp.msub;
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
@@ -687,8 +689,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     switch (s.kind) {
       case STEP_PRE:
         IDN_TRY(launch_preprocess(d_imgs, d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
-                                  e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st,
-                                  fuse ? e->pool_buf : nullptr, fuse ? e->pool_img_bytes : 0));
+                                  e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st));
         break;
       case STEP_CONV:
         if (step_idx == e->fuse_stem_step) {

@@ -159,6 +159,7 @@ struct ConvParams {
   int msub;                   // 128-row sub-tiles per work item (1 or 2)
   FastDiv fd_img_rows, fd_wp, fd_per_img, fd_tiles_w;   // row decode without integer division
   int profile;                // 1: book pipeline-wait cycles per role (bench.py timing mode)
+  int dbg;                    // experiments only (IDN_DBG): switch parts of a kernel off to see what bounds it
   int tc_pair;                // 1: conv_tc_pair_kernel (per-k-block ring on CTA pairs); weight boxes are N/2 rows
   int pair;                   // 1: conv_pair_kernel (CTA pairs, cta_group::2); weight boxes are N/2 rows
   int b_group;                // halo kernel, streamed weights: filter taps per weight stage (1 or 3).  One
@@ -189,7 +190,9 @@ int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner_elems, uint64
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
 int make_tmap_stem(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
 int make_tmap_stem_row(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
-int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const ConvParams& p, int num_sms, cudaStream_t st);
+int make_tmap_stem_band(CUtensorMap* tm, const void* base, int ws_px, int img_h, int nimg_cap);
+int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const CUtensorMap& tmBand, const ConvParams& p,
+                   int num_sms, cudaStream_t st);
 
 // other kernels (pool_head.cu)
 struct PoolParams {
@@ -203,6 +206,9 @@ int launch_maxpool(const PoolParams& p, cudaStream_t st);
 int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
                        const float* fc_w, const float* fc_b, float* feats, float* logits,
                        int32_t* idx, float* prob, cudaStream_t st);
+int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
+                             const float* fc_wt, const float* fc_b, float* logits_out_or_null, int32_t* idx,
+                             float* prob, cudaStream_t st);
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out_or_null,
                         int32_t* idx, float* prob, cudaStream_t st);
 // Copies n_words 32-bit words with SM loads/stores.  Used for the few KB of per-batch records that come

@@ -73,6 +73,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
       ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                            int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tm, uint32_t bar,
                                             int c0, int c1, int c2, int c3) {
   asm volatile(
@@ -1474,8 +1482,13 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
 // =============================================================================================
 // stem_pool_kernel: ResNet18 conv1 + bn1 + relu + maxpool(3, 2, 1) as ONE kernel with plain stores.
 //
-// Same TMA boxes, descriptors and MMA stream as stem_kernel (16 x 8 conv pixels per tile, 14 MMAs).  What
-// differs is who owns which tiles and what the epilogue does.  A CTA walks a contiguous range of "tile
+// The same overlapping no-swizzle descriptors and MMA stream as stem_kernel (16 x 8 conv pixels per tile,
+// 14 MMAs), but the operand is staged ONCE per tile: one TMA box of the 37 input rows x 22 pixels under the
+// tile (6.5 KB).  Conv row g and filter row r read staged row 2 g + r, so filter row r is the same
+// descriptor started r strips further with the strips of consecutive conv rows two strips apart.
+// (stem_kernel loads 16 strips per filter row, 7 boxes = 19.7 KB in 112 short rows per tile; measured, that
+// TMA pattern alone costs ~820 cycles per tile, more than the 14 MMAs.)  Beyond that the kernels differ in
+// who owns which tiles and in what the epilogue does.  A CTA walks a contiguous range of "tile
 // rows" (16 conv rows x 112 columns = 14 tiles) in raster order, so every 3 x 3 pooling window it meets
 // has its upper and left neighbours in tiles the SAME CTA finished a moment ago.  The epilogue keeps just
 // those borders in shared memory:
@@ -1499,6 +1512,7 @@ constexpr int kSpEPix = 17 * 9;
 constexpr int kSpEBytes = kSpEPix * 128;                    // 19584
 constexpr int kSpPRBytes = 112 * 128;                       // 14336
 constexpr int kSpTilesW = 14, kSpTilesH = 7;
+constexpr int kSpBandRows = 2 * kStemTH + 5;                // input rows under a 16-row tile: 2*16 + 7 - 2 = 37
 constexpr int kSpSmemBytes = kSpStages * kStemStageBytes + kStemWBytes + 3 * kSpEBytes + 2 * kSpPRBytes + 512 + 1024;
 
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -1523,7 +1537,7 @@ __device__ __forceinline__ uint32_t sp_chunk(uint32_t buf, int pix, int c16) {
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmRow,
+stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_constant__ CUtensorMap tmRow,
                  const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
@@ -1547,7 +1561,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int tr0 = (int)blockIdx.x * per_cta;
   const int tr1 = min(tr0 + per_cta, total_tr);
 
-  if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmA); ptx::prefetch_tmap(&tmRow); }
+  if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmBand); ptx::prefetch_tmap(&tmRow); }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kSpStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
@@ -1580,14 +1594,12 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int n = tr / kSpTilesH, ty = tr - n * kSpTilesH;
         for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
           if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, tr, p.profile)) { alive = false; break; }
-          ptx::mbar_expect_tx(full_bar(s), 7 * kStemABytes);
           const uint32_t dst = base + s * kStemStageBytes;
-          if (tx >= 0) {
-#pragma unroll
-            for (int r = 0; r < 7; ++r)
-              ptx::tma_load_4d(dst + r * kStemABoxPitch, &tmA, full_bar(s), tx * kStemTW * 8, p.tap_par[r],
-                               ty * kStemTH + p.tap_off[r], n);
+          if (tx >= 0) {      // the 37 input rows x 22 pixels all seven filter rows of the tile read (rows outside the image: zeros)
+            ptx::mbar_expect_tx(full_bar(s), kSpBandRows * kStemStripBytes);
+            ptx::tma_load_3d(dst, &tmBand, full_bar(s), tx * kStemTW * 8, 2 * ty * kStemTH - 3, n);
           } else {            // the conv row above this CTA's first tile row: 14 column blocks of one row
+            ptx::mbar_expect_tx(full_bar(s), 7 * kStemABytes);
 #pragma unroll
             for (int r = 0; r < 7; ++r)
               ptx::tma_load_5d(dst + r * kStemABoxPitch, &tmRow, full_bar(s), 0, 0, p.tap_par[r],
@@ -1613,13 +1625,18 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (!mbar_wait(full_bar(s), ph, 2, tr, p.profile)) { alive = false; break; }
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, kStemStripBytes);
+          // regular tile: conv row g reads staged input row 2 g + r -> strips 2 * 176 bytes apart, filter row r
+          // starts r strips in; one-row tile: 16 strips of filter row r, 176 bytes apart, boxes 3072 bytes apart
+          const uint32_t sbo = tx >= 0 ? 2u * kStemStripBytes : (uint32_t)kStemStripBytes;
+          const uint32_t rstep = tx >= 0 ? (uint32_t)kStemStripBytes : (uint32_t)kStemABoxPitch;
+          const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, sbo);
           const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
 #pragma unroll
           for (int r = 0; r < 7; ++r) {
+            if ((p.dbg & 4) && r > 0) break;
 #pragma unroll
             for (int k = 0; k < 2; ++k)
-              ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * kStemABoxPitch + 32 * k) >> 4),
+              ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * rstep + 32 * k) >> 4),
                              db0 + (uint64_t)((r * 4096 + 2048 * k) >> 4), idesc, (r | k) != 0 ? 1u : 0u);
           }
           ptx::umma_commit(empty_bar(s));
@@ -1677,7 +1694,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             w[2 * j + 0] = relu_bf16x2(pack_bf16x2(a0, a1));      // same rounding as the plain stem
             w[2 * j + 1] = relu_bf16x2(pack_bf16x2(a2, a3));
           }
-          if (tx >= 0) {
+          if (p.dbg & 2) {
+          } else if (tx >= 0) {
             const int e = (g + 1) * 9 + (i + 1);
             sts128(sp_chunk(e_cur, e, 2 * chunk0), w[0], w[1], w[2], w[3]);
             sts128(sp_chunk(e_cur, e, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
@@ -1703,7 +1721,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         epi_bar_sync();
         if (*dead != 0u) { alive = false; break; }
         if (++as == 2) { as = 0; aph ^= 1u; }
-        if (tx < 0) continue;
+        if (tx < 0 || (p.dbg & 1)) { if (tx >= 0) e3 = e3 == 2 ? 0 : e3 + 1; continue; }
         // ---- stage c: pooled pixel (py, px) of the tile, 4 channels per thread
         {
           const int pp = eidx >> 4, q = eidx & 15;
@@ -1935,7 +1953,25 @@ int make_tmap_stem_row(CUtensorMap* tm, const void* base_ptr, int ws_px, int img
   return IDN_OK;
 }
 
-int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const ConvParams& p, int num_sms, cudaStream_t st) {
+// 3-D map (element within an image row, image row, image) for stem_pool_kernel's regular tiles: one box =
+// 37 consecutive input rows x 22 pixels (176 bytes); rows above / below the image read as zeros.
+int make_tmap_stem_band(CUtensorMap* tm, const void* base_ptr, int ws_px, int img_h, int nimg_cap) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return IDN_ECUDA;
+  const uint64_t row = (uint64_t)ws_px * 8;
+  cuuint64_t gdim[3] = {(cuuint64_t)ws_px * 4, (cuuint64_t)img_h, (cuuint64_t)nimg_cap};
+  cuuint64_t gstr[2] = {row, (cuuint64_t)img_h * row};
+  cuuint32_t box[3] = {88, (cuuint32_t)kSpBandRows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base_ptr), gdim, gstr,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(stem band 3d) failed with CUresult " + std::to_string((int)r)); return IDN_ECUDA; }
+  return IDN_OK;
+}
+
+int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const CUtensorMap& tmBand, const ConvParams& p,
+                   int num_sms, cudaStream_t st) {
   const int total = p.num_m_tiles;
   if (total <= 0) return IDN_OK;
   if (p.mode != MODE_STEM || p.num_taps != 7 || p.stem_w == nullptr) { set_error("launch_stem_tc: bad plan"); return IDN_EINVAL; }
@@ -1950,7 +1986,7 @@ int launch_stem_tc(const CUtensorMap& tmA, const CUtensorMap& tmRow, const ConvP
     }
     const int total_tr = p.nimg * kSpTilesH;
     const int grid = total_tr < num_sms ? total_tr : num_sms;
-    IDN_CUDA_TRY(launch_pdl(stem_pool_kernel, dim3(grid), dim3(kThreads), (size_t)kSpSmemBytes, st, tmA, tmRow, p));
+    IDN_CUDA_TRY(launch_pdl(stem_pool_kernel, dim3(grid), dim3(kThreads), (size_t)kSpSmemBytes, st, tmBand, tmRow, p));
     return IDN_OK;
   }
   static bool configured[64] = {false};

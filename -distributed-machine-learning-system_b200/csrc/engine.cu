@@ -108,6 +108,8 @@ struct idn_engine {
   // head
   const bf16* head_act = nullptr; Geom head_g; int head_C = 0;
   float* fc_w = nullptr; float* fc_b = nullptr;        // ResNet fp32 FC
+  float* fc_wt = nullptr;                              // the same weights transposed [512][1000] (fused head)
+  bool no_head_fusion = false;                         // IDN_NO_HEAD_FUSION=1: avgpool, FC, softmax as three kernels
   float* feats = nullptr;                              // ResNet pooled features [cap][512] fp32
   int pre_mode = PRE_OUT_STEM;
   float* logits_pad = nullptr;                         // AlexNet [cap][1024] fp32
@@ -345,6 +347,7 @@ static int add_stem(idn_engine* e, const std::string& name, const void* xs, int 
   if (!e->stem_simt) {
     IDN_TRY(make_tmap_stem(&st.tmA, xs, ws, IDN_CROP, cap));
     IDN_TRY(make_tmap_stem_row(&st.tmA2, xs, ws, IDN_CROP, cap));
+    IDN_TRY(make_tmap_stem_band(&st.tmB, xs, ws, IDN_CROP, cap));
   }
   e->steps.push_back(st);
   return IDN_OK;
@@ -467,6 +470,13 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
   IDN_TRY(dev_alloc(e, &e->feats, (size_t)cap * 512));
   IDN_CUDA_TRY(cudaMemcpy(e->fc_w, fw, (size_t)1000 * 512 * 4, cudaMemcpyHostToDevice));
   IDN_CUDA_TRY(cudaMemcpy(e->fc_b, fb, 4000, cudaMemcpyHostToDevice));
+  {
+    std::vector<float> wt((size_t)512 * 1000);
+    for (int c = 0; c < 1000; ++c)
+      for (int k = 0; k < 512; ++k) wt[(size_t)k * 1000 + c] = fw[(size_t)c * 512 + k];
+    IDN_TRY(dev_alloc(e, &e->fc_wt, wt.size(), false));
+    IDN_CUDA_TRY(cudaMemcpy(e->fc_wt, wt.data(), wt.size() * 4, cudaMemcpyHostToDevice));
+  }
   { Step st; st.kind = STEP_RHEAD; st.name = "avgpool+fc+softmax+top1"; std::memset(&st.cp, 0, sizeof(st.cp)); e->steps.push_back(st); }
   return IDN_OK;
 }
@@ -653,6 +663,7 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   ConvParams& cp = s.cp;
   cp.nimg = n;
   cp.profile = (e->timing && e->wait_profile) ? 1 : 0;
+  { static const int dbg = [] { const char* v = std::getenv("IDN_DBG"); return v ? std::atoi(v) : 0; }(); cp.dbg = dbg; }
   cp.fd_img_rows = make_fastdiv((unsigned)std::max(cp.img_rows, 1));
   cp.fd_wp = make_fastdiv((unsigned)std::max(cp.wp, 1));
   cp.fd_per_img = make_fastdiv((unsigned)std::max(cp.tiles_w * cp.tiles_h, 1));
@@ -661,7 +672,7 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
   else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
   if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
-  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, s.tmA2, cp, e->num_sms, st);
+  if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, s.tmA2, s.tmB, cp, e->num_sms, st);
   if (s.use_halo) {
     const int item_rows = kBlockM * cp.msub;
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
@@ -704,6 +715,11 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
         IDN_TRY(launch_maxpool(s.pp, st));
         break;
       case STEP_RHEAD:
+        if (!e->no_head_fusion) {
+          IDN_TRY(launch_resnet_head_fused(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,
+                                           e->head_g.W, e->head_C, e->fc_wt, e->fc_b, d_logits, d_idx, d_prob, st));
+          break;
+        }
         IDN_TRY(launch_resnet_head(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,
                                    e->head_g.W, e->head_C, e->fc_w, e->fc_b, e->feats,
                                    d_logits ? d_logits : e->d_logits, d_idx, d_prob, st));
@@ -825,6 +841,7 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   e->device = device; e->model = model_id; e->cap = max_batch;
   { const char* v = std::getenv("IDN_STEM_SIMT"); e->stem_simt = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_POOL_FUSION"); e->no_pool_fusion = v && v[0] == '1'; }
+  { const char* v = std::getenv("IDN_NO_HEAD_FUSION"); e->no_head_fusion = v && v[0] == '1'; }
   int rc = IDN_OK;
   auto fail = [&](int code) { idn_engine* raw = e.release(); idn_destroy(raw); return code; };
   {

@@ -1,5 +1,6 @@
-// HBM-bound tail kernels: 3x3/stride-2 max-pool between layouts, ResNet18 head
-// (global average pool + FC + softmax/top-1 in one kernel) and softmax/top-1 over fp32 logits.
+// Tail kernels: 3x3/stride-2 max-pool between layouts, ResNet18 head (global average pool + fp32 FC +
+// softmax/top-1 in ONE kernel on clusters of 4 CTAs; the three-kernel form is kept as its cross-check) and
+// softmax/top-1 over fp32 logits.
 #include "common.cuh"
 
 namespace idn {
@@ -66,7 +67,7 @@ __device__ __forceinline__ void warp_softmax_top1(const float* logits, int lane,
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int q = lane + 32 * i;
-    v[i] = q < kVec ? __ldg(reinterpret_cast<const float4*>(logits) + q)
+    v[i] = q < kVec ? *(reinterpret_cast<const float4*>(logits) + q)       // global or shared memory
                     : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
   }
   float best = -INFINITY;
@@ -250,6 +251,123 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
             make_float4(acc[i][0] + bias.x, acc[i][1] + bias.y, acc[i][2] + bias.z, acc[i][3] + bias.w);
     }
   }
+}
+
+// ------------------------------------------------------------------------ ResNet head, ONE kernel
+// avgpool -> fp32 FC -> softmax / top-1 for 11 images per cluster of 4 CTAs (37 clusters = 148 CTAs at
+// batch 400), nothing but the 8 result bytes per image (and, on request, the logits) leaves the chip:
+//   1. every CTA averages a quarter of the channels of the cluster's 11 images (49 pixels, h then w
+//      ascending, then * 1/49: the order of avgpool_kernel) and stores the fp32 features into the shared
+//      memory of all four CTAs (st.shared::cluster);
+//   2. thread t of CTA r owns class 250 r + t for all 11 images: one coalesced read of the transposed
+//      fp32 weights per k, features broadcast from shared memory, k ascending with fmaf, bias added last
+//      -- the same arithmetic in the same order as fc_fp32_kernel, so the logits are identical bit for bit;
+//      the logits go to the shared memory of the CTA that owns the image (image i -> CTA i % 4);
+//   3. one warp per owned image runs the same warp-shuffle softmax / top-1 as softmax_top1_kernel on the
+//      1000 logits in shared memory.
+constexpr int kHeadImgs = 11, kHeadCluster = 4, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 256;
+constexpr int kHeadOwn = (kHeadImgs + kHeadCluster - 1) / kHeadCluster, kHeadC = 512, kHeadPad = 12;
+
+__device__ __forceinline__ uint32_t head_mapa(const void* p, uint32_t rank) {
+  uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void head_st_remote(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void head_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThreads)
+resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W,
+                   const float* __restrict__ wt /* [512][1000] */, const float* __restrict__ fc_b,
+                   float* __restrict__ logits_out, int32_t* __restrict__ idx, float* __restrict__ prob) {
+  __shared__ __align__(16) float s_feat[kHeadC][kHeadPad];            // [k][image]
+  __shared__ __align__(16) float s_logit[kHeadOwn][IDN_NUM_CLASSES];  // rows of the images this CTA owns
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int img0 = (int)(blockIdx.x / kHeadCluster) * kHeadImgs;
+  const int t = threadIdx.x;
+  pdl_wait();
+  pdl_launch_dependents();
+  // ---- 1. global average pool of channels [128 rank, 128 rank + 128)
+  {
+    const int cp = t & 63, j = t >> 6;
+    const int k0 = 128 * (int)rank + 2 * cp;
+    const float inv = 1.0f / (float)(H * W);
+    for (int im = j; im < kHeadImgs; im += 4) {
+      const int n = img0 + im;
+      float s0 = 0.0f, s1 = 0.0f;
+      if (n < nimg) {
+        const uint32_t* base = reinterpret_cast<const uint32_t*>(act + ((long long)n * img_rows) * kHeadC) + (k0 >> 1);
+        for (int h = 0; h < H; ++h) {
+#pragma unroll 7
+          for (int w = 0; w < W; ++w) {
+            const uint32_t u = __ldg(base + (long long)(h * wp + w) * (kHeadC / 2));
+            s0 += __uint_as_float(u << 16);
+            s1 += __uint_as_float(u & 0xffff0000u);
+          }
+        }
+      }
+#pragma unroll
+      for (uint32_t r = 0; r < (uint32_t)kHeadCluster; ++r) {
+        head_st_remote(head_mapa(&s_feat[k0][im], r), s0 * inv);
+        head_st_remote(head_mapa(&s_feat[k0 + 1][im], r), s1 * inv);
+      }
+    }
+  }
+  head_cluster_sync();
+  // ---- 2. fp32 FC: class c for the cluster's 11 images
+  if (t < kHeadClasses) {
+    const int c = kHeadClasses * (int)rank + t;
+    float acc[kHeadImgs];
+#pragma unroll
+    for (int i = 0; i < kHeadImgs; ++i) acc[i] = 0.0f;
+    const float* wp_ = wt + c;
+#pragma unroll 1
+    for (int k0 = 0; k0 < kHeadC; k0 += 8) {
+      float wv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) wv[u] = __ldg(wp_ + (long long)(k0 + u) * IDN_NUM_CLASSES);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const float4 f0 = *reinterpret_cast<const float4*>(&s_feat[k0 + u][0]);
+        const float4 f1 = *reinterpret_cast<const float4*>(&s_feat[k0 + u][4]);
+        const float4 f2 = *reinterpret_cast<const float4*>(&s_feat[k0 + u][8]);
+        const float fv[12] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w};
+#pragma unroll
+        for (int i = 0; i < kHeadImgs; ++i) acc[i] = fmaf(fv[i], wv[u], acc[i]);
+      }
+    }
+    const float b = __ldg(fc_b + c);
+#pragma unroll
+    for (int i = 0; i < kHeadImgs; ++i)
+      head_st_remote(head_mapa(&s_logit[i / kHeadCluster][c], (uint32_t)(i % kHeadCluster)), acc[i] + b);
+  }
+  head_cluster_sync();
+  // ---- 3. softmax / top-1 of the images this CTA owns: image rank + 4 w by warp w
+  const int warp = t >> 5, lane = t & 31;
+  if (warp < kHeadOwn) {
+    const int im = (int)rank + kHeadCluster * warp;
+    const int n = img0 + im;
+    if (im < kHeadImgs && n < nimg)
+      warp_softmax_top1(&s_logit[warp][0], lane, idx + n, prob + n,
+                        logits_out != nullptr ? logits_out + (long long)n * IDN_NUM_CLASSES : nullptr);
+  }
+}
+
+int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
+                             const float* fc_wt, const float* fc_b, float* logits_out, int32_t* idx,
+                             float* prob, cudaStream_t st) {
+  if (nimg <= 0) return IDN_OK;
+  if (C != kHeadC || fc_wt == nullptr) { set_error("resnet_head: the fused head is built for 512 features"); return IDN_EINVAL; }
+  const int clusters = (nimg + kHeadImgs - 1) / kHeadImgs;
+  IDN_CUDA_TRY(launch_pdl(resnet_head_kernel, dim3(clusters * kHeadCluster), dim3(kHeadThreads), 0, st, act, nimg,
+                          img_rows, wp, H, W, fc_wt, fc_b, logits_out, idx, prob));
+  return IDN_OK;
 }
 
 int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,

@@ -285,3 +285,22 @@ def test_resnet_stem_pool_fusion_is_bit_identical(built_library, monkeypatch):
         j1, q1, m1 = eng.infer(imgs, want_logits=True)
     assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
     assert np.array_equal(l3, l1) and np.array_equal(l2, l1[:7])
+
+
+def test_resnet_head_fusion_is_bit_identical(built_library, monkeypatch):
+    """avgpool + fp32 FC + softmax/top-1 as ONE kernel (clusters of 4 CTAs, 11 images each) against the three
+    separate kernels (IDN_NO_HEAD_FUSION=1): the fused kernel keeps their arithmetic and its order (pixels h, w
+    ascending; k ascending with fmaf; the same warp-shuffle softmax), so logits, classes and probabilities
+    must be identical bit for bit -- for a full cluster, a ragged tail (23 = 2 x 11 + 1) and a single image."""
+    sd = make_state_dict("resnet18", 0, "stress")
+    imgs = [synth_image(i, mixed=True) for i in range(23)]
+    with Engine("resnet18", sd, max_batch=23) as eng:
+        i1, p1, l1 = eng.infer(imgs, want_logits=True)
+        i2, p2, _ = eng.infer(imgs)                      # without the logits copy
+        i3, p3, l3 = eng.infer(imgs[:1], want_logits=True)
+    monkeypatch.setenv("IDN_NO_HEAD_FUSION", "1")
+    with Engine("resnet18", sd, max_batch=23) as eng:
+        j1, q1, m1 = eng.infer(imgs, want_logits=True)
+    assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
+    assert np.array_equal(i2, i1) and np.array_equal(p2, p1)
+    assert np.array_equal(l3, l1[:1]) and np.array_equal(p3, p1[:1])

@@ -1496,11 +1496,13 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
 //           the last conv row above the tile, column 0 = the last conv column left of it (written there by
 //           the previous tile's epilogue);
 //   PR[2] : the last conv row of the previous / of this tile row, 112 pixels.
-// Stage a (all 16 epilogue warps): tcgen05.ld -> scale/shift -> bf16 -> ReLU -> st.shared (16-byte chunks
-// XOR-swizzled by pixel index: conflict free both ways); stage c: each thread takes 4 channels of one of the
-// tile's 32 pooled pixels, reads its nine taps from E and writes 8 bytes -- a warp writes 2 x 128 contiguous
-// bytes.  One named barrier per tile separates a from c; E rotates over three buffers and PR over two so
-// that no second barrier is needed.  Out-of-image taps count as 0, which equals PyTorch's -inf padding
+// Stage a (all 16 epilogue warps): tcgen05.ld -> scale/shift -> bf16 -> st.shared (16-byte chunks XOR-swizzled
+// by pixel column: conflict free both ways); stage c (four of them, one per scheduler, while the others move
+// on to the next tile): a thread takes 4 channels of one pooled column and four pooled rows, reduces the nine
+// conv rows under them horizontally, then vertically, starting from zero (= ReLU), and writes 8 bytes per
+// pooled pixel -- a warp writes 2 x 128 contiguous bytes.  The epilogue is bound by instruction issue, so
+// every address is an offset computed once per kernel.  One named barrier per tile separates a from c; E
+// rotates over three buffers and PR over two so that no second barrier is needed.  Out-of-image taps count as 0, which equals PyTorch's -inf padding
 // because every value is >= 0 after ReLU and every window holds at least its centre.
 // Only the first tile row of a CTA's range can lack its upper neighbour (when the range starts inside an
 // image): that ONE conv row (112 pixels) is recomputed as an extra 1 x 128-pixel tile through a second
@@ -1508,6 +1510,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
 // No red.max, no zero-fill pass, no shuffles; the pooled buffer's padding stays zero from allocation.
 // =============================================================================================
 constexpr int kSpStages = 4;
+constexpr int kSpAcc = 2;                                   // accumulator stages in TMEM (64 columns each)
 constexpr int kSpEPix = 17 * 9;
 constexpr int kSpEBytes = kSpEPix * 128;                    // 19584
 constexpr int kSpPRBytes = 112 * 128;                       // 14336
@@ -1549,8 +1552,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kSpStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kSpStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kSpStages + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kSpStages + 4);
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kSpStages + kSpAcc + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kSpStages + 2 * kSpAcc);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
   volatile uint32_t* dead = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot + 8u - raw_u32));   // "a wait timed out"
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1564,11 +1567,11 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmBand); ptx::prefetch_tmap(&tmRow); }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kSpStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
+    for (int a = 0; a < kSpAcc; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
     ptx::fence_barrier_init();
     *dead = 0u;
   }
-  if (warp == 2) ptx::tmem_alloc<128>(tmem_slot);
+  if (warp == 2) ptx::tmem_alloc<kSpAcc * 64>(tmem_slot);
   {   // resident weights (already in shared-memory order); borders start as zeros
     const uint4* src = reinterpret_cast<const uint4*>(p.stem_w);
     uint4* dst = reinterpret_cast<uint4*>(smem_raw + (w_base - raw_u32));
@@ -1593,7 +1596,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       for (int tr = tr0; tr < tr1 && alive; ++tr) {
         const int n = tr / kSpTilesH, ty = tr - n * kSpTilesH;
         for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
-          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, tr, p.profile)) { alive = false; break; }
+          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, tr, 0)) { alive = false; break; }
           const uint32_t dst = base + s * kStemStageBytes;
           if (tx >= 0) {      // the 37 input rows x 22 pixels all seven filter rows of the tile read (rows outside the image: zeros)
             ptx::mbar_expect_tx(full_bar(s), kSpBandRows * kStemStripBytes);
@@ -1616,14 +1619,18 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
     int s = 0, as = 0;
     uint32_t ph = 0, aph = 0;
     bool alive = true;
+    long long pc0 = 0, pc1 = 0, pc2 = 0;     // profile: cycles waiting for the epilogue / for TMA / issuing
     for (int tr = tr0; tr < tr1 && alive; ++tr) {
       const int ty = tr % kSpTilesH;
       for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
-        if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tr, p.profile)) { alive = false; break; }
+        const long long q0 = p.profile ? clock64() : 0ll;
+        if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tr, 0)) { alive = false; break; }
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * 64);
-        if (!mbar_wait(full_bar(s), ph, 2, tr, p.profile)) { alive = false; break; }
+        const long long q1 = p.profile ? clock64() : 0ll;
+        if (!mbar_wait(full_bar(s), ph, 2, tr, 0)) { alive = false; break; }
         ptx::tc_fence_after();
+        const long long q2 = p.profile ? clock64() : 0ll;
         if (ptx::elect_one()) {
           // regular tile: conv row g reads staged input row 2 g + r -> strips 2 * 176 bytes apart, filter row r
           // starts r strips in; one-row tile: 16 strips of filter row r, 176 bytes apart, boxes 3072 bytes apart
@@ -1643,12 +1650,19 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
           ptx::umma_commit(tfull_bar(as));
         }
         __syncwarp();
+        if (p.profile) { const long long q3 = clock64(); pc0 += q1 - q0; pc1 += q2 - q1; pc2 += q3 - q2; }
         if (++s == kSpStages) { s = 0; ph ^= 1u; }
-        if (++as == 2) { as = 0; aph ^= 1u; }
+        if (++as == kSpAcc) { as = 0; aph ^= 1u; }
       }
     }
+    if (p.profile && lane == 0) {
+      atomicAdd(&g_tc_wait_cycles[1], (unsigned long long)pc0);
+      atomicAdd(&g_tc_wait_cycles[2], (unsigned long long)pc1);
+      atomicAdd(&g_tc_wait_cycles[0], (unsigned long long)pc2);
+    }
   } else if (warp >= 4) {
-    // ================================ epilogue: BN + ReLU -> shared memory -> 3x3/s2 max -> global ========
+    // ================================ epilogue: BN -> shared memory -> max(0, 3x3/s2 window) -> global =======
+    // ReLU is not applied pixel by pixel: max(0, window of rounded values) == window maximum of the ReLU'd values.
     const int ew = (warp - 4) & 3;           // TMEM lane quarter
     const int chunk0 = (warp - 4) >> 2;      // 16-channel chunk of this warp
     const int eidx = (warp - 4) * 32 + lane; // 0..511
@@ -1656,6 +1670,30 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
     const int g = m >> 3, i = m & 7;
     ChunkAffine aff;
     aff.load(p, chunk0 * 16);
+    // Everything below is an offset that does not change from tile to tile.  16-byte chunk c of a pixel in
+    // column x of E (or of PR) sits at chunk c ^ (x & 7): eight neighbouring columns never share banks, and a
+    // column keeps its swizzle from row to row (rows are 9 * 128 bytes apart: immediate offsets).
+    const uint32_t c0 = (uint32_t)(2 * chunk0), c1 = c0 + 1u;
+    const uint32_t swz = (uint32_t)((i + 1) & 7);
+    const uint32_t off_a0 = (uint32_t)((g + 1) * 9 + i + 1) * 128u + ((c0 ^ swz) << 4);
+    const uint32_t off_a1 = (uint32_t)((g + 1) * 9 + i + 1) * 128u + ((c1 ^ swz) << 4);
+    const uint32_t off_n0 = (uint32_t)((g + 1) * 9) * 128u + (c0 << 4);            // column 0 of the next tile's E
+    const uint32_t off_n1 = (uint32_t)((g + 1) * 9) * 128u + (c1 << 4);
+    const uint32_t off_p0 = (uint32_t)i * 128u + ((c0 ^ (uint32_t)i) << 4);         // PR, column 8 tx + i
+    const uint32_t off_p1 = (uint32_t)i * 128u + ((c1 ^ (uint32_t)i) << 4);
+    // row 0 of E <- PR columns 8 tx - 1 .. 8 tx + 7 (threads 0..71: pixel j, chunk cc)
+    const int cj = eidx >> 3;
+    const uint32_t cc = (uint32_t)(eidx & 7);
+    const uint32_t off_r0_dst = (uint32_t)cj * 128u + ((cc ^ (uint32_t)(cj & 7)) << 4);
+    const int off_r0_src = (cj - 1) * 128 + (int)((cc ^ (uint32_t)((cj + 7) & 7)) << 4);
+    // pooling threads (warps 4..7, one per scheduler): pooled column px, 4 channels q, pooled rows 4 half .. 4 half + 3
+    const bool pooler = chunk0 == 0;
+    const int q = m & 15, px = (m >> 4) & 3, half = m >> 6;
+    uint32_t off_c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      off_c[k] = (uint32_t)(8 * half * 9 + 2 * px + k) * 128u + ((((uint32_t)q >> 1) ^ (uint32_t)((2 * px + k) & 7)) << 4) +
+                 (uint32_t)((q & 1) << 3);
     int as = 0, e3 = 0;
     uint32_t aph = 0;
     bool alive = true;
@@ -1663,20 +1701,18 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       const int n = tr / kSpTilesH, ty = tr - n * kSpTilesH;
       const uint32_t pr_cur = pr_base + (uint32_t)(((tr - tr0) & 1) * kSpPRBytes);        // row above this tile row
       const uint32_t pr_next = pr_base + (uint32_t)((((tr - tr0) & 1) ^ 1) * kSpPRBytes); // this tile row's last row
+      bf16* const out_row = p.pool_out + ((long long)n * p.pool_img_rows + (long long)(ty * 8 + 4 * half) * p.pool_wp + px) * 64 + q * 4;
       for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
         const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * 64 + chunk0 * 16);
         const uint32_t e_cur = e_base + (uint32_t)(e3 * kSpEBytes);
         const uint32_t e_nxt = e_base + (uint32_t)((e3 == 2 ? 0 : e3 + 1) * kSpEBytes);
         // ---- stage a
         if (tx >= 0 && eidx < 72) {            // row 0 of E: the conv row above the tile, columns x0-1 .. x0+7
-          const int j = eidx >> 3, c = eidx & 7;
-          const int col = tx * 8 - 1 + j;
           uint4 v = make_uint4(0u, 0u, 0u, 0u);
-          if (ty > 0 && col >= 0) v = lds128(sp_chunk(pr_cur, col, c));
-          sts128(sp_chunk(e_cur, j, c), v.x, v.y, v.z, v.w);
+          if (ty > 0 && (tx > 0 || cj > 0)) v = lds128((uint32_t)((int)pr_cur + tx * 1024 + off_r0_src));
+          sts128(e_cur + off_r0_dst, v.x, v.y, v.z, v.w);
         }
-        const bool ok = mbar_wait(tfull_bar(as), aph, 3, tr, p.profile);
-        if (ok) {
+        if (mbar_wait(tfull_bar(as), aph, 3, tr, 0)) {
           ptx::tc_fence_after();
           uint32_t v[16];
           ptx::tmem_ld_32x32b_x16(taddr, v);
@@ -1687,59 +1723,54 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
           uint32_t w[8];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const float a0 = fmaf(__uint_as_float(v[4 * j + 0]), aff.s4[j].x, aff.b4[j].x);
-            const float a1 = fmaf(__uint_as_float(v[4 * j + 1]), aff.s4[j].y, aff.b4[j].y);
-            const float a2 = fmaf(__uint_as_float(v[4 * j + 2]), aff.s4[j].z, aff.b4[j].z);
-            const float a3 = fmaf(__uint_as_float(v[4 * j + 3]), aff.s4[j].w, aff.b4[j].w);
-            w[2 * j + 0] = relu_bf16x2(pack_bf16x2(a0, a1));      // same rounding as the plain stem
-            w[2 * j + 1] = relu_bf16x2(pack_bf16x2(a2, a3));
+            w[2 * j + 0] = pack_bf16x2(fmaf(__uint_as_float(v[4 * j + 0]), aff.s4[j].x, aff.b4[j].x),
+                                       fmaf(__uint_as_float(v[4 * j + 1]), aff.s4[j].y, aff.b4[j].y));
+            w[2 * j + 1] = pack_bf16x2(fmaf(__uint_as_float(v[4 * j + 2]), aff.s4[j].z, aff.b4[j].z),
+                                       fmaf(__uint_as_float(v[4 * j + 3]), aff.s4[j].w, aff.b4[j].w));
           }
-          if (p.dbg & 2) {
-          } else if (tx >= 0) {
-            const int e = (g + 1) * 9 + (i + 1);
-            sts128(sp_chunk(e_cur, e, 2 * chunk0), w[0], w[1], w[2], w[3]);
-            sts128(sp_chunk(e_cur, e, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
+          if (tx >= 0) {
+            sts128(e_cur + off_a0, w[0], w[1], w[2], w[3]);
+            sts128(e_cur + off_a1, w[4], w[5], w[6], w[7]);
             if (i == 7) {                       // column 0 of the next tile's E (zeros at the start of a tile row)
-              const int e0 = (g + 1) * 9;
               const uint32_t keep = tx == kSpTilesW - 1 ? 0u : 0xffffffffu;
-              sts128(sp_chunk(e_nxt, e0, 2 * chunk0), w[0] & keep, w[1] & keep, w[2] & keep, w[3] & keep);
-              sts128(sp_chunk(e_nxt, e0, 2 * chunk0 + 1), w[4] & keep, w[5] & keep, w[6] & keep, w[7] & keep);
+              sts128(e_nxt + off_n0, w[0] & keep, w[1] & keep, w[2] & keep, w[3] & keep);
+              sts128(e_nxt + off_n1, w[4] & keep, w[5] & keep, w[6] & keep, w[7] & keep);
             }
             if (g == 15) {                      // last conv row of this tile row
-              const int col = tx * 8 + i;
-              sts128(sp_chunk(pr_next, col, 2 * chunk0), w[0], w[1], w[2], w[3]);
-              sts128(sp_chunk(pr_next, col, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
+              sts128(pr_next + (uint32_t)(tx * 1024) + off_p0, w[0], w[1], w[2], w[3]);
+              sts128(pr_next + (uint32_t)(tx * 1024) + off_p1, w[4], w[5], w[6], w[7]);
             }
           } else if (g < kSpTilesW) {           // the recomputed row: accumulator row 8 g + i is column 8 g + i
-            const int col = g * 8 + i;
-            sts128(sp_chunk(pr_cur, col, 2 * chunk0), w[0], w[1], w[2], w[3]);
-            sts128(sp_chunk(pr_cur, col, 2 * chunk0 + 1), w[4], w[5], w[6], w[7]);
+            sts128(pr_cur + (uint32_t)(g * 1024) + off_p0, w[0], w[1], w[2], w[3]);
+            sts128(pr_cur + (uint32_t)(g * 1024) + off_p1, w[4], w[5], w[6], w[7]);
           }
         } else {
           *dead = 1u;
         }
         epi_bar_sync();
         if (*dead != 0u) { alive = false; break; }
-        if (++as == 2) { as = 0; aph ^= 1u; }
-        if (tx < 0 || (p.dbg & 1)) { if (tx >= 0) e3 = e3 == 2 ? 0 : e3 + 1; continue; }
-        // ---- stage c: pooled pixel (py, px) of the tile, 4 channels per thread
-        {
-          const int pp = eidx >> 4, q = eidx & 15;
-          const int py = pp >> 2, px = pp & 3;
-          uint2 mx = make_uint2(0u, 0u);
+        if (++as == kSpAcc) { as = 0; aph ^= 1u; }
+        if (tx < 0) continue;
+        // ---- stage c (one warp per scheduler; the other warps go on to the next tile): horizontal 3-max of the
+        //      nine conv rows under four pooled rows, then vertical 3-max, ReLU by starting from zero
+        if (pooler) {
+          uint2 h[9];
 #pragma unroll
-          for (int dy = 0; dy < 3; ++dy) {
-#pragma unroll
-            for (int dx = 0; dx < 3; ++dx) {
-              const int e = (2 * py + dy) * 9 + 2 * px + dx;
-              const uint2 t = lds64(sp_chunk(e_cur, e, q >> 1) + (uint32_t)((q & 1) << 3));
-              mx.x = max_bf16x2(mx.x, t.x);
-              mx.y = max_bf16x2(mx.y, t.y);
-            }
+          for (int r = 0; r < 9; ++r) {
+            const uint2 a = lds64(e_cur + off_c[0] + (uint32_t)(r * 9 * 128));
+            const uint2 b = lds64(e_cur + off_c[1] + (uint32_t)(r * 9 * 128));
+            const uint2 c = lds64(e_cur + off_c[2] + (uint32_t)(r * 9 * 128));
+            h[r].x = max_bf16x2(max_bf16x2(a.x, b.x), c.x);
+            h[r].y = max_bf16x2(max_bf16x2(a.y, b.y), c.y);
           }
-          const int P = ty * 8 + py, Q = tx * 4 + px;
-          uint2* dst = reinterpret_cast<uint2*>(p.pool_out + ((long long)n * p.pool_img_rows + (long long)P * p.pool_wp + Q) * 64) + q;
-          *dst = mx;
+          bf16* dst = out_row + (long long)(tx * 4) * 64;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint2 o;
+            o.x = max_bf16x2(max_bf16x2(max_bf16x2(h[2 * j].x, h[2 * j + 1].x), h[2 * j + 2].x), 0u);
+            o.y = max_bf16x2(max_bf16x2(max_bf16x2(h[2 * j].y, h[2 * j + 1].y), h[2 * j + 2].y), 0u);
+            *reinterpret_cast<uint2*>(dst + (long long)j * p.pool_wp * 64) = o;
+          }
         }
         e3 = e3 == 2 ? 0 : e3 + 1;
       }
@@ -1749,7 +1780,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   __syncthreads();
   if (warp == 2) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc<128>(tmem_base);
+    ptx::tmem_dealloc<kSpAcc * 64>(tmem_base);
   }
 }
 

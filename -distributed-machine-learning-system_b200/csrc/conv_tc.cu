@@ -1615,50 +1615,74 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
     __syncwarp();
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
+    // One pipeline round = one tile = 14 MMAs.  The two barrier waits of the NEXT tile (~100 cycles each even
+    // when they succeed at once) are taken after the tenth MMA of the current one, while the tensor pipe still
+    // has queued work; the commits of the current tile follow its last MMA as before.
     constexpr uint32_t idesc = make_idesc(kBlockM, 64);
+    constexpr int kSplit = 5;                 // filter rows issued before the look-ahead waits
+    const bool has_halo = tr0 < tr1 && (tr0 % kSpTilesH) > 0;
+    const int ntiles = tr0 < tr1 ? (tr1 - tr0) * kSpTilesW + (has_halo ? 1 : 0) : 0;
     int s = 0, as = 0;
     uint32_t ph = 0, aph = 0;
-    bool alive = true;
-    long long pc0 = 0, pc1 = 0, pc2 = 0;     // profile: cycles waiting for the epilogue / for TMA / issuing
-    for (int tr = tr0; tr < tr1 && alive; ++tr) {
-      const int ty = tr % kSpTilesH;
-      for (int tx = (tr == tr0 && ty > 0) ? -1 : 0; tx < kSpTilesW; ++tx) {
-        const long long q0 = p.profile ? clock64() : 0ll;
-        if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tr, 0)) { alive = false; break; }
-        ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(as * 64);
-        const long long q1 = p.profile ? clock64() : 0ll;
-        if (!mbar_wait(full_bar(s), ph, 2, tr, 0)) { alive = false; break; }
-        ptx::tc_fence_after();
-        const long long q2 = p.profile ? clock64() : 0ll;
-        if (ptx::elect_one()) {
-          // regular tile: conv row g reads staged input row 2 g + r -> strips 2 * 176 bytes apart, filter row r
-          // starts r strips in; one-row tile: 16 strips of filter row r, 176 bytes apart, boxes 3072 bytes apart
-          const uint32_t sbo = tx >= 0 ? 2u * kStemStripBytes : (uint32_t)kStemStripBytes;
-          const uint32_t rstep = tx >= 0 ? (uint32_t)kStemStripBytes : (uint32_t)kStemABoxPitch;
-          const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, sbo);
-          const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
+    long long pc_wait = 0, pc_issue = 0;
+    auto wait_tile = [&](int s_, uint32_t ph_, int as_, uint32_t aph_, int t) -> bool {
+      const long long q0 = p.profile ? clock64() : 0ll;
+      const bool ok = mbar_wait(tempty_bar(as_), aph_ ^ 1u, 1, t, 0) && mbar_wait(full_bar(s_), ph_, 2, t, 0);
+      ptx::tc_fence_after();
+      if (p.profile) pc_wait += clock64() - q0;
+      return ok;
+    };
+    bool alive = ntiles > 0 && wait_tile(0, 0u, 0, 0u, 0);
+    for (int t = 0; t < ntiles && alive; ++t) {
+      const bool regular = !(has_halo && t == 0);
+      // regular tile: conv row g reads staged input row 2 g + r -> strips 2 * 176 bytes apart, filter row r
+      // starts r strips in; one-row tile: 16 strips of filter row r, 176 bytes apart, boxes 3072 bytes apart
+      const uint32_t sbo = regular ? 2u * kStemStripBytes : (uint32_t)kStemStripBytes;
+      const uint32_t rstep = regular ? (uint32_t)kStemStripBytes : (uint32_t)kStemABoxPitch;
+      const uint32_t d_tmem = tmem_base + (uint32_t)(as * 64);
+      const long long q1 = p.profile ? clock64() : 0ll;
+      if (ptx::elect_one()) {
+        const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, sbo);
+        const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
 #pragma unroll
-          for (int r = 0; r < 7; ++r) {
-            if ((p.dbg & 4) && r > 0) break;
+        for (int r = 0; r < kSplit; ++r) {
+          if ((p.dbg & 4) && r > 0) break;
 #pragma unroll
-            for (int k = 0; k < 2; ++k)
-              ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * rstep + 32 * k) >> 4),
-                             db0 + (uint64_t)((r * 4096 + 2048 * k) >> 4), idesc, (r | k) != 0 ? 1u : 0u);
-          }
-          ptx::umma_commit(empty_bar(s));
-          ptx::umma_commit(tfull_bar(as));
+          for (int k = 0; k < 2; ++k)
+            ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * rstep + 32 * k) >> 4),
+                           db0 + (uint64_t)((r * 4096 + 2048 * k) >> 4), idesc, (r | k) != 0 ? 1u : 0u);
         }
-        __syncwarp();
-        if (p.profile) { const long long q3 = clock64(); pc0 += q1 - q0; pc1 += q2 - q1; pc2 += q3 - q2; }
-        if (++s == kSpStages) { s = 0; ph ^= 1u; }
-        if (++as == kSpAcc) { as = 0; aph ^= 1u; }
       }
+      __syncwarp();
+      if (p.profile) pc_issue += clock64() - q1;
+      int ns = s + 1, nas = as + 1;
+      uint32_t nph = ph, naph = aph;
+      if (ns == kSpStages) { ns = 0; nph ^= 1u; }
+      if (nas == kSpAcc) { nas = 0; naph ^= 1u; }
+      if (t + 1 < ntiles && !(p.dbg & 32)) alive = wait_tile(ns, nph, nas, naph, t + 1);
+      const long long q2 = p.profile ? clock64() : 0ll;
+      if (ptx::elect_one()) {
+        const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, sbo);
+        const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
+#pragma unroll
+        for (int r = kSplit; r < 7; ++r) {
+          if (p.dbg & 4) break;
+#pragma unroll
+          for (int k = 0; k < 2; ++k)
+            ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * rstep + 32 * k) >> 4),
+                           db0 + (uint64_t)((r * 4096 + 2048 * k) >> 4), idesc, 1u);
+        }
+        ptx::umma_commit(empty_bar(s));
+        ptx::umma_commit(tfull_bar(as));
+      }
+      __syncwarp();
+      if (p.profile) pc_issue += clock64() - q2;
+      if (t + 1 < ntiles && (p.dbg & 32)) alive = wait_tile(ns, nph, nas, naph, t + 1);
+      s = ns; ph = nph; as = nas; aph = naph;
     }
     if (p.profile && lane == 0) {
-      atomicAdd(&g_tc_wait_cycles[1], (unsigned long long)pc0);
-      atomicAdd(&g_tc_wait_cycles[2], (unsigned long long)pc1);
-      atomicAdd(&g_tc_wait_cycles[0], (unsigned long long)pc2);
+      atomicAdd(&g_tc_wait_cycles[1], (unsigned long long)pc_wait);
+      atomicAdd(&g_tc_wait_cycles[0], (unsigned long long)pc_issue);
     }
   } else if (warp >= 4) {
     // ================================ epilogue: BN -> shared memory -> max(0, 3x3/s2 window) -> global =======

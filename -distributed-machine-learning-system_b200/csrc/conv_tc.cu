@@ -1510,6 +1510,10 @@ stem_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ Con
 // No red.max, no zero-fill pass, no shuffles; the pooled buffer's padding stays zero from allocation.
 // =============================================================================================
 constexpr int kSpStages = 4;
+// Warp roles.  Within a scheduler the highest warp id wins the issue slot (measured on this architecture), so
+// the two warps everything else waits for -- the MMA issuer and the TMA producer -- are the LAST warps of the
+// CTA; as warps 0..3 they lost a quarter of the MMA warp's time to the epilogue warps sharing its scheduler.
+constexpr int kSpWarpTma = kEpiWarps, kSpWarpMma = kEpiWarps + 1, kSpWarpTmem = kEpiWarps + 2;
 constexpr int kSpAcc = 2;                                   // accumulator stages in TMEM (64 columns each)
 constexpr int kSpEPix = 17 * 9;
 constexpr int kSpEBytes = kSpEPix * 128;                    // 19584
@@ -1564,14 +1568,14 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   const int tr0 = (int)blockIdx.x * per_cta;
   const int tr1 = min(tr0 + per_cta, total_tr);
 
-  if (warp == 0 && lane == 0) { ptx::prefetch_tmap(&tmBand); ptx::prefetch_tmap(&tmRow); }
-  if (warp == 1 && lane == 0) {
+  if (warp == kSpWarpTma && lane == 0) { ptx::prefetch_tmap(&tmBand); ptx::prefetch_tmap(&tmRow); }
+  if (warp == kSpWarpMma && lane == 0) {
     for (int s = 0; s < kSpStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < kSpAcc; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), kEpiWarps); }
     ptx::fence_barrier_init();
     *dead = 0u;
   }
-  if (warp == 2) ptx::tmem_alloc<kSpAcc * 64>(tmem_slot);
+  if (warp == kSpWarpTmem) ptx::tmem_alloc<kSpAcc * 64>(tmem_slot);
   {   // resident weights (already in shared-memory order); borders start as zeros
     const uint4* src = reinterpret_cast<const uint4*>(p.stem_w);
     uint4* dst = reinterpret_cast<uint4*>(smem_raw + (w_base - raw_u32));
@@ -1586,8 +1590,10 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   const uint32_t tmem_base = *tmem_slot_ptr;
   pdl_wait();
   pdl_launch_dependents();
+  const long long k_c0 = p.profile ? clock64() : 0ll;                       // profile: SM clock against wall time
+  const unsigned long long k_t0 = p.profile ? ptx::globaltimer() : 0ull;
 
-  if (warp == 0) {
+  if (warp == kSpWarpTma) {
     // ================================ TMA producer ================================
     if (lane == 0) {
       int s = 0;
@@ -1613,7 +1619,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
+  } else if (warp == kSpWarpMma) {
     // ================================ MMA issuer ==================================
     // One pipeline round = one tile = 14 MMAs.  The two barrier waits of the NEXT tile (~100 cycles each even
     // when they succeed at once) are taken after the tenth MMA of the current one, while the tensor pipe still
@@ -1632,6 +1638,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       if (p.profile) pc_wait += clock64() - q0;
       return ok;
     };
+    const long long q_loop0 = p.profile ? clock64() : 0ll;
     bool alive = ntiles > 0 && wait_tile(0, 0u, 0, 0u, 0);
     for (int t = 0; t < ntiles && alive; ++t) {
       const bool regular = !(has_halo && t == 0);
@@ -1683,13 +1690,14 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
     if (p.profile && lane == 0) {
       atomicAdd(&g_tc_wait_cycles[1], (unsigned long long)pc_wait);
       atomicAdd(&g_tc_wait_cycles[0], (unsigned long long)pc_issue);
+      atomicAdd(&g_tc_wait_cycles[5], (unsigned long long)(clock64() - q_loop0));     // the MMA warp's whole loop
     }
-  } else if (warp >= 4) {
+  } else if (warp < kEpiWarps) {
     // ================================ epilogue: BN -> shared memory -> max(0, 3x3/s2 window) -> global =======
     // ReLU is not applied pixel by pixel: max(0, window of rounded values) == window maximum of the ReLU'd values.
-    const int ew = (warp - 4) & 3;           // TMEM lane quarter
-    const int chunk0 = (warp - 4) >> 2;      // 16-channel chunk of this warp
-    const int eidx = (warp - 4) * 32 + lane; // 0..511
+    const int ew = warp & 3;                 // TMEM lane quarter (a warp reaches lanes 32 (wid % 4) .. + 31 only)
+    const int chunk0 = warp >> 2;            // 16-channel chunk of this warp
+    const int eidx = warp * 32 + lane;       // 0..511
     const int m = ew * 32 + lane;            // accumulator row = 8 g + i
     const int g = m >> 3, i = m & 7;
     ChunkAffine aff;
@@ -1710,7 +1718,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
     const uint32_t cc = (uint32_t)(eidx & 7);
     const uint32_t off_r0_dst = (uint32_t)cj * 128u + ((cc ^ (uint32_t)(cj & 7)) << 4);
     const int off_r0_src = (cj - 1) * 128 + (int)((cc ^ (uint32_t)((cj + 7) & 7)) << 4);
-    // pooling threads (warps 4..7, one per scheduler): pooled column px, 4 channels q, pooled rows 4 half .. 4 half + 3
+    // pooling threads (warps 0..3, one per scheduler): pooled column px, 4 channels q, pooled rows 4 half .. 4 half + 3
     const bool pooler = chunk0 == 0;
     const int q = m & 15, px = (m >> 4) & 3, half = m >> 6;
     uint32_t off_c[3];
@@ -1802,7 +1810,17 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (p.profile && threadIdx.x == 0) {
+    const unsigned long long dc = (unsigned long long)(clock64() - k_c0);
+    atomicAdd(&g_tc_wait_cycles[2], dc);                                            // sum over CTAs of main-part cycles
+    atomicMax(&g_tc_wait_cycles[3], dc);                                            // slowest CTA
+    atomicMax(&g_tc_wait_cycles[4], 0xffffffffull - dc);                            // fastest CTA (complement)
+    if (blockIdx.x == 0) {
+      atomicAdd(&g_tc_wait_cycles[6], dc);                                          // CTA 0: cycles ...
+      atomicAdd(&g_tc_wait_cycles[7], ptx::globaltimer() - k_t0);                   // ... and nanoseconds
+    }
+  }
+  if (warp == kSpWarpTmem) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc<kSpAcc * 64>(tmem_base);
   }

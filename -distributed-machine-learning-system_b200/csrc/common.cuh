@@ -159,7 +159,6 @@ struct ConvParams {
   int msub;                   // 128-row sub-tiles per work item (1 or 2)
   FastDiv fd_img_rows, fd_wp, fd_per_img, fd_tiles_w;   // row decode without integer division
   int profile;                // 1: book pipeline-wait cycles per role (bench.py timing mode)
-  int dbg;                    // experiments only (IDN_DBG): switch parts of a kernel off to see what bounds it
   int tc_pair;                // 1: conv_tc_pair_kernel (per-k-block ring on CTA pairs); weight boxes are N/2 rows
   int pair;                   // 1: conv_pair_kernel (CTA pairs, cta_group::2); weight boxes are N/2 rows
   int b_group;                // halo kernel, streamed weights: filter taps per weight stage (1 or 3).  One

@@ -1638,7 +1638,6 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       if (p.profile) pc_wait += clock64() - q0;
       return ok;
     };
-    const long long q_loop0 = p.profile ? clock64() : 0ll;
     bool alive = ntiles > 0 && wait_tile(0, 0u, 0, 0u, 0);
     for (int t = 0; t < ntiles && alive; ++t) {
       const bool regular = !(has_halo && t == 0);
@@ -1653,7 +1652,6 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
         const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
 #pragma unroll
         for (int r = 0; r < kSplit; ++r) {
-          if ((p.dbg & 4) && r > 0) break;
 #pragma unroll
           for (int k = 0; k < 2; ++k)
             ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * rstep + 32 * k) >> 4),
@@ -1666,14 +1664,13 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       uint32_t nph = ph, naph = aph;
       if (ns == kSpStages) { ns = 0; nph ^= 1u; }
       if (nas == kSpAcc) { nas = 0; naph ^= 1u; }
-      if (t + 1 < ntiles && !(p.dbg & 32)) alive = wait_tile(ns, nph, nas, naph, t + 1);
+      if (t + 1 < ntiles) alive = wait_tile(ns, nph, nas, naph, t + 1);
       const long long q2 = p.profile ? clock64() : 0ll;
       if (ptx::elect_one()) {
         const uint64_t da0 = make_nosw_desc(base + s * kStemStageBytes, 16u, sbo);
         const uint64_t db0 = make_nosw_desc(w_base, 1024u, 128u);
 #pragma unroll
         for (int r = kSplit; r < 7; ++r) {
-          if (p.dbg & 4) break;
 #pragma unroll
           for (int k = 0; k < 2; ++k)
             ptx::umma_bf16(d_tmem, da0 + (uint64_t)((r * rstep + 32 * k) >> 4),
@@ -1684,13 +1681,11 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
       }
       __syncwarp();
       if (p.profile) pc_issue += clock64() - q2;
-      if (t + 1 < ntiles && (p.dbg & 32)) alive = wait_tile(ns, nph, nas, naph, t + 1);
       s = ns; ph = nph; as = nas; aph = naph;
     }
     if (p.profile && lane == 0) {
       atomicAdd(&g_tc_wait_cycles[1], (unsigned long long)pc_wait);
       atomicAdd(&g_tc_wait_cycles[0], (unsigned long long)pc_issue);
-      atomicAdd(&g_tc_wait_cycles[5], (unsigned long long)(clock64() - q_loop0));     // the MMA warp's whole loop
     }
   } else if (warp < kEpiWarps) {
     // ================================ epilogue: BN -> shared memory -> max(0, 3x3/s2 window) -> global =======
@@ -1811,13 +1806,11 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmBand, const __grid_consta
   ptx::tc_fence_before();
   __syncthreads();
   if (p.profile && threadIdx.x == 0) {
-    const unsigned long long dc = (unsigned long long)(clock64() - k_c0);
-    atomicAdd(&g_tc_wait_cycles[2], dc);                                            // sum over CTAs of main-part cycles
-    atomicMax(&g_tc_wait_cycles[3], dc);                                            // slowest CTA
-    atomicMax(&g_tc_wait_cycles[4], 0xffffffffull - dc);                            // fastest CTA (complement)
+    // timing mode: [0] / [1] = cycles the MMA warps spent issuing / in barrier waits (summed over CTAs), and
+    // the main part of CTA 0 in [6] cycles and [7] nanoseconds (their ratio is the SM clock under this load)
     if (blockIdx.x == 0) {
-      atomicAdd(&g_tc_wait_cycles[6], dc);                                          // CTA 0: cycles ...
-      atomicAdd(&g_tc_wait_cycles[7], ptx::globaltimer() - k_t0);                   // ... and nanoseconds
+      atomicAdd(&g_tc_wait_cycles[6], (unsigned long long)(clock64() - k_c0));
+      atomicAdd(&g_tc_wait_cycles[7], ptx::globaltimer() - k_t0);
     }
   }
   if (warp == kSpWarpTmem) {

@@ -663,7 +663,6 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   ConvParams& cp = s.cp;
   cp.nimg = n;
   cp.profile = (e->timing && e->wait_profile) ? 1 : 0;
-  { static const int dbg = [] { const char* v = std::getenv("IDN_DBG"); return v ? std::atoi(v) : 0; }(); cp.dbg = dbg; }
   cp.fd_img_rows = make_fastdiv((unsigned)std::max(cp.img_rows, 1));
   cp.fd_wp = make_fastdiv((unsigned)std::max(cp.wp, 1));
   cp.fd_per_img = make_fastdiv((unsigned)std::max(cp.tiles_w * cp.tiles_h, 1));

@@ -259,13 +259,15 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
 //   1. every CTA averages a quarter of the channels of the cluster's 11 images (49 pixels, h then w
 //      ascending, then * 1/49: the order of avgpool_kernel) and stores the fp32 features into the shared
 //      memory of all four CTAs (st.shared::cluster);
-//   2. thread t of CTA r owns class 250 r + t for all 11 images: one coalesced read of the transposed
-//      fp32 weights per k, features broadcast from shared memory, k ascending with fmaf, bias added last
+//   2. thread (t, group) of CTA r owns class 250 r + t for 6 (5) of the 11 images: one coalesced read of the
+//      transposed fp32 weights per k (fetched a block of 8 ahead), features broadcast from shared memory, k
+//      ascending with fmaf, bias added last
 //      -- the same arithmetic in the same order as fc_fp32_kernel, so the logits are identical bit for bit;
 //      the logits go to the shared memory of the CTA that owns the image (image i -> CTA i % 4);
 //   3. one warp per owned image runs the same warp-shuffle softmax / top-1 as softmax_top1_kernel on the
 //      1000 logits in shared memory.
-constexpr int kHeadImgs = 11, kHeadCluster = 4, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 256;
+constexpr int kHeadImgs = 11, kHeadCluster = 4, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 512;
+constexpr int kHeadHW = 7;
 constexpr int kHeadOwn = (kHeadImgs + kHeadCluster - 1) / kHeadCluster, kHeadC = 512, kHeadPad = 12;
 
 __device__ __forceinline__ uint32_t head_mapa(const void* p, uint32_t rank) {
@@ -282,7 +284,7 @@ __device__ __forceinline__ void head_cluster_sync() {
 }
 
 __global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThreads)
-resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp, int H, int W,
+resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
                    const float* __restrict__ wt /* [512][1000] */, const float* __restrict__ fc_b,
                    float* __restrict__ logits_out, int32_t* __restrict__ idx, float* __restrict__ prob) {
   __shared__ __align__(16) float s_feat[kHeadC][kHeadPad];            // [k][image]
@@ -293,59 +295,83 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
   const int t = threadIdx.x;
   pdl_wait();
   pdl_launch_dependents();
-  // ---- 1. global average pool of channels [128 rank, 128 rank + 128)
-  {
-    const int cp = t & 63, j = t >> 6;
+  // ---- 1. global average pool (7 x 7) of channels [128 rank, 128 rank + 128): thread = (channel pair, image);
+  //         the 49 loads of an image are all in flight before the first add
+  for (int item = t; item < 64 * kHeadImgs; item += kHeadThreads) {
+    const int cp = item & 63, im = item >> 6;
     const int k0 = 128 * (int)rank + 2 * cp;
-    const float inv = 1.0f / (float)(H * W);
-    for (int im = j; im < kHeadImgs; im += 4) {
-      const int n = img0 + im;
-      float s0 = 0.0f, s1 = 0.0f;
-      if (n < nimg) {
-        const uint32_t* base = reinterpret_cast<const uint32_t*>(act + ((long long)n * img_rows) * kHeadC) + (k0 >> 1);
-        for (int h = 0; h < H; ++h) {
-#pragma unroll 7
-          for (int w = 0; w < W; ++w) {
-            const uint32_t u = __ldg(base + (long long)(h * wp + w) * (kHeadC / 2));
-            s0 += __uint_as_float(u << 16);
-            s1 += __uint_as_float(u & 0xffff0000u);
-          }
-        }
-      }
+    const int n = img0 + im;
+    float s0 = 0.0f, s1 = 0.0f;
+    if (n < nimg) {
+      const uint32_t* base = reinterpret_cast<const uint32_t*>(act + ((long long)n * img_rows) * kHeadC) + (k0 >> 1);
+      uint32_t u[kHeadHW * kHeadHW];
 #pragma unroll
-      for (uint32_t r = 0; r < (uint32_t)kHeadCluster; ++r) {
-        head_st_remote(head_mapa(&s_feat[k0][im], r), s0 * inv);
-        head_st_remote(head_mapa(&s_feat[k0 + 1][im], r), s1 * inv);
+      for (int h = 0; h < kHeadHW; ++h)
+#pragma unroll
+        for (int w = 0; w < kHeadHW; ++w) u[h * kHeadHW + w] = __ldg(base + (long long)(h * wp + w) * (kHeadC / 2));
+#pragma unroll
+      for (int j = 0; j < kHeadHW * kHeadHW; ++j) {                 // h, then w, ascending: avgpool_kernel's order
+        s0 += __uint_as_float(u[j] << 16);
+        s1 += __uint_as_float(u[j] & 0xffff0000u);
       }
+    }
+    const float inv = 1.0f / (float)(kHeadHW * kHeadHW);
+#pragma unroll
+    for (uint32_t r = 0; r < (uint32_t)kHeadCluster; ++r) {
+      head_st_remote(head_mapa(&s_feat[k0][im], r), s0 * inv);
+      head_st_remote(head_mapa(&s_feat[k0 + 1][im], r), s1 * inv);
     }
   }
   head_cluster_sync();
-  // ---- 2. fp32 FC: class c for the cluster's 11 images
-  if (t < kHeadClasses) {
-    const int c = kHeadClasses * (int)rank + t;
-    float acc[kHeadImgs];
+  // ---- 2. fp32 FC: thread = (class, image group): threads 0..249 take images 0..5 of class 250 rank + t,
+  //         threads 256..505 images 6..10 (the second group's weight loads hit L1).  k ascending, fmaf, bias last.
+  {
+    const int grp = t >> 8, tc = t & 255;
+    if (tc < kHeadClasses) {
+      const int c = kHeadClasses * (int)rank + tc;
+      const int i0 = grp * 6;                                        // images i0 .. i0 + 5 (the last group has 5)
+      float acc[6];
 #pragma unroll
-    for (int i = 0; i < kHeadImgs; ++i) acc[i] = 0.0f;
-    const float* wp_ = wt + c;
+      for (int i = 0; i < 6; ++i) acc[i] = 0.0f;
+      const float* wp_ = wt + c;
+      float wa[8], wb[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) wa[u] = __ldg(wp_ + (long long)u * IDN_NUM_CLASSES);
 #pragma unroll 1
-    for (int k0 = 0; k0 < kHeadC; k0 += 8) {
-      float wv[8];
+      for (int k0 = 0; k0 < kHeadC; k0 += 16) {                      // two blocks of 8 per trip, loads one block ahead
 #pragma unroll
-      for (int u = 0; u < 8; ++u) wv[u] = __ldg(wp_ + (long long)(k0 + u) * IDN_NUM_CLASSES);
+        for (int u = 0; u < 8; ++u) wb[u] = __ldg(wp_ + (long long)(k0 + 8 + u) * IDN_NUM_CLASSES);
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const float4 f0 = *reinterpret_cast<const float4*>(&s_feat[k0 + u][0]);
-        const float4 f1 = *reinterpret_cast<const float4*>(&s_feat[k0 + u][4]);
-        const float4 f2 = *reinterpret_cast<const float4*>(&s_feat[k0 + u][8]);
-        const float fv[12] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w};
+        for (int u = 0; u < 8; ++u) {
+          const float* f = &s_feat[k0 + u][i0];                      // i0 = 0 or 6: 8-byte aligned
+          const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
+                       f2 = *reinterpret_cast<const float2*>(f + 4);
+          acc[0] = fmaf(f0.x, wa[u], acc[0]); acc[1] = fmaf(f0.y, wa[u], acc[1]);
+          acc[2] = fmaf(f1.x, wa[u], acc[2]); acc[3] = fmaf(f1.y, wa[u], acc[3]);
+          acc[4] = fmaf(f2.x, wa[u], acc[4]); acc[5] = fmaf(f2.y, wa[u], acc[5]);
+        }
+        if (k0 + 16 < kHeadC) {
 #pragma unroll
-        for (int i = 0; i < kHeadImgs; ++i) acc[i] = fmaf(fv[i], wv[u], acc[i]);
+          for (int u = 0; u < 8; ++u) wa[u] = __ldg(wp_ + (long long)(k0 + 16 + u) * IDN_NUM_CLASSES);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float* f = &s_feat[k0 + 8 + u][i0];
+          const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
+                       f2 = *reinterpret_cast<const float2*>(f + 4);
+          acc[0] = fmaf(f0.x, wb[u], acc[0]); acc[1] = fmaf(f0.y, wb[u], acc[1]);
+          acc[2] = fmaf(f1.x, wb[u], acc[2]); acc[3] = fmaf(f1.y, wb[u], acc[3]);
+          acc[4] = fmaf(f2.x, wb[u], acc[4]); acc[5] = fmaf(f2.y, wb[u], acc[5]);
+        }
+      }
+      const float b = __ldg(fc_b + c);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        const int im = i0 + i;
+        if (im < kHeadImgs)
+          head_st_remote(head_mapa(&s_logit[im / kHeadCluster][c], (uint32_t)(im % kHeadCluster)), acc[i] + b);
       }
     }
-    const float b = __ldg(fc_b + c);
-#pragma unroll
-    for (int i = 0; i < kHeadImgs; ++i)
-      head_st_remote(head_mapa(&s_logit[i / kHeadCluster][c], (uint32_t)(i % kHeadCluster)), acc[i] + b);
   }
   head_cluster_sync();
   // ---- 3. softmax / top-1 of the images this CTA owns: image rank + 4 w by warp w
@@ -363,10 +389,13 @@ int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, in
                              const float* fc_wt, const float* fc_b, float* logits_out, int32_t* idx,
                              float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  if (C != kHeadC || fc_wt == nullptr) { set_error("resnet_head: the fused head is built for 512 features"); return IDN_EINVAL; }
+  if (C != kHeadC || H != kHeadHW || W != kHeadHW || fc_wt == nullptr) {
+    set_error("resnet_head: the fused head is built for 512 features on a 7 x 7 map");
+    return IDN_EINVAL;
+  }
   const int clusters = (nimg + kHeadImgs - 1) / kHeadImgs;
   IDN_CUDA_TRY(launch_pdl(resnet_head_kernel, dim3(clusters * kHeadCluster), dim3(kHeadThreads), 0, st, act, nimg,
-                          img_rows, wp, H, W, fc_wt, fc_b, logits_out, idx, prob));
+                          img_rows, wp, fc_wt, fc_b, logits_out, idx, prob));
   return IDN_OK;
 }
 

@@ -334,35 +334,34 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
 #pragma unroll
       for (int i = 0; i < 6; ++i) acc[i] = 0.0f;
       const float* wp_ = wt + c;
-      float wa[8], wb[8];
+      // Weight loads run three blocks of 8 ahead of the FMAs (the loop is bound by L2 latency otherwise).
+      float w0[8], w1[8], w2[8], w3[8];
+      auto fetch = [&](float (&w)[8], int k0) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) wa[u] = __ldg(wp_ + (long long)u * IDN_NUM_CLASSES);
-#pragma unroll 1
-      for (int k0 = 0; k0 < kHeadC; k0 += 16) {                      // two blocks of 8 per trip, loads one block ahead
-#pragma unroll
-        for (int u = 0; u < 8; ++u) wb[u] = __ldg(wp_ + (long long)(k0 + 8 + u) * IDN_NUM_CLASSES);
+        for (int u = 0; u < 8; ++u) w[u] = __ldg(wp_ + (long long)(k0 + u) * IDN_NUM_CLASSES);
+      };
+      auto block = [&](const float (&w)[8], int k0) {
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           const float* f = &s_feat[k0 + u][i0];                      // i0 = 0 or 6: 8-byte aligned
           const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
                        f2 = *reinterpret_cast<const float2*>(f + 4);
-          acc[0] = fmaf(f0.x, wa[u], acc[0]); acc[1] = fmaf(f0.y, wa[u], acc[1]);
-          acc[2] = fmaf(f1.x, wa[u], acc[2]); acc[3] = fmaf(f1.y, wa[u], acc[3]);
-          acc[4] = fmaf(f2.x, wa[u], acc[4]); acc[5] = fmaf(f2.y, wa[u], acc[5]);
+          acc[0] = fmaf(f0.x, w[u], acc[0]); acc[1] = fmaf(f0.y, w[u], acc[1]);
+          acc[2] = fmaf(f1.x, w[u], acc[2]); acc[3] = fmaf(f1.y, w[u], acc[3]);
+          acc[4] = fmaf(f2.x, w[u], acc[4]); acc[5] = fmaf(f2.y, w[u], acc[5]);
         }
-        if (k0 + 16 < kHeadC) {
-#pragma unroll
-          for (int u = 0; u < 8; ++u) wa[u] = __ldg(wp_ + (long long)(k0 + 16 + u) * IDN_NUM_CLASSES);
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float* f = &s_feat[k0 + 8 + u][i0];
-          const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
-                       f2 = *reinterpret_cast<const float2*>(f + 4);
-          acc[0] = fmaf(f0.x, wb[u], acc[0]); acc[1] = fmaf(f0.y, wb[u], acc[1]);
-          acc[2] = fmaf(f1.x, wb[u], acc[2]); acc[3] = fmaf(f1.y, wb[u], acc[3]);
-          acc[4] = fmaf(f2.x, wb[u], acc[4]); acc[5] = fmaf(f2.y, wb[u], acc[5]);
-        }
+      };
+      fetch(w0, 0); fetch(w1, 8); fetch(w2, 16);
+#pragma unroll 1
+      for (int k0 = 0; k0 < kHeadC; k0 += 32) {
+        fetch(w3, k0 + 24);
+        block(w0, k0);
+        if (k0 + 32 < kHeadC) fetch(w0, k0 + 32);
+        block(w1, k0 + 8);
+        if (k0 + 32 < kHeadC) fetch(w1, k0 + 40);
+        block(w2, k0 + 16);
+        if (k0 + 32 < kHeadC) fetch(w2, k0 + 48);
+        block(w3, k0 + 24);
       }
       const float b = __ldg(fc_b + c);
 #pragma unroll

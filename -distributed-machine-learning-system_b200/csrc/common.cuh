@@ -224,9 +224,7 @@ struct PreMeta {            // one per image, device resident
 enum { PRE_OUT_NCHW = 0, PRE_OUT_STEM = 1, PRE_OUT_S2D4 = 2 };
 int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d_tables,
                       const uint16_t* d_lut, int n, int out_mode, void* out, int stem_left_pad,
-                      int stem_ws, int raw_words, int src_rows, cudaStream_t st,
-                      void* zero_ptr = nullptr, size_t zero_bytes_per_img = 0);
-void preprocess_tile_need(const int* htab, const int* vtab, int* raw_words, int* src_rows);
+                      int stem_ws, cudaStream_t st);
 // Builds the resample table (Pillow fixed point) of the 224 cropped outputs of one axis.
 void build_axis_table(int in_size, int out_size, int crop_off, std::string* ints /* int32 bytes */);
 void resized_size(int h, int w, int* nh, int* nw);

@@ -87,7 +87,6 @@ struct idn_engine {
   int* h_tables = nullptr;                  // page-locked mirror of the pool (upload source, tile sizing)
   size_t tables_cap = 0, tables_used = 0;   // int32 units
   std::map<std::tuple<int, int, int>, int> table_index;
-  int pre_raw_words = 0, pre_src_rows = 0;     // staged-tile need of the current batch
   uint16_t* d_lut = nullptr;
   void* xs = nullptr;                 // stem input image
   int stem_left = 0, stem_ws = 232;
@@ -629,8 +628,6 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
     if (e->meta_ev[ring]) IDN_CUDA_TRY(cudaEventSynchronize(e->meta_ev[ring]));
     hm = e->h_meta + (size_t)ring * (e->meta_ring > 1 ? e->cap : 0);
   }
-  e->pre_raw_words = 0; e->pre_src_rows = 0;
-  int last_h = -1, last_v = -1;
   for (int i = 0; i < n; ++i) {
     const int H = hw[2 * i], W = hw[2 * i + 1];
     if (H <= 0 || W <= 0) { set_error("image with non-positive size"); return IDN_EINVAL; }
@@ -640,13 +637,6 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
     m.offset = offsets[i] - base; m.H = H; m.W = W;
     IDN_TRY(ensure_table(e, W, nw, crop_offset(nw), &m.htab, copy_on));
     IDN_TRY(ensure_table(e, H, nh, crop_offset(nh), &m.vtab, copy_on));
-    if (m.htab != last_h || m.vtab != last_v) {
-      int rw = 0, sr = 0;
-      preprocess_tile_need(e->h_tables + m.htab, e->h_tables + m.vtab, &rw, &sr);
-      e->pre_raw_words = std::max(e->pre_raw_words, rw);
-      e->pre_src_rows = std::max(e->pre_src_rows, sr);
-      last_h = m.htab; last_v = m.vtab;
-    }
   }
   static_assert(sizeof(PreMeta) % 4 == 0, "PreMeta is copied in 32-bit words");
   IDN_TRY(launch_copy_words(d_dst, hm, sizeof(PreMeta) / 4 * (size_t)n, copy_on));
@@ -699,7 +689,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     switch (s.kind) {
       case STEP_PRE:
         IDN_TRY(launch_preprocess(d_imgs, d_meta, e->d_tables, e->d_lut, n, e->pre_mode, e->xs,
-                                  e->stem_left, e->stem_ws, e->pre_raw_words, e->pre_src_rows, st));
+                                  e->stem_left, e->stem_ws, st));
         break;
       case STEP_CONV:
         if (step_idx == e->fuse_stem_step) {
@@ -1057,8 +1047,7 @@ int idn_preprocess_u8hwc(int device, const uint8_t* imgs, const int64_t* offsets
   cudaMemcpy(tmp.d_lut, lut, sizeof(lut), cudaMemcpyHostToDevice);
   cudaMemcpy(d_in, imgs, hi, cudaMemcpyHostToDevice);
   rc = fill_meta(&tmp, offsets, hw, n, 0);
-  if (rc == IDN_OK) rc = launch_preprocess(d_in, tmp.d_meta, tmp.d_tables, tmp.d_lut, n, PRE_OUT_NCHW, d_out, 0, 0,
-                                        tmp.pre_raw_words, tmp.pre_src_rows, nullptr);
+  if (rc == IDN_OK) rc = launch_preprocess(d_in, tmp.d_meta, tmp.d_tables, tmp.d_lut, n, PRE_OUT_NCHW, d_out, 0, 0, nullptr);
   if (rc == IDN_OK && cudaDeviceSynchronize() != cudaSuccess) { set_error("preprocess kernel failed"); rc = IDN_ECUDA; }
   if (rc == IDN_OK && cudaMemcpy(out, d_out, out_elems * 2, cudaMemcpyDeviceToHost) != cudaSuccess) {
     set_error("preprocess D2H failed"); rc = IDN_ECUDA;

@@ -158,7 +158,7 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
 
   // ---- per-call contents of the array: tables and per-image records are rewritten every call
   //      (nothing from an earlier call is read, so nothing has to be cleared)
-  int used = 0, nkeys = 0, raw_words = 0, src_rows = 0;
+  int used = 0, nkeys = 0;
   auto table_for = [&](int in_size, int out_size, int crop) -> int {
     for (int k = 0; k < nkeys; ++k)
       if (g_keys[k].in_size == in_size && g_keys[k].out_size == out_size && g_keys[k].crop == crop)
@@ -184,10 +184,6 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
     }
     PreMeta& m = g_host_meta[i];
     m.offset = offsets[i]; m.H = H; m.W = W; m.htab = ht; m.vtab = vt;
-    int rw = 0, sr = 0;
-    preprocess_tile_need(g_host_tables + ht, g_host_tables + vt, &rw, &sr);
-    if (rw > raw_words) raw_words = rw;
-    if (sr > src_rows) src_rows = sr;
   }
   // The sources are ordinary (pageable) static arrays: each of these copies makes the HOST wait until the
   // work already queued on `st` has finished and the bytes have been staged, and returns only then -- so
@@ -197,5 +193,5 @@ extern "C" int idn_preprocess_u8hwc_noalloc(int device, const uint8_t* d_imgs_pa
   return launch_preprocess(d_imgs_packed, reinterpret_cast<const PreMeta*>(ds.scratch + kMetaOff),
                            reinterpret_cast<const int*>(ds.scratch + kTablesOff),
                            reinterpret_cast<const uint16_t*>(ds.scratch + kLutOff), n, PRE_OUT_NCHW,
-                           d_out_nchw_bf16, 0, 0, raw_words, src_rows, st);
+                           d_out_nchw_bf16, 0, 0, st);
 }

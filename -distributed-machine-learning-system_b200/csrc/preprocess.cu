@@ -179,7 +179,9 @@ template <int OUT_MODE, int NT>
 __device__ __forceinline__ void pre_fast_band(const uint8_t* __restrict__ src, const PreMeta& m,
                                               const int* __restrict__ ht, const PreVRow* s_v, const uint16_t* s_lut,
                                               void* out, int n, int ylo, int yhi, int first_row, int left_pad, int ws) {
-  const int x = threadIdx.x;
+  // Column of this thread.  For the space-to-depth writer the columns are rotated by two so that lanes
+  // 4 j .. 4 j + 3 hold the four pixels (dx = 0..3) of ONE s2d pixel row: (x + 2) % 4 == lane % 4.
+  const int x = OUT_MODE == PRE_OUT_S2D4 ? (int)((threadIdx.x + IDN_CROP - 2) % IDN_CROP) : (int)threadIdx.x;
   const int hks = ht[0];
   // horizontal taps, window shifted left at the right edge so that [x0, x0 + NT) stays inside the row
   int x0 = ht[1 + x];
@@ -237,7 +239,33 @@ __device__ __forceinline__ void pre_fast_band(const uint8_t* __restrict__ src, c
     for (int j = 0; j < NT; ++j) {
       a0 += bsel(hrow[j], 0) * v.c[j]; a1 += bsel(hrow[j], 1) * v.c[j]; a2 += bsel(hrow[j], 2) * v.c[j];
     }
-    pre_emit<OUT_MODE>(out, s_lut, n, y, x, (uint32_t)(a0 >> 22), (uint32_t)(a1 >> 22), (uint32_t)(a2 >> 22), left_pad, ws);
+    if (OUT_MODE != PRE_OUT_S2D4) {
+      pre_emit<OUT_MODE>(out, s_lut, n, y, x, (uint32_t)(a0 >> 22), (uint32_t)(a1 >> 22), (uint32_t)(a2 >> 22), left_pad, ws);
+    } else {
+      // The 4 pixels x 3 channels of a lane quad are 24 contiguous bytes of the s2d image: three lanes store 8
+      // bytes each after two shuffles (three 2-byte stores per lane made the kernel LSU-bound).  The quad of
+      // threads 0..3 straddles the row's last and first s2d pixel (two real pixels each): plain stores there.
+      const uint32_t r = s_lut[(uint32_t)(a0 >> 22)], g = s_lut[256 + (uint32_t)(a1 >> 22)], b = s_lut[512 + (uint32_t)(a2 >> 22)];
+      const uint32_t rg = r | (g << 16);
+      const uint32_t rg_n = __shfl_down_sync(0xffffffffu, rg, 1), b_n = __shfl_down_sync(0xffffffffu, b, 1);
+      const int by = (y + 2) >> 2, dy = (y + 2) & 3, q = (int)threadIdx.x & 3;
+      if (threadIdx.x >= 4) {
+        const int bx = (int)threadIdx.x >> 2;
+        uint32_t w0, w1;
+        if (q == 0) { w0 = rg; w1 = b | (rg_n << 16); }                          // r0 g0 | b0 r1
+        else if (q == 1) { w0 = (rg >> 16) | (b << 16); w1 = rg_n; }             // g1 b1 | r2 g2
+        else { w0 = b | (rg_n << 16); w1 = (rg_n >> 16) | (b_n << 16); }         // b2 r3 | g3 b3   (lane q == 2)
+        if (q != 3) {
+          uint2* o = reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(out) +
+                                              (((long long)n * 57 + by) * 57 + bx) * 64 + dy * 12) + q;
+          *o = make_uint2(w0, w1);
+        }
+      } else {
+        const int bx = (x + 2) >> 2;
+        uint16_t* o = reinterpret_cast<uint16_t*>(out) + (((long long)n * 57 + by) * 57 + bx) * 64 + (dy * 4 + q) * 3;
+        o[0] = (uint16_t)r; o[1] = (uint16_t)g; o[2] = (uint16_t)b;
+      }
+    }
   }
 }
 
@@ -283,7 +311,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
   if (fast) {
     if (nt == 3) pre_fast_band<OUT_MODE, 3>(src, m, ht, s_v, s_lut, out, n, ylo, yhi, first_row, left_pad, ws);
     else pre_fast_band<OUT_MODE, 4>(src, m, ht, s_v, s_lut, out, n, ylo, yhi, first_row, left_pad, ws);
-  } else {
+  } else {                                              // huge downscales, images narrower than the window
     for (int y = ylo; y < yhi; ++y) {
       int o[3];
       pre_direct_pixel(src, m.W, ht, vt, tid, y, o);

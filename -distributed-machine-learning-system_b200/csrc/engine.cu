@@ -988,8 +988,39 @@ int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, c
   }
   for (int b = 0; b < kSlots; ++b)
     if (h->slot[b].busy) { set_error("idn_infer_u8hwc: collect pending submissions first"); return IDN_EINVAL; }
-  // tensor batches of max_batch images, up to kSlots in flight: the copies of the next batches overlap
-  // the kernels of the current one
+  // Tensor batches with up to kSlots of them in flight: the copy of the next batch overlaps the kernels of the
+  // current one.  An input longer than max_batch is cut into batches of max_batch.  An input that fits ONE
+  // tensor batch -- the reference's call shape, one blocking deeplearning() per shard
+  // (mp4_machinelearning.py:596) -- would copy all its bytes before the first kernel starts (60 MB = 1.1 ms
+  // for 400 images); it is cut into a few sub-batches instead, so that only the first sub-batch's copy and the
+  // last one's kernels are exposed.  Results do not depend on the cut (per-image arithmetic is independent of
+  // the batch an image falls in; tests/test_gpu_model.py).  AlexNet's pass is shorter than its copy: equal
+  // fifths keep the tail short.  ResNet18's is longer: a small first sub-batch starts the GPU early and the
+  // big ones behind it run at full tile efficiency.  IDN_SINGLE_CALL_CUTS="a,b,c" (per cent) overrides.
+  std::vector<int> cuts;
+  if (n <= h->cap && n >= 128) {
+    std::vector<int> pct = h->model == IDN_MODEL_ALEXNET ? std::vector<int>{20, 20, 20, 20, 20} : std::vector<int>{10, 30, 60};
+    if (const char* v = std::getenv("IDN_SINGLE_CALL_CUTS")) {
+      std::vector<int> q;
+      int sum = 0;
+      for (const char* c = v; *c;) {
+        char* end = nullptr;
+        const long x = std::strtol(c, &end, 10);
+        if (end == c || x <= 0) { q.clear(); break; }
+        q.push_back((int)x); sum += (int)x;
+        c = *end == ',' ? end + 1 : end;
+      }
+      if (!q.empty() && sum == 100) pct = q;
+    }
+    int done = 0, acc = 0;
+    for (size_t k = 0; k < pct.size(); ++k) {
+      acc += pct[k];
+      const int upto = k + 1 == pct.size() ? n : (int)((long long)n * acc / 100);
+      if (upto > done) { cuts.push_back(upto - done); done = upto; }
+    }
+  } else {
+    for (int i0 = 0; i0 < n; i0 += h->cap) cuts.push_back(std::min(h->cap, n - i0));
+  }
   int tickets[kSlots], first[kSlots], head = 0, count = 0;
   auto collect_oldest = [&]() {
     const int i0 = first[head];
@@ -999,13 +1030,14 @@ int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, c
     return rc;
   };
   int rc = IDN_OK;
-  for (int i0 = 0; i0 < n && rc == IDN_OK; i0 += h->cap) {
+  int i0 = 0;
+  for (size_t k = 0; k < cuts.size() && rc == IDN_OK; ++k) {
     if (count == kSlots) rc = collect_oldest();
     if (rc != IDN_OK) break;
-    const int m = std::min(h->cap, n - i0);
+    const int m = cuts[k];
     const int at = (head + count) % kSlots;
     rc = idn_submit_u8hwc(h, imgs, offsets + i0, hw + 2 * i0, m, logits != nullptr, &tickets[at]);
-    if (rc == IDN_OK) { first[at] = i0; ++count; }
+    if (rc == IDN_OK) { first[at] = i0; ++count; i0 += m; }
   }
   while (rc == IDN_OK && count > 0) rc = collect_oldest();
   if (rc != IDN_OK) {                           // drain so that the handle stays usable
@@ -1067,6 +1099,33 @@ int idn_step_info(idn_handle h, int step, char* name, int name_len, int32_t* chw
     else if (s.out_kind == 3) { chw[0] = IDN_NUM_CLASSES; chw[1] = 1; chw[2] = 1; }
     else { chw[0] = s.out_C; chw[1] = s.out_H; chw[2] = s.out_W; }
   }
+  return IDN_OK;
+}
+
+int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
+  if (!h || !name || name_len <= 0 || step < 0 || step >= (int)h->steps.size()) { set_error("bad step"); return IDN_EINVAL; }
+  const Step& s = h->steps[step];
+  const ConvParams& cp = s.cp;
+  std::string k;
+  auto N = [](int v) { return std::to_string(v); };
+  const bool fuse = h->fuse_stem_step == step && !h->no_pool_fusion && !h->stem_simt;
+  switch (s.kind) {
+    case STEP_PRE: k = "preprocess_kernel<" + N(h->pre_mode) + ">"; break;
+    case STEP_POOL: k = (h->fuse_pool_step == step && !h->no_pool_fusion && !h->stem_simt) ? "(folded into stem_pool_kernel)" : "maxpool3x3s2_kernel"; break;
+    case STEP_RHEAD: k = h->no_head_fusion ? "avgpool_kernel + fc_fp32_kernel + softmax_top1_kernel" : "resnet_head_kernel"; break;
+    case STEP_SOFTMAX: k = "softmax_top1_kernel"; break;
+    case STEP_CONV:
+      if (h->impl != IDN_IMPL_TC || (cp.mode == MODE_STEM && h->stem_simt)) k = "conv_simt_kernel";
+      else if (cp.mode == MODE_STEM) k = fuse ? "stem_pool_kernel" : "stem_kernel";
+      else if (s.use_halo && cp.pair && s.b_resident) k = "conv_pair_res_kernel<" + N(cp.msub) + ", " + N(cp.num_taps == 9 ? 9 : 0) + ">";
+      else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + ">";
+      else if (s.use_halo) k = "conv_halo_kernel<" + N(s.block_n) + ", " + N(cp.msub) + ", " + N(s.b_resident ? 1 : 0) + ", " +
+                               N(s.b_resident ? (cp.num_taps == 9 ? 9 : 0) : (cp.b_group == 3 ? 3 : 0)) + ">";
+      else if (cp.tc_pair) k = "conv_tc_pair_kernel<" + N(s.block_n) + ">";
+      else k = "conv_tc_kernel<" + N(s.block_n) + ">";
+      break;
+  }
+  std::snprintf(name, name_len, "%s", k.c_str());
   return IDN_OK;
 }
 

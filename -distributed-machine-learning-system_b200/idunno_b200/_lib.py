@@ -38,6 +38,7 @@ SIGNATURES = {
     "idn_num_steps": (C.c_int, [C.c_void_p]),
     "idn_step_info": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.c_void_p]),
     "idn_read_activation": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "idn_step_kernel": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_int]),
     "idn_debug_stop_after": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_kernel_launches": (C.c_int64, [C.c_void_p]),
     "idn_set_timing": (C.c_int, [C.c_void_p, C.c_int]),

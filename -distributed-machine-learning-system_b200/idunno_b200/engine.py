@@ -152,6 +152,15 @@ class Engine:
             out.append((name.value.decode(), tuple(chw)))
         return out
 
+    def step_kernels(self):
+        """[(step name, CUDA kernel the step launches)]"""
+        out = []
+        for i, (name, _) in enumerate(self.steps()):
+            buf = C.create_string_buffer(160)
+            _lib.check(self._lib.idn_step_kernel(self._h, i, buf, 160), "idn_step_kernel")
+            out.append((name, buf.value.decode()))
+        return out
+
     def read_activation(self, step: int, n: int) -> np.ndarray:
         name, (c, h, w) = self.steps()[step]
         out = np.zeros((n, c, h, w), dtype=np.float32)

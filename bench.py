@@ -1,28 +1,34 @@
 #!/usr/bin/env python
 """Benchmark of the worker-side inference hot path (BASELINE.json metric: images/sec at
-"batch 400" for AlexNet and ResNet18).
+"batch 400" for AlexNet and ResNet18, with the fraction of the tensor roofline).
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (oracle port)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU implementation
 
 A step = one 400-image query through the hot path (uint8 HWC 224x224 images -> top-1 index and
-probability).  Primary workload (value / e2e / roofline): BASELINE.json configs[1], AlexNet batch
-400 over range 0-3999; the same measurements for ResNet18 are reported under "resnet18".
-With N > 1 (torchrun, one rank per GPU) every rank runs its own 400-image sub-range per step (the
-coordinator's range split gives each of N ranks 400 of a 400*N-image query: weak scaling) and the
-per-image results are gathered to rank 0 over NCCL inside the timed step.
+probability).  Headline workload (value / e2e / roofline): BASELINE.json configs[1], AlexNet batch 400
+over range 0-3999; ResNet18 (configs[2]) rides in the same line under "resnet18" (value, e2e, roofline
+fraction, and the 0-79999 range split over the ranks by the reference's rule).  With N > 1 (torchrun, one
+rank per GPU) every rank runs its own 400-image sub-range per step (weak scaling) and per-image results
+are gathered to rank 0 over NCCL inside the timed step.
 
-  value : images/s, inputs already resident in HBM, CUDA-event timed on the launching stream,
-          barrier + synchronize on both sides, max over ranks.
-  e2e   : images/s through the C-ABI call with HOST buffers (idn_infer_u8hwc): pinned uint8 in,
-          H2D + kernels + D2H of the results inside the timed region.
+  value : images/s, inputs resident in HBM, CUDA-event timed on the launching stream, barrier +
+          synchronize on both sides, max over ranks.
+  e2e   : images/s through the C-ABI calls with HOST buffers: pinned uint8 in, H2D + kernels + D2H of
+          the results inside the timed region (idn_submit_u8hwc / idn_collect, three in flight);
+          single_call_value is ONE blocking idn_infer_u8hwc per 400 images, the reference's call shape.
+The line is kept under 1400 characters; per-kernel times, pipeline counters and the other legs go to
+gpurun_out/bench_detail.json.
 """
 from __future__ import annotations
 
 import argparse
+import csv
 import json
 import os
+import re
 import sys
+import tempfile
 import threading
 import time
 
@@ -35,6 +41,7 @@ for _p in (ROOT, PKG):
 import numpy as np  # noqa: E402
 
 BATCH = 400
+IMG_BYTES = 224 * 224 * 3
 FLOP_PER_IMG = {"alexnet": 1428376960, "resnet18": 3628146688}
 PRE_BYTES_PER_IMG = 451584                                            # 224x224 source, bf16 out
 STEP_FLOPS = {   # algorithmic FLOPs per image of each tensor-core plan step (2*M*N*K, logical)
@@ -50,16 +57,13 @@ STEP_FLOPS = {   # algorithmic FLOPs per image of each tensor-core plan step (2*
         [(f"layer{l}.{b}.{c}", 231211008) for l in (2, 3, 4)
          for (b, c) in ((0, "conv2+add"), (1, "conv1"), (1, "conv2+add"))]),
 }
-WORKLOAD = {"alexnet": "AlexNet batch 400 over range 0-3999 (uint8 224x224 HWC -> top-1 idx/prob)",
-            "resnet18": "ResNet18 batch 400 over range 0-79999 sharded by rank (uint8 224x224 HWC -> top-1)"}
-# dram__bytes_read+write per launch of the dominant kernel from the committed `ncu --set full`
-# capture (profiles/), keyed by (model, step); None until a capture exists for that kernel.
-NCU_TRAFFIC_BYTES: dict = {
-    # profiles/r01f_alexnet_pair_ncu_full.csv: conv_pair_kernel<192,5>, 43.77 MB read + 59.92 MB written
-    ("alexnet", "features.3+relu"): 103693568,
-    # profiles/r01c_stem_pool2 (stem_kernel with the max-pool folded in): 326.9 MB read + 113.8 MB written
-    ("resnet18", "conv1+bn1+relu"): 440713728,
-}
+WORKLOAD = {"alexnet": "AlexNet batch 400, range 0-3999, u8 224x224 HWC -> top-1 idx/prob",
+            "resnet18": "ResNet18 batch 400, range 0-79999 sharded by rank"}
+# `ncu --set full` summaries under profiles/ (tools/ncu_summary.py) from which roofline.traffic is read:
+# the row whose kernel name matches the kernel the dominant step launches (idn_step_kernel).
+TRAFFIC_CAPTURES = {"alexnet": ["profiles/r02_alexnet_ncu_full.csv", "profiles/r01f_alexnet_pair_ncu_full.csv"],
+                    "resnet18": ["profiles/r02_resnet18_ncu_full.csv", "profiles/r02b_resnet18_preprocess_stem_head_ncu_full.csv"]}
+DETAIL_PATH = os.path.join(ROOT, "gpurun_out", "bench_detail.json")
 
 
 def load_peaks():
@@ -73,14 +77,34 @@ def load_peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
 
 
+def traffic_from_capture(model: str, kernel: str):
+    """(bytes per launch, file) of `kernel` from the newest committed capture that holds it, else (None, None)."""
+    for rel in TRAFFIC_CAPTURES.get(model, []):
+        path = os.path.join(ROOT, rel)
+        if not os.path.exists(path):
+            continue
+        with open(path) as f:
+            rows = list(csv.reader(f))
+        hdr = rows[0]
+        try:
+            kn, rd, wr = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        except ValueError:
+            continue
+        unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
+        for r in rows[2:]:
+            if len(r) > wr and re.search(r"\b" + re.escape(kernel), r[kn]):
+                return int(float(r[rd]) * unit.get(rows[1][rd], 1e6) + float(r[wr]) * unit.get(rows[1][wr], 1e6)), rel
+    return None, None
+
+
 class ClockSampler:
-    """Samples SM clock and throttle reasons of one GPU while the timed region runs (NVML)."""
+    """Samples SM clock, power and throttle reasons of one GPU while a timed region runs (NVML)."""
     REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap",
                0x8: "hw_slowdown", 0x10: "sync_boost", 0x20: "sw_thermal_slowdown",
                0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
 
     def __init__(self, index: int):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.samples, self.power, self.reasons, self.max_mhz = [], [], set(), None
         self._stop = threading.Event()
         self._thread = None
         try:
@@ -97,6 +121,7 @@ class ClockSampler:
         while not self._stop.is_set():
             try:
                 self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self._h) / 1000.0)
                 mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
                 for bit, name in self.REASONS.items():
                     if mask & bit and name != "gpu_idle":
@@ -116,11 +141,13 @@ class ClockSampler:
         if self._thread is not None:
             self._thread.join()
 
-    def summary(self):
+    def summary(self, power=False):
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
-        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
-                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+        out = {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        if power and self.power:
+            out["power_w_max"] = round(max(self.power), 1)
+        return out
 
 
 def make_batches(n_batches: int, seed: int):
@@ -128,11 +155,13 @@ def make_batches(n_batches: int, seed: int):
     return [noise_images(BATCH, seed=seed + b) for b in range(n_batches)]
 
 
-def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_baseline):
+def bench_model(model, rank, world, device, args, peaks, dist):
     import torch
-    from idunno_b200 import Engine
+    from idunno_b200 import Engine, sharding
     from idunno_b200.synth import make_state_dict
 
+    steps, warmup = args.steps, max(args.warmup, 3)
+    dev = f"cuda:{device}"
     sd = make_state_dict(model, 0, "default")
     eng = Engine(model, sd, device=device, max_batch=BATCH)
     stream = torch.cuda.Stream(device=device)      # a real (non-NULL) stream: NULL selects the handle's own
@@ -141,36 +170,39 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
 
     n_pool = 4                                     # 4 x 60.2 MB of distinct uint8 input > 126 MB L2
     host_batches = make_batches(n_pool, seed=100 * rank + (0 if model == "alexnet" else 50))
-    img_bytes = 224 * 224 * 3
-    offsets = (np.arange(BATCH, dtype=np.int64) * img_bytes)
+    offsets = (np.arange(BATCH, dtype=np.int64) * IMG_BYTES)
     hw = np.tile(np.asarray([[224, 224]], dtype=np.int32), (BATCH, 1))
-    dev_batches = [torch.from_numpy(b.reshape(-1)).to(f"cuda:{device}") for b in host_batches]
+    dev_batches = [torch.from_numpy(b.reshape(-1)).to(dev) for b in host_batches]
     pinned = [torch.from_numpy(b.reshape(-1)).pin_memory() for b in host_batches]
-    d_idx = torch.zeros(BATCH, dtype=torch.int32, device=f"cuda:{device}")
-    d_prob = torch.zeros(BATCH, dtype=torch.float32, device=f"cuda:{device}")
+    # results of a step: [idx int32 x 400 | prob fp32 x 400] in ONE buffer, so that the gather needs no eager op
+    res = torch.zeros(2 * BATCH, dtype=torch.int32, device=dev)
+    d_idx, d_prob = res[:BATCH], res[BATCH:].view(torch.float32)
     gathered, pending_gathers = None, []
     if world > 1:     # two sets: the gather of step i is still in flight while step i+1 computes
-        gathered = [[torch.zeros(BATCH, 2, dtype=torch.float32, device=f"cuda:{device}") for _ in range(world)]
-                    for _ in range(2)]
+        gathered = [[torch.zeros(2 * BATCH, dtype=torch.int32, device=dev) for _ in range(world)] for _ in range(2)]
 
     def drain_gathers(keep=0):
         while len(pending_gathers) > keep:
             pending_gathers.pop(0).wait()          # the timing stream waits for that collective
 
     def step_device(i):
-        b = dev_batches[i % n_pool]
-        eng.infer_device(b.data_ptr(), offsets, hw, d_idx.data_ptr(), d_prob.data_ptr())
-        if world > 1:   # result return: (idx, prob) per image to every rank's view (8 bytes per image, NCCL).
-            # Asynchronous: the collective starts when this step's kernels are done, the next step's kernels
-            # do not wait for it; every gather is waited for before the timed region ends.
-            mine = torch.stack([d_idx.to(torch.float32), d_prob], dim=1)
-            pending_gathers.append(dist.all_gather(gathered[i % 2], mine, async_op=True))
+        eng.infer_device(dev_batches[i % n_pool].data_ptr(), offsets, hw, d_idx.data_ptr(), d_prob.data_ptr())
+        if world > 1:   # result return of the query: 8 bytes per image to rank 0's view (NCCL), asynchronous --
+            # the next step's kernels do not wait for it; every gather is waited for inside the timed region
+            pending_gathers.append(dist.all_gather(gathered[i % 2], res, async_op=True))
             drain_gathers(keep=1)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world > 1:
+            t = torch.tensor([x], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
 
     def timed(fn, k):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -181,14 +213,9 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
         drain_gathers()
         ev1.record(stream)
         barrier()
-        ms = ev0.elapsed_time(ev1)
-        if world > 1:
-            t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{device}")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+        return max_over_ranks(ev0.elapsed_time(ev1))
 
-    for i in range(max(warmup, 3)):
+    for i in range(warmup):
         step_device(i)
     drain_gathers()
     eng.sync()
@@ -197,44 +224,74 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
         ms = timed(step_device, steps)
     eng.sync()                                      # also surfaces a stalled-pipeline report
     if world > 1:                                   # the last gather really carries this rank's last results
-        last = gathered[(steps - 1) % 2][rank]
-        assert torch.equal(last, torch.stack([d_idx.to(torch.float32), d_prob], dim=1)), "gathered results differ"
+        assert torch.equal(gathered[(steps - 1) % 2][rank], res), "gathered results differ"
     launches = eng.kernel_launches - l0
     value = BATCH * world * steps / (ms / 1e3)
+    detail = {"ms_per_step": ms / steps}
+
+    # ---- sustained leg: the same step back to back for >= args.sustain seconds, clocks and power sampled
+    sustained = None
+    if args.sustain > 0:
+        k = max(steps, int(args.sustain * 1e3 / (ms / steps)) + 1)
+        with ClockSampler(device) as sclk:
+            ms_s = timed(step_device, k)
+        v = BATCH * world * k / (ms_s / 1e3)
+        tf = v / world * FLOP_PER_IMG[model] / 1e12
+        sustained = {"value": round(v, 1), "seconds": round(ms_s / 1e3, 2), "tflops_per_gpu": round(tf, 1),
+                     "frac_of_sustained_peak": round(tf / peaks["tf_sustained"], 4), "clocks": sclk.summary(power=True)}
 
     # ---- end to end through the host-buffer C-ABI calls: every step copies its own 400 images from
     #      pinned host memory and reads its (idx, prob) back; up to three steps are in flight
-    #      (idn_submit_u8hwc / idn_collect), so the copy of step i+1 overlaps the kernels of step i
-    host_submit = [0.0]
     def run_e2e(k):
         pending = []
         for i in range(k):
             if len(pending) == 3:                  # IDN_MAX_IN_FLIGHT
                 eng.collect(pending.pop(0))
-            h0 = time.perf_counter()
             pending.append(eng.submit_packed(offsets, hw, pinned[i % n_pool].data_ptr()))
-            host_submit[0] += time.perf_counter() - h0
         while pending:
             eng.collect(pending.pop(0))
     run_e2e(3)
-    host_submit[0] = 0.0
     e2e_steps = max(steps, 100)     # ~0.1-0.2 s: filling/draining the 3-deep pipeline is < 2 %, host jitter averages out
     barrier()
     t0 = time.perf_counter()
     run_e2e(e2e_steps)
     barrier()
-    ms_e2e = (time.perf_counter() - t0) * 1e3
-    if world > 1:
-        t = torch.tensor([ms_e2e], dtype=torch.float64, device=f"cuda:{device}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_e2e = float(t.item())
+    ms_e2e = max_over_ranks((time.perf_counter() - t0) * 1e3)
     e2e_value = BATCH * world * e2e_steps / (ms_e2e / 1e3)
-    # the one-call form (idn_infer_u8hwc, copy then kernels then read-back, nothing overlapped)
+    # the one-call form: ONE blocking idn_infer_u8hwc per 400-image shard, the reference's call shape
     def step_host(i):
         eng.infer_packed(None, offsets, hw, packed_ptr=pinned[i % n_pool].data_ptr())
     step_host(0)
-    ms_sync = timed(step_host, 5)
-    e2e_sync_value = BATCH * world * 5 / (ms_sync / 1e3)
+    step_host(1)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(10):
+        step_host(i)
+    barrier()
+    single = BATCH * world * 10 / max_over_ranks(time.perf_counter() - t0)
+    # copy-only ceiling of this box's host link: the same pinned buffers, nothing else running
+    copy_stream = torch.cuda.Stream(device=device)
+    sink = torch.empty(BATCH * IMG_BYTES, dtype=torch.uint8, device=dev)
+    def copies(k):
+        with torch.cuda.stream(copy_stream):
+            for i in range(k):
+                sink.copy_(pinned[i % n_pool], non_blocking=True)
+        copy_stream.synchronize()
+    copies(3)
+    barrier()
+    t0 = time.perf_counter()
+    copies(40)
+    dt_copy = time.perf_counter() - t0
+    barrier()
+    h2d_gbs = 40 * BATCH * IMG_BYTES / dt_copy / 1e9          # this rank's rate while every rank copies
+    if world > 1:
+        t = torch.tensor([h2d_gbs], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        h2d_gbs = float(t.item())
+    ceiling = h2d_gbs * 1e9 / IMG_BYTES
+    e2e = {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": BATCH * IMG_BYTES + BATCH * 24,
+           "d2h_bytes_per_step": BATCH * 8, "single_call_value": round(single, 1),
+           "h2d_ceiling_gbs": round(h2d_gbs, 1), "frac_of_h2d_ceiling": round(e2e_value / ceiling, 3)}
 
     # ---- per-kernel durations (CUDA events around every plan step, on the same stream)
     eng.set_timing(True)
@@ -248,101 +305,156 @@ def bench_model(model, rank, world, device, steps, warmup, peaks, dist, do_cpu_b
             continue                               # first timed pass creates the events
         for name, t in eng.step_times_ms():
             acc[name] = acc.get(name, 0.0) + t / reps
-    eng.set_timing(2)                              # one more pass with the pipeline-wait counters on
+    eng.set_timing(2)                              # one more pass with the pipeline counters on
     step_device(0)
     drain_gathers()
     eng.sync()
     waits = {name: [int(x) for x in w] for name, w in eng.step_wait_cycles() if int(w.sum()) > 0}
     eng.set_timing(False)
+    kernels = dict(eng.step_kernels())
     flops = STEP_FLOPS[model]
     tc_steps = {k: v for k, v in acc.items() if k in flops}
     dom = max(tc_steps, key=tc_steps.get)
     achieved = flops[dom] * BATCH / (tc_steps[dom] * 1e-3) / 1e12
-    peak = peaks["tf_sustained"]
-    roofline = {"bound": "tensor", "kernel": f"tcgen05 implicit-GEMM conv [{dom}]", "achieved": round(achieved, 2),
-                "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
-                "traffic": NCU_TRAFFIC_BYTES.get((model, dom)),
-                "peak_source": f"MEASURED_PEAKS.json bf16 sustained ({peaks['source']}); the kernel is timed inside a "
-                               "full step, so the sustained figure is the denominator (a short kernel can exceed it)",
-                "frac_of_burst": round(achieved / peaks["tf_burst"], 4) if peaks.get("tf_burst") else None,
+    traffic, traffic_file = traffic_from_capture(model, kernels[dom])
+    # A sub-millisecond kernel timed with events inside a ~10 ms region runs at burst clocks: the burst figure
+    # is its denominator; against the sustained figure a good kernel reads above 1.
+    roofline = {"bound": "tensor", "kernel": f"{kernels[dom]} [{dom}]", "achieved": round(achieved, 1),
+                "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(achieved / peaks["tf_burst"], 4),
+                "frac_of_sustained": round(achieved / peaks["tf_sustained"], 4), "peak_source": peaks["source"] + " burst",
+                "traffic": traffic, "traffic_source": traffic_file,
                 "kernel_ms": round(tc_steps[dom], 4), "step_share": round(tc_steps[dom] / sum(acc.values()), 4)}
     whole = value / world * FLOP_PER_IMG[model] / 1e12
     pre_ms = acc.get("preprocess")
-    out = {
-        "value": round(value, 1), "ms_per_step": round(ms / steps, 4),
-        "e2e": {"value": round(e2e_value, 1), "unit": "images/s",
-                "h2d_bytes_per_step": BATCH * img_bytes + BATCH * 24,
-                "d2h_bytes_per_step": BATCH * 8, "steps": e2e_steps,
-                "how": "idn_submit_u8hwc/idn_collect, up to three 400-image steps in flight, host wall clock",
-                "single_call_value": round(e2e_sync_value, 1),
-                "host_ms_per_submit": round(host_submit[0] / e2e_steps * 1e3, 3)},
-        "roofline": roofline,
-        "whole_net": {"tflops": round(whole, 2), "frac_of_measured_sustained": round(whole / peak, 4),
-                      "frac_of_measured_burst": round(whole / peaks["tf_burst"], 4),
+    detail.update({
+        "kernel_ms": {k: round(v, 4) for k, v in acc.items()}, "kernels": kernels, "wait_cycles": waits,
+        "whole_net": {"tflops_per_gpu": round(whole, 1), "frac_of_burst": round(whole / peaks["tf_burst"], 4),
+                      "frac_of_sustained_peak_in_a_burst_run": round(whole / peaks["tf_sustained"], 4),
                       "frac_of_spec_2250": round(whole / 2250.0, 4)},
         "preprocess": None if not pre_ms else {
             "ms": round(pre_ms, 4), "gbps": round(PRE_BYTES_PER_IMG * BATCH / (pre_ms * 1e-3) / 1e9, 1),
             "frac_of_measured_hbm": round(PRE_BYTES_PER_IMG * BATCH / (pre_ms * 1e-3) / 1e9 / peaks["hbm"], 4)},
-        "kernel_ms": {k: round(v, 4) for k, v in acc.items()},
-        "wait_cycles": waits,
-        "gpu_launches": int(launches), "clocks": clk.summary(),
-    }
-    if do_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline(model, sd, host_batches[0], sample=96 if model == "alexnet" else 64)
+        "sustained": sustained})
+
+    # ---- BASELINE.json configs[2] as worded: ResNet18 over range 0-79999, split over the ranks by the
+    #      reference's rule (mp4_machinelearning.py:516-536), ONE gather of (idx, prob) at the end: strong scaling
+    range_leg = None
+    if model == "resnet18" and args.range_images > 0:
+        total = args.range_images
+        shard = [s for s in sharding.split_range(0, total - 1, list(range(world))) if s[0] == rank][0]
+        count = shard[2] - shard[1] + 1
+        cmax = -(-total // world) + 1
+        mine = torch.zeros(2 * cmax, dtype=torch.int32, device=dev)
+        i_all, p_all = mine[:cmax], mine[cmax:].view(torch.float32)
+        everyone = [torch.zeros(2 * cmax, dtype=torch.int32, device=dev) for _ in range(world)] if world > 1 else None
+
+        def run_range():
+            for b, i0 in enumerate(range(0, count, BATCH)):
+                n = min(BATCH, count - i0)
+                eng.infer_device(dev_batches[b % n_pool].data_ptr(), offsets[:n], hw[:n],
+                                 i_all.data_ptr() + 4 * i0, p_all.data_ptr() + 4 * i0)
+            if world > 1:
+                dist.all_gather(everyone, mine)
+        ms_r = timed(lambda i: run_range(), 1)
+        ms_r = min(ms_r, timed(lambda i: run_range(), 1))
+        range_leg = {"images": total, "value": round(total / (ms_r / 1e3), 1), "ms": round(ms_r, 2),
+                     "scaling": "strong", "split": "reference rule, one gather at the end"}
+
     eng.close()
+    return {"value": round(value, 1), "ms_per_step": round(ms / steps, 4), "e2e": e2e, "roofline": roofline,
+            "gpu_launches": int(launches), "clocks": clk.summary(), "range_leg": range_leg, "detail": detail,
+            "sd": sd, "images": host_batches[0]}
+
+
+# ------------------------------------------------------------------------------------- CPU legs
+def cpu_legs(model, sd, images, n_faithful=400):
+    """BASELINE.md section 3, on this box's host cores:
+    (i)  faithful: the reference's own deeplearning() over range 0-399 (oracle/_ref: the unmodified module),
+         batch-1 loop, model constructed inside the call as the reference does (alexnet_resnet.py:16-22);
+    (ii) best effort: the same torchvision model preloaded, ONE [400,3,224,224] fp32 forward, the
+         reference's preprocess timed separately."""
+    import torch
+    import torchvision
+    from oracle import ref_path, run_ref
+    cores = torch.get_num_threads()
+    out = {"unit": "images/s", "cores": cores, "host_cpus": os.cpu_count()}
+    imgs = {i: images[i] for i in range(n_faithful)}
+    if run_ref.available():
+        with tempfile.TemporaryDirectory() as d:
+            rr = run_ref.ReferenceRun(d, {model: sd})
+            rr.write_images(model, imgs)
+            rr.deeplearning(model, 0, 3)                                    # warm caches / lazy imports
+            res, secs = rr.deeplearning(model, 0, n_faithful - 1)
+        out.update(value=round(len(res) / secs, 2), kind="reference",
+                   sample=f"unmodified reference deeplearning() over range 0-{n_faithful - 1} (batch-1 loop, model built "
+                          f"inside the call), {secs:.1f} s")
+    else:
+        t0 = time.time()
+        ref_path.infer_arrays(model, sd, [images[i] for i in range(64)], library_preprocess=True)
+        secs = time.time() - t0
+        out.update(value=round(64 / secs, 2), kind="port",
+                   sample=f"oracle port (oracle/_ref absent), batch-1 loop over 64 images, model preloaded, {secs:.1f} s")
+    net = getattr(torchvision.models, model)(weights=None)
+    net.load_state_dict(sd)
+    net.eval()
+    t0 = time.time()
+    x = torch.from_numpy(np.stack([ref_path.preprocess_library(images[i]) for i in range(BATCH)]))
+    t_pre = time.time() - t0
+    with torch.no_grad():
+        net(x[:16])
+        t0 = time.time()
+        net(x)
+        t_fwd = time.time() - t0
+    out["best_effort"] = {"value": round(BATCH / t_fwd, 1), "what": "preloaded model, one [400,3,224,224] fp32 forward",
+                          "preprocess_images_per_s": round(BATCH / t_pre, 1)}
     return out
 
 
-def cpu_baseline(model, sd, images, sample):
-    """The oracle (CPU port of the reference's per-image loop, alexnet_resnet.py:57-87) timed on this
-    box's host cores on a bounded sample of the same workload."""
-    import torch
-    from oracle import ref_path
-    imgs = [images[i] for i in range(sample)]
-    ref_path.infer_arrays(model, sd, imgs[:4], library_preprocess=True)   # warm-up
-    t0 = time.time()
-    ref_path.infer_arrays(model, sd, imgs, library_preprocess=True)
-    dt = time.time() - t0
-    return {"value": round(sample / dt, 2), "unit": "images/s", "cores": torch.get_num_threads(),
-            "host_cpus": os.cpu_count(), "kind": "port",
-            "sample": f"first {sample} images of one 400-image query, batch-1 loop as the reference "
-                      f"(preprocess + forward + softmax/top-1), model preloaded"}
-
-
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation of the path (oracle port; the
-    reference file itself cannot travel to the GPU box).  Rank 0 only."""
+    """--impl reference: the reference's own CPU implementation of the path on this box's host cores, all
+    the threads it can use.  A step = one deeplearning() call over a 32-image shard (model construction
+    inside the call, as the reference does).  oracle/_ref (the unmodified module, byte-compiled) when it
+    travelled here, else the oracle port.  Rank 0 only."""
     if rank != 0:
         return
     import torch
     from idunno_b200.synth import make_state_dict
-    from oracle import ref_path
+    from oracle import ref_path, run_ref
     # torchrun exports OMP_NUM_THREADS=1; the reference arm uses every host core it can
     torch.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
-    per_step = 32
+    per_step = 80                                   # the reference's own shard: a 400-image query over its 5 workers
+    use_ref = run_ref.available()
     res = {}
-    for model in ("alexnet", "resnet18"):
-        sd = make_state_dict(model, 0, "default")
-        batch = make_batches(1, seed=0 if model == "alexnet" else 50)[0]
-        imgs = [batch[i] for i in range(per_step)]
-        for _ in range(max(1, min(args.warmup, 3))):
-            ref_path.infer_arrays(model, sd, imgs, library_preprocess=True)
-        t0 = time.time()
-        for _ in range(args.steps):
-            ref_path.infer_arrays(model, sd, imgs, library_preprocess=True)
-        dt = time.time() - t0
-        res[model] = (per_step * args.steps / dt, dt / args.steps * 1e3)
+    with tempfile.TemporaryDirectory() as d:
+        sds = {m: make_state_dict(m, 0, "default") for m in ("alexnet", "resnet18")}
+        rr = run_ref.ReferenceRun(d, sds) if use_ref else None
+        for model in ("alexnet", "resnet18"):
+            batch = make_batches(1, seed=0 if model == "alexnet" else 50)[0]
+            imgs = [batch[i] for i in range(per_step)]
+            if use_ref:
+                rr.write_images(model, dict(enumerate(imgs)))
+                step = lambda: rr.deeplearning(model, 0, per_step - 1)
+            else:
+                step = lambda: ref_path.infer_arrays(model, sds[model], imgs, library_preprocess=True)
+            for _ in range(max(1, min(args.warmup, 3))):
+                step()
+            t0 = time.time()
+            for _ in range(args.steps):
+                step()
+            dt = time.time() - t0
+            res[model] = (per_step * args.steps / dt, dt / args.steps * 1e3)
     v, ms = res["alexnet"]
     cores = torch.get_num_threads()
-    sample = (f"each step = {per_step} images of a 400-image query, batch-1 loop as the reference "
-              f"(alexnet_resnet.py:48-90), model preloaded, {cores} torch threads")
+    kind = "reference" if use_ref else "port"
+    sample = (f"each step = one deeplearning() over a {per_step}-image shard of the 400-image query, batch-1 loop, "
+              f"model built inside the call (alexnet_resnet.py:16-22), {cores} torch threads")
     line = {"impl": "reference", "metric": "images/sec", "value": round(v, 2), "unit": "images/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": WORKLOAD["alexnet"], "tensor_batch": 1, "weights": "random-init seed 0"},
             "cpu_baseline": {"value": round(v, 2), "unit": "images/s", "cores": cores,
-                             "host_cpus": os.cpu_count(), "kind": "port", "sample": sample},
+                             "host_cpus": os.cpu_count(), "kind": kind, "sample": sample},
             "e2e": {"value": round(v, 2), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "resnet18": {"value": round(res["resnet18"][0], 2), "ms_per_step": round(res["resnet18"][1], 3)}}
     print(json.dumps(line), flush=True)
@@ -355,6 +467,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--models", default="alexnet,resnet18")
+    ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the back-to-back leg per model (0: skip)")
+    ap.add_argument("--range-images", type=int, default=80000, help="ResNet18 range leg (BASELINE configs[2]); 0: skip")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -382,8 +497,7 @@ def main():
     peaks = load_peaks()
     results = {}
     for model in args.models.split(","):
-        results[model] = bench_model(model, rank, world, local, args.steps, args.warmup, peaks, dist,
-                                     do_cpu_baseline=(rank == 0 and world == 1))
+        results[model] = bench_model(model, rank, world, local, args, peaks, dist)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -391,27 +505,54 @@ def main():
         return
     prim = "alexnet" if "alexnet" in results else next(iter(results))
     r = results[prim]
+    cpu = {}
+    if world == 1 and not args.no_cpu:
+        torch.set_num_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+        for m, rm in results.items():
+            cpu[m] = cpu_legs(m, rm["sd"], rm["images"])
     line = {"metric": "images/sec", "value": r["value"], "unit": "images/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD[prim], "tensor_batch": BATCH,
-                       "images_per_step": BATCH * world, "weights": "random-init seed 0 (torchvision init)",
-                       "l2": "inputs cycle through 4 distinct 60.2 MB uint8 batches per rank (241 MB > 126 MB L2); "
-                             "weights + activations per step also exceed L2",
-                       "parallelism": (f"range-sharded dp{world}, asynchronous NCCL all_gather of (idx, prob) per step, all waited for "
-                                       "inside the timed region") if world > 1 else "1 GPU",
-                       "host_binding": (f"each rank pinned to the {len(numa_cores)} cores NVML reports next to its GPU"
-                                        if numa_cores else "none")},
-            "roofline": r["roofline"], "e2e": r["e2e"], "clocks": r["clocks"],
-            "gpu_launches": r["gpu_launches"], "whole_net": r["whole_net"], "preprocess": r["preprocess"],
-            "kernel_ms": r["kernel_ms"], "wait_cycles": r["wait_cycles"]}
-    if "cpu_baseline" in r:
-        line["cpu_baseline"] = r["cpu_baseline"]
-    for other in results:
-        if other != prim:
-            line[other] = dict(results[other], workload=WORKLOAD[other])
-    print(json.dumps(line), flush=True)
+            "config": {"workload": WORKLOAD[prim], "tensor_batch": BATCH, "images_per_step": BATCH * world,
+                       "weights": "random-init seed 0",
+                       "l2": "inputs cycle through 4 distinct 60 MB batches per rank (241 MB > 126 MB L2)",
+                       "parallelism": f"range-sharded dp{world}, async NCCL all_gather of (idx, prob) per step" if world > 1 else "1 GPU"},
+            "roofline": {k: v for k, v in r["roofline"].items() if k not in ("kernel_ms", "step_share")},
+            "e2e": r["e2e"], "clocks": r["clocks"], "gpu_launches": r["gpu_launches"]}
+    if prim in cpu:
+        c = cpu[prim]
+        line["cpu_baseline"] = {"value": c["value"], "unit": c["unit"], "cores": c["cores"], "kind": c["kind"],
+                                "sample": c["sample"], "best_effort_value": c["best_effort"]["value"]}
+    if "resnet18" in results and prim != "resnet18":
+        rr = results["resnet18"]
+        line["resnet18"] = {"value": rr["value"], "ms_per_step": rr["ms_per_step"], "e2e": rr["e2e"]["value"],
+                            "single_call": rr["e2e"]["single_call_value"], "roofline_frac": rr["roofline"]["frac"],
+                            "whole_net_frac_of_burst": rr["detail"]["whole_net"]["frac_of_burst"]}
+        if rr["range_leg"]:
+            line["resnet18"]["range_0_79999"] = {"value": rr["range_leg"]["value"], "ms": rr["range_leg"]["ms"], "scaling": "strong"}
+        if "resnet18" in cpu:
+            line["resnet18"]["cpu_faithful"] = cpu["resnet18"]["value"]
+    if r["detail"].get("sustained"):
+        s = r["detail"]["sustained"]
+        line["sustained"] = {"value": s["value"], "seconds": s["seconds"], "frac_of_sustained_peak": s["frac_of_sustained_peak"],
+                             "sm_mhz": s["clocks"].get("sm_mhz"), "power_w_max": s["clocks"].get("power_w_max")}
+    detail = {"line": line, "host_binding": numa_cores, "cpu_baseline": cpu,
+              "models": {m: dict(rm["detail"], roofline=rm["roofline"], e2e=rm["e2e"], range_leg=rm["range_leg"],
+                                 workload=WORKLOAD[m]) for m, rm in results.items()}}
+    try:
+        os.makedirs(os.path.dirname(DETAIL_PATH), exist_ok=True)
+        with open(DETAIL_PATH if world == 1 else DETAIL_PATH.replace(".json", f"_{world}gpu.json"), "w") as f:
+            json.dump(detail, f, indent=1)
+    except OSError:
+        pass
+    text = json.dumps(line)
+    for drop in ("sustained", "clocks.samples"):            # the driver's record keeps 1500 characters
+        if len(text) <= 1400:
+            break
+        line.pop(drop, None)
+        text = json.dumps(line)
+    print(text, flush=True)
 
 
 if __name__ == "__main__":

@@ -81,7 +81,10 @@ int idn_set_impl(idn_handle h, int impl);
  *   logits      : optional [n][1000] fp32 (NULL to skip)
  * Host buffers in and out: the call copies inputs to the device, runs, copies results back and
  * returns after they have arrived.  Inputs longer than max_batch are processed as tensor batches of
- * max_batch images with up to IDN_MAX_IN_FLIGHT of them in flight (see idn_submit_u8hwc). */
+ * max_batch images with up to IDN_MAX_IN_FLIGHT of them in flight (see idn_submit_u8hwc).  An input of
+ * 128 .. max_batch images -- the reference's call shape, one blocking deeplearning() per shard -- is cut
+ * into a few sub-batches the same way, so that its copy overlaps its kernels (results do not depend on
+ * the cut). */
 int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs_packed, const int64_t* offsets,
                     const int32_t* hw, int n, int32_t* top1_idx, float* top1_prob, float* logits);
 
@@ -129,6 +132,10 @@ int idn_preprocess_u8hwc(int device, const uint8_t* imgs_packed, const int64_t* 
 int idn_num_steps(idn_handle h);
 int idn_step_info(idn_handle h, int step, char* name, int name_len, int32_t* chw /* [3] */);
 int idn_read_activation(idn_handle h, int step, int n, float* out_nchw);
+/* Name of the CUDA kernel (template instance as a profiler prints it, e.g. "conv_pair_kernel<192, 5>") that
+ * plan step `step` launches; bench.py uses it to check that a committed profiler capture it quotes DRAM
+ * traffic from really is the kernel it timed. */
+int idn_step_kernel(idn_handle h, int step, char* name, int name_len);
 /* Later passes run the plan only up to and including `step` (-1: whole plan), so that an
  * activation buffer that a later step reuses can be read back right after its producer. */
 int idn_debug_stop_after(idn_handle h, int step);

@@ -57,8 +57,7 @@ STEP_FLOPS = {   # algorithmic FLOPs per image of each tensor-core plan step (2*
         [(f"layer{l}.{b}.{c}", 231211008) for l in (2, 3, 4)
          for (b, c) in ((0, "conv2+add"), (1, "conv1"), (1, "conv2+add"))]),
 }
-WORKLOAD = {"alexnet": "AlexNet batch 400, range 0-3999, u8 224x224 HWC -> top-1 idx/prob",
-            "resnet18": "ResNet18 batch 400, range 0-79999 sharded by rank"}
+WORKLOAD = {"alexnet": "AlexNet batch 400 over range 0-3999", "resnet18": "ResNet18 batch 400 over range 0-79999"}
 # `ncu --set full` summaries under profiles/ (tools/ncu_summary.py) from which roofline.traffic is read:
 # the row whose kernel name matches the kernel the dominant step launches (idn_step_kernel).
 TRAFFIC_CAPTURES = {"alexnet": ["profiles/r02_alexnet_ncu_full.csv", "profiles/r01f_alexnet_pair_ncu_full.csv"],
@@ -93,7 +92,7 @@ def traffic_from_capture(model: str, kernel: str):
         unit = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}
         for r in rows[2:]:
             if len(r) > wr and re.search(r"\b" + re.escape(kernel), r[kn]):
-                return int(float(r[rd]) * unit.get(rows[1][rd], 1e6) + float(r[wr]) * unit.get(rows[1][wr], 1e6)), rel
+                return int(float(r[rd]) * unit.get(rows[1][rd], 1e6) + float(r[wr]) * unit.get(rows[1][wr], 1e6)), os.path.basename(rel)
     return None, None
 
 
@@ -319,10 +318,10 @@ def bench_model(model, rank, world, device, args, peaks, dist):
     traffic, traffic_file = traffic_from_capture(model, kernels[dom])
     # A sub-millisecond kernel timed with events inside a ~10 ms region runs at burst clocks: the burst figure
     # is its denominator; against the sustained figure a good kernel reads above 1.
-    roofline = {"bound": "tensor", "kernel": f"{kernels[dom]} [{dom}]", "achieved": round(achieved, 1),
+    roofline = {"bound": "tensor", "kernel": f"{kernels[dom].replace(', ', ',')} {dom}", "achieved": round(achieved, 1),
                 "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": round(achieved / peaks["tf_burst"], 4),
-                "frac_of_sustained": round(achieved / peaks["tf_sustained"], 4), "peak_source": peaks["source"] + " burst",
-                "traffic": traffic, "traffic_source": traffic_file,
+                "frac_of_sustained": round(achieved / peaks["tf_sustained"], 4), "peak_src": peaks["source"] + " burst",
+                "traffic": traffic, "traffic_src": traffic_file,
                 "kernel_ms": round(tc_steps[dom], 4), "step_share": round(tc_steps[dom] / sum(acc.values()), 4)}
     whole = value / world * FLOP_PER_IMG[model] / 1e12
     pre_ms = acc.get("preprocess")
@@ -386,14 +385,13 @@ def cpu_legs(model, sd, images, n_faithful=400):
             rr.deeplearning(model, 0, 3)                                    # warm caches / lazy imports
             res, secs = rr.deeplearning(model, 0, n_faithful - 1)
         out.update(value=round(len(res) / secs, 2), kind="reference",
-                   sample=f"unmodified reference deeplearning() over range 0-{n_faithful - 1} (batch-1 loop, model built "
-                          f"inside the call), {secs:.1f} s")
+                   sample=f"unmodified reference deeplearning() range 0-{n_faithful - 1}, {secs:.1f} s")
     else:
         t0 = time.time()
         ref_path.infer_arrays(model, sd, [images[i] for i in range(64)], library_preprocess=True)
         secs = time.time() - t0
         out.update(value=round(64 / secs, 2), kind="port",
-                   sample=f"oracle port (oracle/_ref absent), batch-1 loop over 64 images, model preloaded, {secs:.1f} s")
+                   sample=f"oracle port (no oracle/_ref), 64 images, model preloaded, {secs:.1f} s")
     net = getattr(torchvision.models, model)(weights=None)
     net.load_state_dict(sd)
     net.eval()
@@ -515,9 +513,8 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
             "config": {"workload": WORKLOAD[prim], "tensor_batch": BATCH, "images_per_step": BATCH * world,
-                       "weights": "random-init seed 0",
-                       "l2": "inputs cycle through 4 distinct 60 MB batches per rank (241 MB > 126 MB L2)",
-                       "parallelism": f"range-sharded dp{world}, async NCCL all_gather of (idx, prob) per step" if world > 1 else "1 GPU"},
+                       "weights": "random-init seed 0", "l2": "inputs 4x60MB per rank > L2",
+                       "parallelism": f"range-sharded dp{world}, NCCL gather of (idx, prob) per step" if world > 1 else "1 GPU"},
             "roofline": {k: v for k, v in r["roofline"].items() if k not in ("kernel_ms", "step_share")},
             "e2e": r["e2e"], "clocks": r["clocks"], "gpu_launches": r["gpu_launches"]}
     if prim in cpu:
@@ -527,16 +524,14 @@ def main():
     if "resnet18" in results and prim != "resnet18":
         rr = results["resnet18"]
         line["resnet18"] = {"value": rr["value"], "ms_per_step": rr["ms_per_step"], "e2e": rr["e2e"]["value"],
-                            "single_call": rr["e2e"]["single_call_value"], "roofline_frac": rr["roofline"]["frac"],
-                            "whole_net_frac_of_burst": rr["detail"]["whole_net"]["frac_of_burst"]}
-        if rr["range_leg"]:
-            line["resnet18"]["range_0_79999"] = {"value": rr["range_leg"]["value"], "ms": rr["range_leg"]["ms"], "scaling": "strong"}
-        if "resnet18" in cpu:
-            line["resnet18"]["cpu_faithful"] = cpu["resnet18"]["value"]
+                            "single_call": rr["e2e"]["single_call_value"], "roofline_frac": rr["roofline"]["frac"]}
+        if rr["range_leg"]:                          # BASELINE configs[2] as worded: fixed range, strong scaling
+            line["resnet18"]["range80k"] = rr["range_leg"]["value"]
+            line["resnet18"]["range80k_ms"] = rr["range_leg"]["ms"]
     if r["detail"].get("sustained"):
         s = r["detail"]["sustained"]
-        line["sustained"] = {"value": s["value"], "seconds": s["seconds"], "frac_of_sustained_peak": s["frac_of_sustained_peak"],
-                             "sm_mhz": s["clocks"].get("sm_mhz"), "power_w_max": s["clocks"].get("power_w_max")}
+        line["sustained"] = {"value": s["value"], "s": s["seconds"], "frac_of_sustained_peak": s["frac_of_sustained_peak"],
+                             "sm_mhz": s["clocks"].get("sm_mhz")}
     detail = {"line": line, "host_binding": numa_cores, "cpu_baseline": cpu,
               "models": {m: dict(rm["detail"], roofline=rm["roofline"], e2e=rm["e2e"], range_leg=rm["range_leg"],
                                  workload=WORKLOAD[m]) for m, rm in results.items()}}
@@ -547,10 +542,14 @@ def main():
     except OSError:
         pass
     text = json.dumps(line)
-    for drop in ("sustained", "clocks.samples"):            # the driver's record keeps 1500 characters
+    for drop in (("roofline", "peak_src"), ("config", "images_per_step"), ("sustained", "s"), ("config", "l2"),
+                 ("roofline", "traffic_src"), ("sustained",)):   # the driver's record keeps 1500 characters
         if len(text) <= 1400:
             break
-        line.pop(drop, None)
+        if len(drop) == 1:
+            line.pop(drop[0], None)
+        elif drop[0] in line:
+            line[drop[0]].pop(drop[1], None)
         text = json.dumps(line)
     print(text, flush=True)
 

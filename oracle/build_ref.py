@@ -1,11 +1,11 @@
 """TEST / BASELINE INFRASTRUCTURE ONLY -- recipe for oracle/_ref/.
 
 Byte-compiles the UNMODIFIED reference hot-path module where it lies, /root/reference/alexnet_resnet.py,
-into oracle/_ref/alexnet_resnet.pyc (git-ignored output; no reference source enters the repository).  The
-.pyc travels to the GPU box with the snapshot, where /root/reference does not exist, so that bench.py's
+into oracle/_ref/alexnet_resnet.bin (CPython byte code; git-ignored output; no reference source enters the repository).  The
+file travels to the GPU box with the snapshot, where /root/reference does not exist, so that bench.py's
 `--impl reference` arm and its `cpu_baseline` leg time the reference's OWN code (`kind: "reference"`)
 instead of the restatement in oracle/ref_path.py.  Run by __graft_entry__.build() when /root/reference is
-present; same interpreter version on both machines (the .pyc is tied to it).
+present; same interpreter version on both machines (byte code is tied to it).
 """
 from __future__ import annotations
 
@@ -14,7 +14,7 @@ import py_compile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = "/root/reference/alexnet_resnet.py"
-OUT = os.path.join(HERE, "_ref", "alexnet_resnet.pyc")
+OUT = os.path.join(HERE, "_ref", "alexnet_resnet.bin")      # CPython byte code (.pyc content; snapshots skip *.pyc)
 
 
 def build() -> str | None:

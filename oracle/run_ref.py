@@ -12,7 +12,7 @@ import sys
 import types
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-PYC = os.path.join(HERE, "_ref", "alexnet_resnet.pyc")
+PYC = os.path.join(HERE, "_ref", "alexnet_resnet.bin")
 
 
 def available() -> bool:

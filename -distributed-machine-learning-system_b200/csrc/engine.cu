@@ -994,12 +994,14 @@ int idn_infer_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, c
   // (mp4_machinelearning.py:596) -- would copy all its bytes before the first kernel starts (60 MB = 1.1 ms
   // for 400 images); it is cut into a few sub-batches instead, so that only the first sub-batch's copy and the
   // last one's kernels are exposed.  Results do not depend on the cut (per-image arithmetic is independent of
-  // the batch an image falls in; tests/test_gpu_model.py).  AlexNet's pass is shorter than its copy: equal
-  // fifths keep the tail short.  ResNet18's is longer: a small first sub-batch starts the GPU early and the
-  // big ones behind it run at full tile efficiency.  IDN_SINGLE_CALL_CUTS="a,b,c" (per cent) overrides.
+  // the batch an image falls in; tests/test_gpu_model.py).  Measured on B200 (profiles/README.md, round 2):
+  // every extra pass costs its kernels' fill and drain (~0.1 ms AlexNet, ~0.3 ms ResNet18), so few cuts win --
+  // thirds for AlexNet (its pass is shorter than its copy), 10/30/60 % for ResNet18 (a small first sub-batch
+  // starts the GPU early, the big ones behind it keep their tile efficiency).
+  // IDN_SINGLE_CALL_CUTS="a,b,c" (per cent) overrides.
   std::vector<int> cuts;
   if (n <= h->cap && n >= 128) {
-    std::vector<int> pct = h->model == IDN_MODEL_ALEXNET ? std::vector<int>{20, 20, 20, 20, 20} : std::vector<int>{10, 30, 60};
+    std::vector<int> pct = h->model == IDN_MODEL_ALEXNET ? std::vector<int>{34, 33, 33} : std::vector<int>{10, 30, 60};
     if (const char* v = std::getenv("IDN_SINGLE_CALL_CUTS")) {
       std::vector<int> q;
       int sum = 0;

@@ -78,3 +78,49 @@ def test_staging_pipeline_matches_single_call(built_library, tmp_path, monkeypat
     assert list(ind) == indices == [i for i in range(20, 43) if i != 31]
     assert np.array_equal(idx, want_idx) and np.array_equal(prob, want_prob)
     assert np.array_equal(again[1], idx) and np.array_equal(again[2], prob)
+
+
+def test_concurrent_jobs_c1_c2_and_measured_fair_share(built_library):
+    """SURVEY 8f-3 on the GPU: AlexNet and ResNet18 query streams run concurrently through the box runner
+    (two ranks on cuda:0); the coordinator's c1 (images per second in the 30 s window) and c2 (mean /
+    quartiles / sigma of seconds per 400-image query) come from MEASURED shard times, the averages the
+    reference leaves at the constant 100 (mp4_machinelearning.py:138,676) are updated from them, and the
+    worker count of later queries is the fair-share formula (:504-514) evaluated on those averages."""
+    from idunno_b200 import boxrun, sharding
+    os.environ["PYTHONPATH"] = PKG + os.pathsep + os.environ.get("PYTHONPATH", "")
+    port = 25000 + os.getpid() % 3000 + 23
+    batch = 40
+    classify = boxrun.gpu_classifier(0, batch)
+    span = batch * 4
+    want = {m: classify(m, 0, span - 1) for m in ("alexnet", "resnet18")}
+    runner = boxrun.BoxRunner("127.0.0.1", port, 2, classify, seed=0)
+    p = mp.get_context("spawn").Process(target=boxrun.gpu_worker_main,
+                                        args=("127.0.0.1", port, 1, batch, None, ("alexnet", "resnet18"), 0))
+    p.start()
+    try:
+        runner.wait_for_workers(300)
+        queries = [(m, q, 0, span - 1) for q in range(6) for m in ("alexnet", "resnet18")]
+        done = runner.run_queries(queries)                       # fair share decides the worker counts
+        coord = runner.coord
+        c1, c2, avg = coord.c1(), coord.c2(), dict(coord.avg_time)
+        last_counts = {m: len(coord.worker_set[(m, 5)]) for m in ("alexnet", "resnet18")}
+    finally:
+        runner.shutdown()
+        p.join(timeout=30)
+        if p.is_alive():
+            p.kill()
+    assert len(done) == 12
+    for (m, q), (ind, idx, prob) in done.items():
+        assert np.array_equal(ind, np.arange(span))
+        assert np.array_equal(idx, want[m][1]) and np.array_equal(prob, want[m][2])
+    for m in ("alexnet", "resnet18"):
+        # every image of the six queries finished inside the window: c1 is exactly their count / 30 s
+        assert c1[m] == pytest.approx(6 * span / 30.0)
+        mean_s, q1, q2, q3, sd = c2[m]
+        assert 0 < q1 <= q2 <= q3 and mean_s > 0 and sd >= 0
+        assert avg[m] != 100.0 and avg[m] == pytest.approx(mean_s, rel=0.5)   # measured, no longer the constant
+        # the last query of each model was split over the fair share computed from the measured averages
+        assert 1 <= last_counts[m] <= 2
+    print(f"\n[boxrun] c1 = {c1}  c2 mean s/400 = { {m: round(c2[m][0], 4) for m in c2} }  fair share on 2 ranks = "
+          f"{ {m: sharding.fair_share(m, avg, 2) for m in avg} }  workers of the last queries = {last_counts}")
+    assert p.exitcode == 0

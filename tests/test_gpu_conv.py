@@ -121,3 +121,61 @@ def test_many_tiles_per_cta(built_library):
     x, wt, sc, sh, res, want = _case(*shape, seed=77)
     got = conv2d_nchw(x, wt, sc, sh, res, stride=1, pad=1, relu=True, impl="tc")
     assert _err(got, want) < TOL
+
+
+# Product layers at sizes that select the kernels the batch-400 plans use (round-1 review: these ran only inside
+# whole-model tests of a few images, where the planner picks narrower tiles).
+PRODUCT_SHAPES = [
+    (96, 128, 28, 28, 256, 3, 2, 1, False, True),    # layer3.0.conv1: stride-2 3x3, conv_tc_pair_kernel<256>
+    (150, 256, 14, 14, 512, 3, 2, 1, False, True),   # layer4.0.conv1: the same kernel, two N tiles
+    (8, 128, 28, 28, 256, 1, 2, 0, False, False),    # layer3.0.downsample
+    (8, 256, 14, 14, 512, 1, 2, 0, False, False),    # layer4.0.downsample
+    (6, 384, 13, 13, 256, 3, 1, 1, False, True),     # AlexNet features.8: conv_pair_kernel<256, 3>, Cin 384
+    (6, 256, 13, 13, 256, 3, 1, 1, False, True),     # AlexNet features.10
+]
+
+
+@pytest.mark.parametrize("shape", PRODUCT_SHAPES, ids=lambda s: "x".join(map(str, s)))
+def test_product_layer_shapes(built_library, shape):
+    n, cin, h, w, cout, r, stride, pad, residual, relu = shape
+    x, wt, sc, sh, res, want = _case(*shape, seed=(n * 131 + cin) % 10000)
+    got = conv2d_nchw(x, wt, sc, sh, res, stride=stride, pad=pad, relu=relu, impl="tc")
+    assert got.shape == want.shape
+    assert _err(got, want) < TOL
+
+
+def test_fc6_shape_on_cta_pairs(built_library):
+    """AlexNet classifier.1 as the batch-400 plan runs it: M = 400, K = 9216, N = 4096 on conv_tc_pair_kernel<128>
+    (144 k-blocks through the ring, 32 N tiles, two pair items per N tile)."""
+    g = torch.Generator().manual_seed(9)
+    n, k, m = 400, 9216, 4096
+    x = _bf16_round(torch.randn(n, k, 1, 1, generator=g))
+    wt = _bf16_round(torch.randn(m, k, 1, 1, generator=g) / 96.0)
+    b = torch.randn(m, generator=g)
+    want = F.relu(F.conv2d(x, wt, b)).numpy()
+    got = conv2d_nchw(x.numpy(), wt.numpy(), None, b.numpy(), None, relu=True, impl="tc")
+    assert _err(got, want) < TOL
+
+
+def test_alexnet_stem_as_space_to_depth_conv(built_library):
+    """AlexNet features.0 (11x11, stride 4, pad 2) the way the plan computes it: a 3x3 stride-1 convolution over
+    the 4x4 space-to-depth image (57 x 57 x 48(+16), block origin at pixel (-2, -2); engine.cu build_alexnet).
+    Built here on the host from an NCHW image and the 11x11 weights, run through the library's 3x3 kernel with
+    'same' padding, and compared on the 55 x 55 interior with torch's strided convolution."""
+    g = torch.Generator().manual_seed(13)
+    n = 5
+    x = _bf16_round(torch.randn(n, 3, 224, 224, generator=g))
+    w11 = _bf16_round(torch.randn(64, 3, 11, 11, generator=g) / np.sqrt(363.0))
+    bias = torch.randn(64, generator=g) * 0.1
+    want = F.relu(F.conv2d(x, w11, bias, stride=4, padding=2)).numpy()                     # [n, 64, 55, 55]
+    xp = F.pad(x, (2, 2, 2, 2))                                                             # 228 = 57 * 4
+    s2d = xp.view(n, 3, 57, 4, 57, 4).permute(0, 3, 5, 1, 2, 4).reshape(n, 48, 57, 57)      # channel (dy*4+dx)*3 + c
+    s2d = torch.cat([s2d, torch.zeros(n, 16, 57, 57)], dim=1)
+    w3 = torch.zeros(64, 64, 3, 3)
+    for r in range(11):
+        for s in range(11):
+            a, dy, b_, dx = r // 4, r % 4, s // 4, s % 4
+            w3[:, (dy * 4 + dx) * 3:(dy * 4 + dx) * 3 + 3, a, b_] = w11[:, :, r, s]
+    got = conv2d_nchw(s2d.numpy(), w3.numpy(), None, bias.numpy(), None, stride=1, pad=1, relu=True, impl="tc")
+    # 'same' output pixel (i, j) = valid output (i - 1, j - 1): valid rows/cols 0..54 sit at 1..55
+    assert _err(got[:, :, 1:56, 1:56], want) < TOL

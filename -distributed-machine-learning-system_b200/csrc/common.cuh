@@ -170,8 +170,10 @@ struct ConvParams {
 };
 
 // launchers (conv_tc.cu / conv_simt.cu)
+// A second convolution over the same output tiling that rides in the first one's launch (conv_tc.cu).
+struct ConvSecond { const CUtensorMap* tmA; const CUtensorMap* tmB; const ConvParams* p; };
 int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int block_n,
-                   int num_sms, cudaStream_t st);
+                   int num_sms, cudaStream_t st, const ConvSecond* second = nullptr);
 int launch_conv_simt(const ConvParams& p, cudaStream_t st);
 // Chooses the halo-kernel configuration for a stride-1 multi-tap convolution; returns false when
 // the layer should stay on conv_tc_kernel.  Fills p.halo_* / stages / msub, *block_n, *b_resident.

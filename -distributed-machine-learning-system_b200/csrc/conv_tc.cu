@@ -478,7 +478,14 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo
 template <int BLOCK_N>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ ConvParams p) {
+               const __grid_constant__ ConvParams p, const __grid_constant__ CUtensorMap tmA2,
+               const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ ConvParams p2) {
+  // Optional second problem over the SAME output tiling (p2.num_m_tiles != 0): after tile (m, n) of the first
+  // convolution every role runs tile (m, n) of the second one through the same rings.  ResNet18's 1x1 / stride-2
+  // downsample rides in the launch of the block's 3x3 / stride-2 convolution this way: both read the same
+  // parity planes (the downsample's single tap is the centre tap's box, still in L2), and its short tiles fill
+  // in behind the long ones instead of paying a launch, a pipeline fill and a tail of their own.
+  const int nprob = p2.num_m_tiles != 0 ? 2 : 1;
   using Cfg = TcCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -497,11 +504,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.num_m_tiles * p.num_n_tiles;
-  const int k_blocks = p.num_taps * p.c_blocks;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    if (nprob == 2) { ptx::prefetch_tmap(&tmA2); ptx::prefetch_tmap(&tmB2); }
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -531,17 +538,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
         const int m_tile = tile / p.num_n_tiles;
         const int n_tile = tile - m_tile * p.num_n_tiles;
-        int tap = 0, cb = 0;
-        for (int kb = 0; kb < k_blocks; ++kb) {
-          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
-          const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
-          const uint32_t b_dst = a_dst + Cfg::A_BYTES;
-          ptx::mbar_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
-          ptx::tma_load_2d(a_dst, &tmA, full_bar(s), cb * kBlockK,
-                           m_tile * kBlockM + p.tap_off[tap]);
-          ptx::tma_load_2d(b_dst, &tmB, full_bar(s), kb * kBlockK, n_tile * BLOCK_N);
-          if (++cb == p.c_blocks) { cb = 0; ++tap; }
-          if (++s == kStages) { s = 0; ph ^= 1u; }
+        for (int pr = 0; pr < nprob && alive; ++pr) {
+          const ConvParams& q = pr ? p2 : p;
+          const CUtensorMap* ta = pr ? &tmA2 : &tmA;
+          const CUtensorMap* tb = pr ? &tmB2 : &tmB;
+          const int k_blocks = q.num_taps * q.c_blocks;
+          int tap = 0, cb = 0;
+          for (int kb = 0; kb < k_blocks; ++kb) {
+            if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
+            const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
+            const uint32_t b_dst = a_dst + Cfg::A_BYTES;
+            ptx::mbar_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
+            ptx::tma_load_2d(a_dst, ta, full_bar(s), cb * kBlockK, m_tile * kBlockM + q.tap_off[tap]);
+            ptx::tma_load_2d(b_dst, tb, full_bar(s), kb * kBlockK, n_tile * BLOCK_N);
+            if (++cb == q.c_blocks) { cb = 0; ++tap; }
+            if (++s == kStages) { s = 0; ph ^= 1u; }
+          }
         }
       }
     }
@@ -552,9 +564,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int s = 0, as = 0;
     uint32_t ph = 0, aph = 0;
     bool alive = true;
-    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x)
+    for (int pr = 0; pr < nprob && alive; ++pr) {
+      const int k_blocks = pr ? p2.num_taps * p2.c_blocks : p.num_taps * p.c_blocks;
       // epilogue has drained this accumulator
-      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile, p.profile)) break;
+      if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, tile, p.profile)) { alive = false; break; }
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
       for (int kb = 0; kb < k_blocks; ++kb) {
@@ -585,14 +599,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int row_in_tile = ew * 32 + lane;
     int as = 0;
     uint32_t aph = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    bool alive = true;
+    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x)
+    for (int pr = 0; pr < nprob; ++pr) {
+      const ConvParams& q = pr ? p2 : p;
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
-      const RowInfo ri = decode_row(p, m_tile, row_in_tile);
-      if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) break;
+      const RowInfo ri = decode_row(q, m_tile, row_in_tile);
+      if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) { alive = false; break; }
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
+      epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
@@ -631,7 +648,9 @@ struct TcPairCfg {
 template <int BLOCK_N>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ ConvParams p) {
+                    const __grid_constant__ ConvParams p, const __grid_constant__ CUtensorMap tmA2,
+                    const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ ConvParams p2) {
+  const int nprob = p2.num_m_tiles != 0 ? 2 : 1;        // optional second problem over the same tiling (see conv_tc_kernel)
   using Cfg = TcPairCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -651,11 +670,11 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int pair = (int)(blockIdx.x >> 1), num_pairs = (int)(gridDim.x >> 1);
   const int m_pairs = (p.num_m_tiles + 1) >> 1;
   const int total_items = m_pairs * p.num_n_tiles;
-  const int k_blocks = p.num_taps * p.c_blocks;
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
+    if (nprob == 2) { ptx::prefetch_tmap(&tmA2); ptx::prefetch_tmap(&tmB2); }
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
@@ -681,17 +700,23 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int m_pair = item / p.num_n_tiles;
         const int n_tile = item - m_pair * p.num_n_tiles;
         const int m_tile = 2 * m_pair + (int)rank;
-        int tap = 0, cb = 0;
-        for (int kb = 0; kb < k_blocks; ++kb) {
-          if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
-          const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
-          const uint32_t lead_bar = ptx::mapa(full_bar(s), 0);
-          if (leader) ptx::mbar_expect_tx(full_bar(s), 2u * (uint32_t)Cfg::STAGE_BYTES);
-          ptx::tma_load_2d_pair(a_dst, &tmA, lead_bar, cb * kBlockK, m_tile * kBlockM + p.tap_off[tap]);
-          ptx::tma_load_2d_pair(a_dst + Cfg::A_BYTES, &tmB, lead_bar, kb * kBlockK,
-                                n_tile * BLOCK_N + (int)rank * Cfg::HALF_N);
-          if (++cb == p.c_blocks) { cb = 0; ++tap; }
-          if (++s == kStages) { s = 0; ph ^= 1u; }
+        for (int pr = 0; pr < nprob && alive; ++pr) {
+          const ConvParams& q = pr ? p2 : p;
+          const CUtensorMap* ta = pr ? &tmA2 : &tmA;
+          const CUtensorMap* tb = pr ? &tmB2 : &tmB;
+          const int k_blocks = q.num_taps * q.c_blocks;
+          int tap = 0, cb = 0;
+          for (int kb = 0; kb < k_blocks; ++kb) {
+            if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
+            const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
+            const uint32_t lead_bar = ptx::mapa(full_bar(s), 0);
+            if (leader) ptx::mbar_expect_tx(full_bar(s), 2u * (uint32_t)Cfg::STAGE_BYTES);
+            ptx::tma_load_2d_pair(a_dst, ta, lead_bar, cb * kBlockK, m_tile * kBlockM + q.tap_off[tap]);
+            ptx::tma_load_2d_pair(a_dst + Cfg::A_BYTES, tb, lead_bar, kb * kBlockK,
+                                  n_tile * BLOCK_N + (int)rank * Cfg::HALF_N);
+            if (++cb == q.c_blocks) { cb = 0; ++tap; }
+            if (++s == kStages) { s = 0; ph ^= 1u; }
+          }
         }
       }
     }
@@ -702,8 +727,10 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int s = 0, as = 0;
     uint32_t ph = 0, aph = 0;
     bool alive = true;
-    for (int item = pair; item < total_items && alive; item += num_pairs) {
-      if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) break;
+    for (int item = pair; item < total_items && alive; item += num_pairs)
+    for (int pr = 0; pr < nprob && alive; ++pr) {
+      const int k_blocks = pr ? p2.num_taps * p2.c_blocks : p.num_taps * p.c_blocks;
+      if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) { alive = false; break; }
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
       for (int kb = 0; kb < k_blocks; ++kb) {
@@ -730,14 +757,17 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int chunk0 = (warp - 4) >> 2;
     int as = 0;
     uint32_t aph = 0;
-    for (int item = pair; item < total_items; item += num_pairs) {
+    bool alive = true;
+    for (int item = pair; item < total_items && alive; item += num_pairs)
+    for (int pr = 0; pr < nprob; ++pr) {
+      const ConvParams& q = pr ? p2 : p;
       const int m_pair = item / p.num_n_tiles;
       const int n_tile = item - m_pair * p.num_n_tiles;
-      const RowInfo ri = decode_row(p, 2 * m_pair + (int)rank, ew * 32 + lane);
-      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+      const RowInfo ri = decode_row(q, 2 * m_pair + (int)rank, ew * 32 + lane);
+      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) { alive = false; break; }
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-      epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0);
+      epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
@@ -1858,13 +1888,20 @@ int conv_tc_configure() {
   return IDN_OK;
 }
 
+// The optional second problem of a launch (see conv_tc_kernel): none = a zeroed ConvParams and the first maps again.
+static const ConvParams& no_second_problem() {
+  static const ConvParams z = [] { ConvParams c; std::memset(&c, 0, sizeof(c)); return c; }();
+  return z;
+}
+
 template <int BLOCK_N>
 static int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
-                      int num_sms, cudaStream_t st) {
+                      const ConvSecond* second, int num_sms, cudaStream_t st) {
   const int total = p.num_m_tiles * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   const int grid = total < num_sms ? total : num_sms;
-  IDN_CUDA_TRY(launch_pdl(conv_tc_kernel<BLOCK_N>, dim3(grid), dim3(kThreads), (size_t)TcCfg<BLOCK_N>::SMEM_BYTES, st, tmA, tmB, p));
+  IDN_CUDA_TRY(launch_pdl(conv_tc_kernel<BLOCK_N>, dim3(grid), dim3(kThreads), (size_t)TcCfg<BLOCK_N>::SMEM_BYTES, st, tmA, tmB, p,
+                          second ? *second->tmA : tmA, second ? *second->tmB : tmB, second ? *second->p : no_second_problem()));
   return IDN_OK;
 }
 
@@ -1889,8 +1926,8 @@ bool plan_tc_pair(int num_taps, int n_total, long long m_tiles_cap, int num_sms,
 }
 
 template <int BLOCK_N>
-static int launch_tc_pair_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int num_sms,
-                              cudaStream_t st) {
+static int launch_tc_pair_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
+                              const ConvSecond* second, int num_sms, cudaStream_t st) {
   const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles;
   if (total <= 0) return IDN_OK;
   static int configured[64] = {0};
@@ -1903,16 +1940,22 @@ static int launch_tc_pair_one(const CUtensorMap& tmA, const CUtensorMap& tmB, co
   }
   const int pairs = std::min(total, num_sms / 2);
   IDN_CUDA_TRY(launch_pdl(conv_tc_pair_kernel<BLOCK_N>, dim3(2 * pairs), dim3(kThreads),
-                          (size_t)TcPairCfg<BLOCK_N>::SMEM_BYTES, st, tmA, tmB, p));
+                          (size_t)TcPairCfg<BLOCK_N>::SMEM_BYTES, st, tmA, tmB, p,
+                          second ? *second->tmA : tmA, second ? *second->tmB : tmB, second ? *second->p : no_second_problem()));
   return IDN_OK;
 }
 
 int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p, int block_n,
-                   int num_sms, cudaStream_t st) {
+                   int num_sms, cudaStream_t st, const ConvSecond* second) {
+  if (second && (second->p->num_m_tiles != p.num_m_tiles || second->p->num_n_tiles != p.num_n_tiles ||
+                 second->p->mode != MODE_FLAT || second->p->n_total != p.n_total)) {
+    set_error("launch_conv_tc: the second problem must share the first one's output tiling");
+    return IDN_EINVAL;
+  }
   if (p.tc_pair) {
     if (p.mode != MODE_FLAT || p.num_n_tiles * block_n != p.n_total) { set_error("launch_conv_tc: bad pair shape"); return IDN_EINVAL; }
-    if (block_n == 128) return launch_tc_pair_one<128>(tmA, tmB, p, num_sms, st);
-    if (block_n == 256) return launch_tc_pair_one<256>(tmA, tmB, p, num_sms, st);
+    if (block_n == 128) return launch_tc_pair_one<128>(tmA, tmB, p, second, num_sms, st);
+    if (block_n == 256) return launch_tc_pair_one<256>(tmA, tmB, p, second, num_sms, st);
     set_error("launch_conv_tc: unsupported pair tile");
     return IDN_EINVAL;
   }
@@ -1922,10 +1965,10 @@ int launch_conv_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvPar
   }
   if (p.mode != MODE_FLAT) { set_error("launch_conv_tc: flat layouts only"); return IDN_EINVAL; }
   switch (block_n) {
-    case 64: return launch_one<64>(tmA, tmB, p, num_sms, st);
-    case 128: return launch_one<128>(tmA, tmB, p, num_sms, st);
-    case 192: return launch_one<192>(tmA, tmB, p, num_sms, st);
-    case 256: return launch_one<256>(tmA, tmB, p, num_sms, st);
+    case 64: return launch_one<64>(tmA, tmB, p, second, num_sms, st);
+    case 128: return launch_one<128>(tmA, tmB, p, second, num_sms, st);
+    case 192: return launch_one<192>(tmA, tmB, p, second, num_sms, st);
+    case 256: return launch_one<256>(tmA, tmB, p, second, num_sms, st);
   }
   set_error("launch_conv_tc: unsupported N tile");
   return IDN_EINVAL;

@@ -54,6 +54,8 @@ struct Step {
   ConvParams cp;
   int block_n = 0;
   bool use_halo = false, b_resident = false;   // conv_halo_kernel instead of conv_tc_kernel
+  int second = -1;         // plan step of a convolution that rides in this step's launch (1x1 downsample)
+  int merged_into = -1;    // ... and, on that step, the step whose launch carries it
   // pool
   PoolParams pp;
   // what the step wrote (for idn_read_activation)
@@ -109,6 +111,7 @@ struct idn_engine {
   float* fc_w = nullptr; float* fc_b = nullptr;        // ResNet fp32 FC
   float* fc_wt = nullptr;                              // the same weights transposed [512][1000] (fused head)
   bool no_head_fusion = false;                         // IDN_NO_HEAD_FUSION=1: avgpool, FC, softmax as three kernels
+  bool no_ds_fusion = false;                           // IDN_NO_DS_FUSION=1: 1x1 downsamples as launches of their own
   float* feats = nullptr;                              // ResNet pooled features [cap][512] fp32
   int pre_mode = PRE_OUT_STEM;
   float* logits_pad = nullptr;                         // AlexNet [cap][1024] fp32
@@ -386,6 +389,8 @@ struct BlobReader {
   }
 };
 
+static int try_merge_conv_steps(idn_engine* e, int a, int b, const ConvWeights& wb);
+
 static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
   const int cap = e->cap;
   BlobReader br{blob, count};
@@ -446,6 +451,7 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
       ConvSpec ds; ds.R = 1; ds.S = 1; ds.stride = 2; ds.pad = 0; ds.relu = false;
       IDN_TRY(conv_bn(&wd, C, chans[li - 1], 1, false));
       IDN_TRY(add_conv(e, L + ".0.downsample", planes, wd, ds, d, nullptr, cap));
+      IDN_TRY(try_merge_conv_steps(e, (int)e->steps.size() - 2, (int)e->steps.size() - 1, wd));
       IDN_TRY(add_conv(e, L + ".0.conv2+add", t, w2, c3r, o, &d, cap));
     }
     // ---- block 1: input o, output -> parity planes of the next stage (or `a` for the last)
@@ -649,8 +655,7 @@ static int fill_meta(idn_engine* e, const int64_t* offsets, const int32_t* hw, i
 }
 
 // --------------------------------------------------------------------------------- forward pass
-static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_t st) {
-  ConvParams& cp = s.cp;
+static void prepare_conv_params(idn_engine* e, ConvParams& cp, int n) {
   cp.nimg = n;
   cp.profile = (e->timing && e->wait_profile) ? 1 : 0;
   cp.fd_img_rows = make_fastdiv((unsigned)std::max(cp.img_rows, 1));
@@ -660,6 +665,15 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
   const long long rows = (long long)n * cp.img_rows;
   if (cp.mode == MODE_STEM) cp.num_m_tiles = n * cp.tiles_w * cp.tiles_h;
   else cp.num_m_tiles = (int)((rows + kBlockM - 1) / kBlockM);
+}
+
+// Whether the 1x1 downsample steps ride in the launches of their 3x3 stride-2 partners in this pass.
+static bool ds_fusion_active(const idn_engine* e, int impl) { return impl == IDN_IMPL_TC && !e->no_ds_fusion; }
+
+static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_t st) {
+  ConvParams& cp = s.cp;
+  prepare_conv_params(e, cp, n);
+  const long long rows = (long long)n * cp.img_rows;
   if (impl != IDN_IMPL_TC) return launch_conv_simt(cp, st);
   if (cp.mode == MODE_STEM) return e->stem_simt ? launch_conv_simt(cp, st) : launch_stem_tc(s.tmA, s.tmA2, s.tmB, cp, e->num_sms, st);
   if (s.use_halo) {
@@ -667,7 +681,31 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
     return launch_conv_halo(s.tmA, s.tmA2, s.tmB, cp, s.block_n, s.b_resident, e->num_sms, st);
   }
+  if (s.second >= 0 && ds_fusion_active(e, impl)) {
+    Step& t = e->steps[s.second];
+    prepare_conv_params(e, t.cp, n);
+    const ConvSecond sec{&t.tmA, &t.tmB, &t.cp};
+    return launch_conv_tc(s.tmA, s.tmB, cp, s.block_n, e->num_sms, st, &sec);
+  }
   return launch_conv_tc(s.tmA, s.tmB, cp, s.block_n, e->num_sms, st);
+}
+
+// Lets convolution step `b` (the block's 1x1 / stride-2 downsample) ride in the launch of step `a` (its 3x3 /
+// stride-2 partner): both read the same parity planes and produce the same output geometry, so they share the
+// M x N tiling; b adopts a's N tile and kernel flavour (its weight boxes are re-made to match).
+static int try_merge_conv_steps(idn_engine* e, int a, int b, const ConvWeights& wb) {
+  Step& sa = e->steps[a];
+  Step& sb = e->steps[b];
+  if (sa.use_halo || sb.use_halo || sa.cp.mode != MODE_FLAT || sb.cp.mode != MODE_FLAT) return IDN_OK;
+  if (sa.cp.img_rows != sb.cp.img_rows || sa.cp.wp != sb.cp.wp || sa.cp.n_total != sb.cp.n_total) return IDN_OK;
+  sb.block_n = sa.block_n;
+  sb.cp.tc_pair = sa.cp.tc_pair;
+  sb.cp.num_n_tiles = sa.cp.num_n_tiles;
+  IDN_TRY(make_tmap_2d(&sb.tmB, wb.wt, (uint64_t)wb.ktot, (uint64_t)wb.n_total, (uint64_t)wb.ktot * 2, kBlockK,
+                       (uint32_t)(sb.cp.tc_pair ? sb.block_n / 2 : sb.block_n)));
+  sa.second = b;
+  sb.merged_into = a;
+  return IDN_OK;
 }
 
 static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx, float* d_prob,
@@ -696,6 +734,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
           s.cp.pool_out = fuse ? e->pool_buf : nullptr;
           s.cp.pool_img_rows = e->pool_img_rows; s.cp.pool_wp = e->pool_wp;
         }
+        if (s.merged_into >= 0 && ds_fusion_active(e, e->impl)) { e->launches -= 1; break; }   // rode in that step's launch
         IDN_TRY(launch_conv_step(e, s, n, e->impl, st));
         break;
       case STEP_POOL:
@@ -831,6 +870,7 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   { const char* v = std::getenv("IDN_STEM_SIMT"); e->stem_simt = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_POOL_FUSION"); e->no_pool_fusion = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_HEAD_FUSION"); e->no_head_fusion = v && v[0] == '1'; }
+  { const char* v = std::getenv("IDN_NO_DS_FUSION"); e->no_ds_fusion = v && v[0] == '1'; }
   int rc = IDN_OK;
   auto fail = [&](int code) { idn_engine* raw = e.release(); idn_destroy(raw); return code; };
   {
@@ -1117,7 +1157,8 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
     case STEP_RHEAD: k = h->no_head_fusion ? "avgpool_kernel + fc_fp32_kernel + softmax_top1_kernel" : "resnet_head_kernel"; break;
     case STEP_SOFTMAX: k = "softmax_top1_kernel"; break;
     case STEP_CONV:
-      if (h->impl != IDN_IMPL_TC || (cp.mode == MODE_STEM && h->stem_simt)) k = "conv_simt_kernel";
+      if (s.merged_into >= 0 && h->impl == IDN_IMPL_TC && !h->no_ds_fusion) k = "(rides in the launch of step " + N(s.merged_into) + ")";
+      else if (h->impl != IDN_IMPL_TC || (cp.mode == MODE_STEM && h->stem_simt)) k = "conv_simt_kernel";
       else if (cp.mode == MODE_STEM) k = fuse ? "stem_pool_kernel" : "stem_kernel";
       else if (s.use_halo && cp.pair && s.b_resident) k = "conv_pair_res_kernel<" + N(cp.msub) + ", " + N(cp.num_taps == 9 ? 9 : 0) + ">";
       else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + ">";

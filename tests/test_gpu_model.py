@@ -304,3 +304,43 @@ def test_resnet_head_fusion_is_bit_identical(built_library, monkeypatch):
     assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
     assert np.array_equal(i2, i1) and np.array_equal(p2, p1)
     assert np.array_equal(l3, l1[:1]) and np.array_equal(p3, p1[:1])
+
+
+def test_downsample_riding_in_the_stride2_launch_is_bit_identical(built_library, monkeypatch):
+    """ResNet18's three 1x1 / stride-2 downsample convolutions run as a second problem inside the launch of
+    their 3x3 / stride-2 partner (same parity planes, same output tiling); IDN_NO_DS_FUSION=1 launches them on
+    their own.  The arithmetic is the same, so every logit must be identical -- also layer by layer for the
+    downsample outputs themselves (read back after the merged launch), for a batch that uses the CTA-pair
+    flavour of the kernel (96 images) and for a small one."""
+    sd = make_state_dict("resnet18", 0, "stress")
+    imgs = [synth_image(i, mixed=(i % 4 == 0)) for i in range(96)]
+    with Engine("resnet18", sd, max_batch=96) as eng:
+        names = [n for n, _ in eng.steps()]
+        kern = dict(eng.step_kernels())
+        assert all("rides in the launch" in kern[f"layer{l}.0.downsample"] for l in (2, 3, 4))
+        launches0 = eng.kernel_launches
+        i1, p1, l1 = eng.infer(imgs, want_logits=True)
+        per_pass = eng.kernel_launches - launches0
+        i2, p2, l2 = eng.infer(imgs[:5], want_logits=True)
+        taps = {}
+        for l in (2, 3, 4):
+            si = names.index(f"layer{l}.0.downsample")
+            eng.stop_after(si)
+            eng.infer(imgs[:7])
+            taps[l] = eng.read_activation(si, 7)
+        eng.stop_after(-1)
+    monkeypatch.setenv("IDN_NO_DS_FUSION", "1")
+    with Engine("resnet18", sd, max_batch=96) as eng:
+        launches0 = eng.kernel_launches
+        j1, q1, m1 = eng.infer(imgs, want_logits=True)
+        per_pass_unfused = eng.kernel_launches - launches0
+        for l in (2, 3, 4):
+            si = names.index(f"layer{l}.0.downsample")
+            eng.stop_after(si)
+            eng.infer(imgs[:7])
+            assert np.array_equal(eng.read_activation(si, 7), taps[l]), f"layer{l}.0.downsample"
+        eng.stop_after(-1)
+    assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
+    assert np.array_equal(l2, l1[:5])
+    print(f"\n[resnet18] kernel launches per pass: {per_pass} (downsamples riding along) vs {per_pass_unfused}")
+    assert per_pass == per_pass_unfused - 3 and per_pass <= 20

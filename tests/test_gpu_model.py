@@ -318,8 +318,9 @@ def test_downsample_riding_in_the_stride2_launch_is_bit_identical(built_library,
         names = [n for n, _ in eng.steps()]
         kern = dict(eng.step_kernels())
         assert all("rides in the launch" in kern[f"layer{l}.0.downsample"] for l in (2, 3, 4))
-        launches0 = eng.kernel_launches
         i1, p1, l1 = eng.infer(imgs, want_logits=True)
+        launches0 = eng.kernel_launches                   # second pass: the resample tables are on the device
+        eng.infer(imgs)
         per_pass = eng.kernel_launches - launches0
         i2, p2, l2 = eng.infer(imgs[:5], want_logits=True)
         taps = {}
@@ -331,8 +332,9 @@ def test_downsample_riding_in_the_stride2_launch_is_bit_identical(built_library,
         eng.stop_after(-1)
     monkeypatch.setenv("IDN_NO_DS_FUSION", "1")
     with Engine("resnet18", sd, max_batch=96) as eng:
-        launches0 = eng.kernel_launches
         j1, q1, m1 = eng.infer(imgs, want_logits=True)
+        launches0 = eng.kernel_launches
+        eng.infer(imgs)
         per_pass_unfused = eng.kernel_launches - launches0
         for l in (2, 3, 4):
             si = names.index(f"layer{l}.0.downsample")
@@ -343,4 +345,4 @@ def test_downsample_riding_in_the_stride2_launch_is_bit_identical(built_library,
     assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
     assert np.array_equal(l2, l1[:5])
     print(f"\n[resnet18] kernel launches per pass: {per_pass} (downsamples riding along) vs {per_pass_unfused}")
-    assert per_pass == per_pass_unfused - 3 and per_pass <= 20
+    assert per_pass == per_pass_unfused - 3 and per_pass <= 20, (per_pass, per_pass_unfused)

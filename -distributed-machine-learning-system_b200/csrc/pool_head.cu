@@ -254,21 +254,27 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
 }
 
 // ------------------------------------------------------------------------ ResNet head, ONE kernel
-// avgpool -> fp32 FC -> softmax / top-1 for 11 images per cluster of 4 CTAs (37 clusters = 148 CTAs at
-// batch 400), nothing but the 8 result bytes per image (and, on request, the logits) leaves the chip:
-//   1. every CTA averages a quarter of the channels of the cluster's 11 images (49 pixels, h then w
-//      ascending, then * 1/49: the order of avgpool_kernel) and stores the fp32 features into the shared
-//      memory of all four CTAs (st.shared::cluster);
-//   2. thread (t, group) of CTA r owns class 250 r + t for 6 (5) of the 11 images: one coalesced read of the
-//      transposed fp32 weights per k (fetched a block of 8 ahead), features broadcast from shared memory, k
-//      ascending with fmaf, bias added last
-//      -- the same arithmetic in the same order as fc_fp32_kernel, so the logits are identical bit for bit;
-//      the logits go to the shared memory of the CTA that owns the image (image i -> CTA i % 4);
-//   3. one warp per owned image runs the same warp-shuffle softmax / top-1 as softmax_top1_kernel on the
-//      1000 logits in shared memory.
-constexpr int kHeadImgs = 11, kHeadCluster = 4, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 512;
-constexpr int kHeadHW = 7;
-constexpr int kHeadOwn = (kHeadImgs + kHeadCluster - 1) / kHeadCluster, kHeadC = 512, kHeadPad = 12;
+// avgpool -> fp32 FC -> softmax / top-1 for 23 images per cluster of 8 CTAs (18 clusters = 144 CTAs at batch
+// 400, one wave), nothing but the 8 result bytes per image (and, on request, the logits) leaves the chip:
+//   1. every CTA averages an eighth of the channels of the cluster's 23 images (49 pixels, h then w ascending,
+//      then * 1/49: the order of avgpool_kernel; the 49 loads of an item are all in flight before the first add)
+//      and stores the fp32 features into the shared memory of all eight CTAs (st.shared::cluster);
+//   2. CTA r owns classes 125 r .. 125 r + 124; thread (class, group) accumulates 6 (5) of the 23 images, k
+//      ascending with fmaf, bias added last -- the arithmetic and order of fc_fp32_kernel, so logits are
+//      identical bit for bit.  The CTA's [512 x 125] slice of the transposed fp32 weights streams through a
+//      three-stage shared-memory ring with cp.async (32 rows per stage): the first version read it with plain
+//      loads and was bound by L2 latency -- every cluster asks for the same lines at the same moment (ncu: 70 %
+//      of the samples on FFMAs waiting for their weight).  Logits go to the shared memory of the CTA that owns
+//      the image (image i -> CTA i % 8);
+//   3. one warp per owned image runs the same warp-shuffle softmax / top-1 as softmax_top1_kernel on the 1000
+//      logits in shared memory.
+constexpr int kHeadImgs = 23, kHeadCluster = 8, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 512;
+constexpr int kHeadHW = 7, kHeadC = 512, kHeadPad = 24, kHeadGroup = 6;
+constexpr int kHeadOwn = (kHeadImgs + kHeadCluster - 1) / kHeadCluster;           // 3
+constexpr int kHeadKStage = 32, kHeadStages = 3, kHeadWPitch = 128;
+constexpr int kHeadSmemBytes = (kHeadC * kHeadPad + kHeadOwn * IDN_NUM_CLASSES + kHeadStages * kHeadKStage * kHeadWPitch) * 4;
+static_assert(kHeadClasses * kHeadCluster == IDN_NUM_CLASSES && kHeadClasses <= kHeadWPitch, "class split");
+static_assert((kHeadThreads / 128) * kHeadGroup >= kHeadImgs, "image groups");
 
 __device__ __forceinline__ uint32_t head_mapa(const void* p, uint32_t rank) {
   uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
@@ -282,24 +288,40 @@ __device__ __forceinline__ void head_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void head_cp_async4(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
 
 __global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThreads)
 resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
                    const float* __restrict__ wt /* [512][1000] */, const float* __restrict__ fc_b,
                    float* __restrict__ logits_out, int32_t* __restrict__ idx, float* __restrict__ prob) {
-  __shared__ __align__(16) float s_feat[kHeadC][kHeadPad];            // [k][image]
-  __shared__ __align__(16) float s_logit[kHeadOwn][IDN_NUM_CLASSES];  // rows of the images this CTA owns
+  extern __shared__ __align__(16) float head_smem[];
+  float (*s_feat)[kHeadPad] = reinterpret_cast<float (*)[kHeadPad]>(head_smem);                       // [k][image]
+  float (*s_logit)[IDN_NUM_CLASSES] = reinterpret_cast<float (*)[IDN_NUM_CLASSES]>(head_smem + kHeadC * kHeadPad);
+  float* s_w = head_smem + kHeadC * kHeadPad + kHeadOwn * IDN_NUM_CLASSES;                            // [stage][k][class]
   uint32_t rank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   const int img0 = (int)(blockIdx.x / kHeadCluster) * kHeadImgs;
   const int t = threadIdx.x;
+  const float* wslice = wt + kHeadClasses * (int)rank;
+  auto stage_weights = [&](int stage) {                    // rows [32 stage, 32 stage + 32) of the slice -> ring
+    float* dst = s_w + (stage % kHeadStages) * kHeadKStage * kHeadWPitch;
+    for (int i = t; i < kHeadKStage * kHeadClasses; i += kHeadThreads) {
+      const int row = i / kHeadClasses, col = i - row * kHeadClasses;
+      head_cp_async4(dst + row * kHeadWPitch + col, wslice + (long long)(stage * kHeadKStage + row) * IDN_NUM_CLASSES + col);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  stage_weights(0);                                        // weights do not depend on the previous kernel
+  stage_weights(1);
+  head_cluster_sync();                                     // every CTA of the cluster runs: its shared memory may be written
   pdl_wait();
   pdl_launch_dependents();
-  // ---- 1. global average pool (7 x 7) of channels [128 rank, 128 rank + 128): thread = (channel pair, image);
-  //         the 49 loads of an image are all in flight before the first add
-  for (int item = t; item < 64 * kHeadImgs; item += kHeadThreads) {
-    const int cp = item & 63, im = item >> 6;
-    const int k0 = 128 * (int)rank + 2 * cp;
+  // ---- 1. global average pool (7 x 7) of channels [64 rank, 64 rank + 64): item = (channel pair, image)
+  for (int item = t; item < 32 * kHeadImgs; item += kHeadThreads) {
+    const int cp = item & 31, im = item >> 5;
+    const int k0 = 64 * (int)rank + 2 * cp;
     const int n = img0 + im;
     float s0 = 0.0f, s1 = 0.0f;
     if (n < nimg) {
@@ -323,49 +345,40 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
     }
   }
   head_cluster_sync();
-  // ---- 2. fp32 FC: thread = (class, image group): threads 0..249 take images 0..5 of class 250 rank + t,
-  //         threads 256..505 images 6..10 (the second group's weight loads hit L1).  k ascending, fmaf, bias last.
+  // ---- 2. fp32 FC
   {
-    const int grp = t >> 8, tc = t & 255;
-    if (tc < kHeadClasses) {
-      const int c = kHeadClasses * (int)rank + tc;
-      const int i0 = grp * 6;                                        // images i0 .. i0 + 5 (the last group has 5)
-      float acc[6];
+    const int grp = t >> 7, tc = t & 127;
+    const bool active = tc < kHeadClasses;
+    const int i0 = grp * kHeadGroup;                                 // images i0 .. i0 + 5
+    float acc[kHeadGroup];
 #pragma unroll
-      for (int i = 0; i < 6; ++i) acc[i] = 0.0f;
-      const float* wp_ = wt + c;
-      // Weight loads run three blocks of 8 ahead of the FMAs (the loop is bound by L2 latency otherwise).
-      float w0[8], w1[8], w2[8], w3[8];
-      auto fetch = [&](float (&w)[8], int k0) {
-#pragma unroll
-        for (int u = 0; u < 8; ++u) w[u] = __ldg(wp_ + (long long)(k0 + u) * IDN_NUM_CLASSES);
-      };
-      auto block = [&](const float (&w)[8], int k0) {
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float* f = &s_feat[k0 + u][i0];                      // i0 = 0 or 6: 8-byte aligned
+    for (int i = 0; i < kHeadGroup; ++i) acc[i] = 0.0f;
+    constexpr int kNumStages = kHeadC / kHeadKStage;                 // 16
+    for (int st = 0; st < kNumStages; ++st) {
+      if (st + 2 < kNumStages) stage_weights(st + 2);
+      else asm volatile("cp.async.commit_group;" ::: "memory");     // keep one group per iteration for the wait below
+      asm volatile("cp.async.wait_group 2;" ::: "memory");           // this thread's copies of stage `st` have landed
+      __syncthreads();                                               // ... and everybody else's
+      if (active) {
+        const float* w = s_w + (st % kHeadStages) * kHeadKStage * kHeadWPitch + tc;
+#pragma unroll 8
+        for (int kk = 0; kk < kHeadKStage; ++kk) {
+          const float wv = w[kk * kHeadWPitch];
+          const float* f = &s_feat[st * kHeadKStage + kk][i0];       // i0 * 4 bytes is a multiple of 8
           const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
                        f2 = *reinterpret_cast<const float2*>(f + 4);
-          acc[0] = fmaf(f0.x, w[u], acc[0]); acc[1] = fmaf(f0.y, w[u], acc[1]);
-          acc[2] = fmaf(f1.x, w[u], acc[2]); acc[3] = fmaf(f1.y, w[u], acc[3]);
-          acc[4] = fmaf(f2.x, w[u], acc[4]); acc[5] = fmaf(f2.y, w[u], acc[5]);
+          acc[0] = fmaf(f0.x, wv, acc[0]); acc[1] = fmaf(f0.y, wv, acc[1]);
+          acc[2] = fmaf(f1.x, wv, acc[2]); acc[3] = fmaf(f1.y, wv, acc[3]);
+          acc[4] = fmaf(f2.x, wv, acc[4]); acc[5] = fmaf(f2.y, wv, acc[5]);
         }
-      };
-      fetch(w0, 0); fetch(w1, 8); fetch(w2, 16);
-#pragma unroll 1
-      for (int k0 = 0; k0 < kHeadC; k0 += 32) {
-        fetch(w3, k0 + 24);
-        block(w0, k0);
-        if (k0 + 32 < kHeadC) fetch(w0, k0 + 32);
-        block(w1, k0 + 8);
-        if (k0 + 32 < kHeadC) fetch(w1, k0 + 40);
-        block(w2, k0 + 16);
-        if (k0 + 32 < kHeadC) fetch(w2, k0 + 48);
-        block(w3, k0 + 24);
       }
+      __syncthreads();                                               // the ring slot is rewritten two iterations on
+    }
+    if (active) {
+      const int c = kHeadClasses * (int)rank + tc;
       const float b = __ldg(fc_b + c);
 #pragma unroll
-      for (int i = 0; i < 6; ++i) {
+      for (int i = 0; i < kHeadGroup; ++i) {
         const int im = i0 + i;
         if (im < kHeadImgs)
           head_st_remote(head_mapa(&s_logit[im / kHeadCluster][c], (uint32_t)(im % kHeadCluster)), acc[i] + b);
@@ -373,7 +386,7 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
     }
   }
   head_cluster_sync();
-  // ---- 3. softmax / top-1 of the images this CTA owns: image rank + 4 w by warp w
+  // ---- 3. softmax / top-1 of the images this CTA owns: image rank + 8 w by warp w
   const int warp = t >> 5, lane = t & 31;
   if (warp < kHeadOwn) {
     const int im = (int)rank + kHeadCluster * warp;
@@ -392,9 +405,16 @@ int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, in
     set_error("resnet_head: the fused head is built for 512 features on a 7 x 7 map");
     return IDN_EINVAL;
   }
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(resnet_head_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHeadSmemBytes));
+    configured[dev & 63] = true;
+  }
   const int clusters = (nimg + kHeadImgs - 1) / kHeadImgs;
-  IDN_CUDA_TRY(launch_pdl(resnet_head_kernel, dim3(clusters * kHeadCluster), dim3(kHeadThreads), 0, st, act, nimg,
-                          img_rows, wp, fc_wt, fc_b, logits_out, idx, prob));
+  IDN_CUDA_TRY(launch_pdl(resnet_head_kernel, dim3(clusters * kHeadCluster), dim3(kHeadThreads), (size_t)kHeadSmemBytes, st,
+                          act, nimg, img_rows, wp, fc_wt, fc_b, logits_out, idx, prob));
   return IDN_OK;
 }
 

@@ -477,6 +477,9 @@ def main():
         run_reference(args, rank, world)
         return
 
+    # libraries (NCCL's version banner, ...) must not write into the one-line result: park stdout on stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     import __graft_entry__ as ge
@@ -551,6 +554,8 @@ def main():
         elif drop[0] in line:
             line[drop[0]].pop(drop[1], None)
         text = json.dumps(line)
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     print(text, flush=True)
 
 

@@ -109,7 +109,7 @@ struct idn_engine {
   // head
   const bf16* head_act = nullptr; Geom head_g; int head_C = 0;
   float* fc_w = nullptr; float* fc_b = nullptr;        // ResNet fp32 FC
-  float* fc_wt = nullptr;                              // the same weights transposed [512][1000] (fused head)
+  float* fc_wt = nullptr;                              // the same weights transposed, [8][512][128] (fused head)
   bool no_head_fusion = false;                         // IDN_NO_HEAD_FUSION=1: avgpool, FC, softmax as three kernels
   bool no_ds_fusion = false;                           // IDN_NO_DS_FUSION=1: 1x1 downsamples as launches of their own
   float* feats = nullptr;                              // ResNet pooled features [cap][512] fp32
@@ -476,9 +476,10 @@ static int build_resnet18(idn_engine* e, const float* blob, size_t count) {
   IDN_CUDA_TRY(cudaMemcpy(e->fc_w, fw, (size_t)1000 * 512 * 4, cudaMemcpyHostToDevice));
   IDN_CUDA_TRY(cudaMemcpy(e->fc_b, fb, 4000, cudaMemcpyHostToDevice));
   {
-    std::vector<float> wt((size_t)512 * 1000);
+    // transposed, one contiguous [512][128] slice per cluster rank of the fused head (classes 125 r .. 125 r + 124)
+    std::vector<float> wt((size_t)8 * 512 * 128, 0.0f);
     for (int c = 0; c < 1000; ++c)
-      for (int k = 0; k < 512; ++k) wt[(size_t)k * 1000 + c] = fw[(size_t)c * 512 + k];
+      for (int k = 0; k < 512; ++k) wt[((size_t)(c / 125) * 512 + k) * 128 + (c % 125)] = fw[(size_t)c * 512 + k];
     IDN_TRY(dev_alloc(e, &e->fc_wt, wt.size(), false));
     IDN_CUDA_TRY(cudaMemcpy(e->fc_wt, wt.data(), wt.size() * 4, cudaMemcpyHostToDevice));
   }

@@ -259,22 +259,23 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
 //   1. every CTA averages an eighth of the channels of the cluster's 23 images (49 pixels, h then w ascending,
 //      then * 1/49: the order of avgpool_kernel; the 49 loads of an item are all in flight before the first add)
 //      and stores the fp32 features into the shared memory of all eight CTAs (st.shared::cluster);
-//   2. CTA r owns classes 125 r .. 125 r + 124; thread (class, group) accumulates 6 (5) of the 23 images, k
+//   2. CTA r owns classes 125 r .. 125 r + 124; thread (class, group) accumulates 8 (7) of the 23 images, k
 //      ascending with fmaf, bias added last -- the arithmetic and order of fc_fp32_kernel, so logits are
-//      identical bit for bit.  The CTA's [512 x 125] slice of the transposed fp32 weights streams through a
-//      three-stage shared-memory ring with cp.async (32 rows per stage): the first version read it with plain
-//      loads and was bound by L2 latency -- every cluster asks for the same lines at the same moment (ncu: 70 %
-//      of the samples on FFMAs waiting for their weight).  Logits go to the shared memory of the CTA that owns
-//      the image (image i -> CTA i % 8);
+//      identical bit for bit.  The CTA's slice of the transposed fp32 weights ([512][128], one contiguous block
+//      per cluster rank, built at load time) streams through a three-stage shared-memory ring, ONE 16 KB bulk
+//      copy (cp.async.bulk + mbarrier) per 32 rows: the first version read weights with plain loads and was bound
+//      by L2 latency -- every cluster asks for the same lines at the same moment (ncu: 70 % of the samples on
+//      FFMAs waiting for their weight).  Logits go to the shared memory of the CTA that owns the image (i % 8);
 //   3. one warp per owned image runs the same warp-shuffle softmax / top-1 as softmax_top1_kernel on the 1000
 //      logits in shared memory.
-constexpr int kHeadImgs = 23, kHeadCluster = 8, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 512;
-constexpr int kHeadHW = 7, kHeadC = 512, kHeadPad = 24, kHeadGroup = 6;
+constexpr int kHeadImgs = 23, kHeadCluster = 8, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 384;
+constexpr int kHeadHW = 7, kHeadC = 512, kHeadPad = 24, kHeadGroup = 8;
 constexpr int kHeadOwn = (kHeadImgs + kHeadCluster - 1) / kHeadCluster;           // 3
 constexpr int kHeadKStage = 32, kHeadStages = 3, kHeadWPitch = 128;
-constexpr int kHeadSmemBytes = (kHeadC * kHeadPad + kHeadOwn * IDN_NUM_CLASSES + kHeadStages * kHeadKStage * kHeadWPitch) * 4;
+constexpr int kHeadStageBytes = kHeadKStage * kHeadWPitch * 4;                      // 16 KB: one bulk copy
+constexpr int kHeadSmemBytes = (kHeadC * kHeadPad + kHeadOwn * IDN_NUM_CLASSES + kHeadStages * kHeadKStage * kHeadWPitch) * 4 + 64;
 static_assert(kHeadClasses * kHeadCluster == IDN_NUM_CLASSES && kHeadClasses <= kHeadWPitch, "class split");
-static_assert((kHeadThreads / 128) * kHeadGroup >= kHeadImgs, "image groups");
+static_assert((kHeadThreads / 128) * kHeadGroup >= kHeadImgs && (kHeadThreads / 128) * kHeadGroup <= kHeadPad, "image groups");
 
 __device__ __forceinline__ uint32_t head_mapa(const void* p, uint32_t rank) {
   uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
@@ -288,33 +289,43 @@ __device__ __forceinline__ void head_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void head_cp_async4(float* smem_dst, const float* gsrc) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+__device__ __forceinline__ void head_bulk_load(float* smem_dst, const float* gsrc, uint32_t bytes, uint64_t* bar) {
+  const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(b), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes), "r"(b) : "memory");
+}
+__device__ __forceinline__ void head_bar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+  uint32_t ok = 0;
+  while (!ok)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(b), "r"(parity) : "memory");
 }
 
 __global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThreads)
 resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
-                   const float* __restrict__ wt /* [512][1000] */, const float* __restrict__ fc_b,
-                   float* __restrict__ logits_out, int32_t* __restrict__ idx, float* __restrict__ prob) {
+                   const float* __restrict__ wt8 /* [8 ranks][512][128]: transposed, one slice per cluster rank */,
+                   const float* __restrict__ fc_b, float* __restrict__ logits_out, int32_t* __restrict__ idx,
+                   float* __restrict__ prob) {
   extern __shared__ __align__(16) float head_smem[];
   float (*s_feat)[kHeadPad] = reinterpret_cast<float (*)[kHeadPad]>(head_smem);                       // [k][image]
   float (*s_logit)[IDN_NUM_CLASSES] = reinterpret_cast<float (*)[IDN_NUM_CLASSES]>(head_smem + kHeadC * kHeadPad);
   float* s_w = head_smem + kHeadC * kHeadPad + kHeadOwn * IDN_NUM_CLASSES;                            // [stage][k][class]
+  uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_w + kHeadStages * kHeadKStage * kHeadWPitch);        // full[stage]
   uint32_t rank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   const int img0 = (int)(blockIdx.x / kHeadCluster) * kHeadImgs;
   const int t = threadIdx.x;
-  const float* wslice = wt + kHeadClasses * (int)rank;
-  auto stage_weights = [&](int stage) {                    // rows [32 stage, 32 stage + 32) of the slice -> ring
-    float* dst = s_w + (stage % kHeadStages) * kHeadKStage * kHeadWPitch;
-    for (int i = t; i < kHeadKStage * kHeadClasses; i += kHeadThreads) {
-      const int row = i / kHeadClasses, col = i - row * kHeadClasses;
-      head_cp_async4(dst + row * kHeadWPitch + col, wslice + (long long)(stage * kHeadKStage + row) * IDN_NUM_CLASSES + col);
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-  stage_weights(0);                                        // weights do not depend on the previous kernel
-  stage_weights(1);
+  const float* wslice = wt8 + (size_t)rank * kHeadC * kHeadWPitch;
+  constexpr int kNumStages = kHeadC / kHeadKStage;                 // 16 stages of 32 rows = 16 KB each
+  if (t == 0) {
+    for (int i = 0; i < kHeadStages; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"((uint32_t)__cvta_generic_to_shared(&s_bar[i])) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int i = 0; i < kHeadStages; ++i)                  // weights do not depend on the previous kernel: start now
+      head_bulk_load(s_w + i * kHeadKStage * kHeadWPitch, wslice + (size_t)i * kHeadKStage * kHeadWPitch, kHeadStageBytes, &s_bar[i]);
+  }
   head_cluster_sync();                                     // every CTA of the cluster runs: its shared memory may be written
   pdl_wait();
   pdl_launch_dependents();
@@ -345,36 +356,33 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
     }
   }
   head_cluster_sync();
-  // ---- 2. fp32 FC
+  // ---- 2. fp32 FC: thread = (class, group of 8 images)
   {
     const int grp = t >> 7, tc = t & 127;
-    const bool active = tc < kHeadClasses;
-    const int i0 = grp * kHeadGroup;                                 // images i0 .. i0 + 5
+    const int i0 = grp * kHeadGroup;                                 // images i0 .. i0 + 7 (slot 23 is padding)
     float acc[kHeadGroup];
 #pragma unroll
     for (int i = 0; i < kHeadGroup; ++i) acc[i] = 0.0f;
-    constexpr int kNumStages = kHeadC / kHeadKStage;                 // 16
     for (int st = 0; st < kNumStages; ++st) {
-      if (st + 2 < kNumStages) stage_weights(st + 2);
-      else asm volatile("cp.async.commit_group;" ::: "memory");     // keep one group per iteration for the wait below
-      asm volatile("cp.async.wait_group 2;" ::: "memory");           // this thread's copies of stage `st` have landed
-      __syncthreads();                                               // ... and everybody else's
-      if (active) {
-        const float* w = s_w + (st % kHeadStages) * kHeadKStage * kHeadWPitch + tc;
+      const int slot = st % kHeadStages;
+      head_bar_wait(&s_bar[slot], (uint32_t)((st / kHeadStages) & 1));
+      const float* w = s_w + slot * kHeadKStage * kHeadWPitch + tc;
 #pragma unroll 8
-        for (int kk = 0; kk < kHeadKStage; ++kk) {
-          const float wv = w[kk * kHeadWPitch];
-          const float* f = &s_feat[st * kHeadKStage + kk][i0];       // i0 * 4 bytes is a multiple of 8
-          const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
-                       f2 = *reinterpret_cast<const float2*>(f + 4);
-          acc[0] = fmaf(f0.x, wv, acc[0]); acc[1] = fmaf(f0.y, wv, acc[1]);
-          acc[2] = fmaf(f1.x, wv, acc[2]); acc[3] = fmaf(f1.y, wv, acc[3]);
-          acc[4] = fmaf(f2.x, wv, acc[4]); acc[5] = fmaf(f2.y, wv, acc[5]);
-        }
+      for (int kk = 0; kk < kHeadKStage; ++kk) {
+        const float wv = w[kk * kHeadWPitch];
+        const float4 f0 = *reinterpret_cast<const float4*>(&s_feat[st * kHeadKStage + kk][i0]);
+        const float4 f1 = *reinterpret_cast<const float4*>(&s_feat[st * kHeadKStage + kk][i0 + 4]);
+        acc[0] = fmaf(f0.x, wv, acc[0]); acc[1] = fmaf(f0.y, wv, acc[1]);
+        acc[2] = fmaf(f0.z, wv, acc[2]); acc[3] = fmaf(f0.w, wv, acc[3]);
+        acc[4] = fmaf(f1.x, wv, acc[4]); acc[5] = fmaf(f1.y, wv, acc[5]);
+        acc[6] = fmaf(f1.z, wv, acc[6]); acc[7] = fmaf(f1.w, wv, acc[7]);
       }
-      __syncthreads();                                               // the ring slot is rewritten two iterations on
+      __syncthreads();                                               // everybody is done with this ring slot
+      if (t == 0 && st + kHeadStages < kNumStages)
+        head_bulk_load(s_w + slot * kHeadKStage * kHeadWPitch, wslice + (size_t)(st + kHeadStages) * kHeadKStage * kHeadWPitch,
+                       kHeadStageBytes, &s_bar[slot]);
     }
-    if (active) {
+    if (tc < kHeadClasses) {
       const int c = kHeadClasses * (int)rank + tc;
       const float b = __ldg(fc_b + c);
 #pragma unroll

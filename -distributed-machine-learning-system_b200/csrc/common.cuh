@@ -208,8 +208,8 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
                        const float* fc_w, const float* fc_b, float* feats, float* logits,
                        int32_t* idx, float* prob, cudaStream_t st);
 int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
-                             const float* fc_wt, const float* fc_b, float* logits_out_or_null, int32_t* idx,
-                             float* prob, cudaStream_t st);
+                             const float* fc_wt, const float* fc_b, float* feats, float* logits_out_or_null,
+                             int32_t* idx, float* prob, cudaStream_t st);
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out_or_null,
                         int32_t* idx, float* prob, cudaStream_t st);
 // Copies n_words 32-bit words with SM loads/stores.  Used for the few KB of per-batch records that come

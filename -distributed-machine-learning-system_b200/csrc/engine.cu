@@ -746,7 +746,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
       case STEP_RHEAD:
         if (!e->no_head_fusion) {
           IDN_TRY(launch_resnet_head_fused(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,
-                                           e->head_g.W, e->head_C, e->fc_wt, e->fc_b, d_logits, d_idx, d_prob, st));
+                                           e->head_g.W, e->head_C, e->fc_wt, e->fc_b, e->feats, d_logits, d_idx, d_prob, st));
           break;
         }
         IDN_TRY(launch_resnet_head(e->head_act, n, e->head_g.img_rows(), e->head_g.Wp, e->head_g.H,

@@ -257,8 +257,8 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
 // avgpool -> fp32 FC -> softmax / top-1 for 23 images per cluster of 8 CTAs (18 clusters = 144 CTAs at batch
 // 400, one wave), nothing but the 8 result bytes per image (and, on request, the logits) leaves the chip:
 //   1. every CTA averages an eighth of the channels of the cluster's 23 images (49 pixels, h then w ascending,
-//      then * 1/49: the order of avgpool_kernel; the 49 loads of an item are all in flight before the first add)
-//      and stores the fp32 features into the shared memory of all eight CTAs (st.shared::cluster);
+//      then * 1/49: the order of avgpool_kernel; the 49 loads of an item are all in flight before the first add);
+//      the eight slices meet in every CTA's shared memory by way of a small global scratch (L2) and a cluster barrier;
 //   2. CTA r owns classes 125 r .. 125 r + 124; thread (class, group) accumulates 8 (7) of the 23 images, k
 //      ascending with fmaf, bias added last -- the arithmetic and order of fc_fp32_kernel, so logits are
 //      identical bit for bit.  The CTA's slice of the transposed fp32 weights ([512][128], one contiguous block
@@ -306,8 +306,8 @@ __device__ __forceinline__ void head_bar_wait(uint64_t* bar, uint32_t parity) {
 __global__ void __cluster_dims__(kHeadCluster, 1, 1) __launch_bounds__(kHeadThreads)
 resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
                    const float* __restrict__ wt8 /* [8 ranks][512][128]: transposed, one slice per cluster rank */,
-                   const float* __restrict__ fc_b, float* __restrict__ logits_out, int32_t* __restrict__ idx,
-                   float* __restrict__ prob) {
+                   const float* __restrict__ fc_b, float* feats /* [n][512] scratch */, float* __restrict__ logits_out,
+                   int32_t* __restrict__ idx, float* __restrict__ prob) {
   extern __shared__ __align__(16) float head_smem[];
   float (*s_feat)[kHeadPad] = reinterpret_cast<float (*)[kHeadPad]>(head_smem);                       // [k][image]
   float (*s_logit)[IDN_NUM_CLASSES] = reinterpret_cast<float (*)[IDN_NUM_CLASSES]>(head_smem + kHeadC * kHeadPad);
@@ -349,13 +349,19 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
       }
     }
     const float inv = 1.0f / (float)(kHeadHW * kHeadHW);
-#pragma unroll
-    for (uint32_t r = 0; r < (uint32_t)kHeadCluster; ++r) {
-      head_st_remote(head_mapa(&s_feat[k0][im], r), s0 * inv);
-      head_st_remote(head_mapa(&s_feat[k0 + 1][im], r), s1 * inv);
-    }
+    if (n < nimg) *reinterpret_cast<float2*>(feats + (long long)n * kHeadC + k0) = make_float2(s0 * inv, s1 * inv);
   }
+  // The eight CTAs exchange their channel slices through global memory (L2): a warp writes 256 contiguous
+  // bytes and reads them back coalesced.  (Storing each value into eight remote shared memories cost one
+  // 4-byte DSMEM transaction per lane and store -- ~12 k of them arriving per CTA -- and was most of the kernel.)
+  __threadfence();
   head_cluster_sync();
+  for (int i = t; i < kHeadImgs * kHeadC; i += kHeadThreads) {
+    const int im = i / kHeadC, k = i - im * kHeadC;
+    const int n = img0 + im;
+    s_feat[k][im] = n < nimg ? __ldcg(feats + (long long)n * kHeadC + k) : 0.0f;
+  }
+  __syncthreads();
   // ---- 2. fp32 FC: thread = (class, group of 8 images)
   {
     const int grp = t >> 7, tc = t & 127;
@@ -406,7 +412,7 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
 }
 
 int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
-                             const float* fc_wt, const float* fc_b, float* logits_out, int32_t* idx,
+                             const float* fc_wt, const float* fc_b, float* feats, float* logits_out, int32_t* idx,
                              float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
   if (C != kHeadC || H != kHeadHW || W != kHeadHW || fc_wt == nullptr) {
@@ -422,7 +428,7 @@ int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, in
   }
   const int clusters = (nimg + kHeadImgs - 1) / kHeadImgs;
   IDN_CUDA_TRY(launch_pdl(resnet_head_kernel, dim3(clusters * kHeadCluster), dim3(kHeadThreads), (size_t)kHeadSmemBytes, st,
-                          act, nimg, img_rows, wp, fc_wt, fc_b, logits_out, idx, prob));
+                          act, nimg, img_rows, wp, fc_wt, fc_b, feats, logits_out, idx, prob));
   return IDN_OK;
 }
 

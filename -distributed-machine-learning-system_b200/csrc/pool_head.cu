@@ -259,7 +259,7 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
 //   1. every CTA averages an eighth of the channels of the cluster's 23 images (49 pixels, h then w ascending,
 //      then * 1/49: the order of avgpool_kernel; the 49 loads of an item are all in flight before the first add);
 //      the eight slices meet in every CTA's shared memory by way of a small global scratch (L2) and a cluster barrier;
-//   2. CTA r owns classes 125 r .. 125 r + 124; thread (class, group) accumulates 8 (7) of the 23 images, k
+//   2. CTA r owns classes 125 r .. 125 r + 124; a thread accumulates 4 classes x 6 images in registers, k
 //      ascending with fmaf, bias added last -- the arithmetic and order of fc_fp32_kernel, so logits are
 //      identical bit for bit.  The CTA's slice of the transposed fp32 weights ([512][128], one contiguous block
 //      per cluster rank, built at load time) streams through a three-stage shared-memory ring, ONE 16 KB bulk
@@ -269,13 +269,13 @@ fc_fp32_kernel(const float* __restrict__ feats, int nimg, int C, const float* __
 //   3. one warp per owned image runs the same warp-shuffle softmax / top-1 as softmax_top1_kernel on the 1000
 //      logits in shared memory.
 constexpr int kHeadImgs = 23, kHeadCluster = 8, kHeadClasses = IDN_NUM_CLASSES / kHeadCluster, kHeadThreads = 384;
-constexpr int kHeadHW = 7, kHeadC = 512, kHeadPad = 24, kHeadGroup = 8;
+constexpr int kHeadHW = 7, kHeadC = 512, kHeadPad = 24, kHeadGroup = 6, kHeadIGroups = 4;
 constexpr int kHeadOwn = (kHeadImgs + kHeadCluster - 1) / kHeadCluster;           // 3
 constexpr int kHeadKStage = 32, kHeadStages = 3, kHeadWPitch = 128;
 constexpr int kHeadStageBytes = kHeadKStage * kHeadWPitch * 4;                      // 16 KB: one bulk copy
 constexpr int kHeadSmemBytes = (kHeadC * kHeadPad + kHeadOwn * IDN_NUM_CLASSES + kHeadStages * kHeadKStage * kHeadWPitch) * 4 + 64;
 static_assert(kHeadClasses * kHeadCluster == IDN_NUM_CLASSES && kHeadClasses <= kHeadWPitch, "class split");
-static_assert((kHeadThreads / 128) * kHeadGroup >= kHeadImgs && (kHeadThreads / 128) * kHeadGroup <= kHeadPad, "image groups");
+static_assert(kHeadIGroups * kHeadGroup >= kHeadImgs && kHeadIGroups * kHeadGroup <= kHeadPad && kHeadIGroups * 32 <= kHeadThreads, "image groups");
 
 __device__ __forceinline__ uint32_t head_mapa(const void* p, uint32_t rank) {
   uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
@@ -362,40 +362,56 @@ resnet_head_kernel(const bf16* __restrict__ act, int nimg, int img_rows, int wp,
     s_feat[k][im] = n < nimg ? __ldcg(feats + (long long)n * kHeadC + k) : 0.0f;
   }
   __syncthreads();
-  // ---- 2. fp32 FC: thread = (class, group of 8 images)
+  // ---- 2. fp32 FC: thread = 4 classes x 6 images (128 threads: 32 class groups x 4 image groups).  The loop is
+  //         bound by shared-memory wavefronts (a warp-wide load costs one per 128 requested bytes, broadcast or
+  //         not), so each thread reuses what it loads: 10 words for 24 FMAs per k.  k ascending, fmaf, bias last.
   {
-    const int grp = t >> 7, tc = t & 127;
-    const int i0 = grp * kHeadGroup;                                 // images i0 .. i0 + 7 (slot 23 is padding)
-    float acc[kHeadGroup];
+    const int cg = t & 31, ig = t >> 5;                              // ig < 4 computes; the other warps only wait
+    const bool worker = ig < kHeadIGroups;
+    const int i0 = ig * kHeadGroup;
+    float acc[kHeadGroup][4];
 #pragma unroll
-    for (int i = 0; i < kHeadGroup; ++i) acc[i] = 0.0f;
+    for (int i = 0; i < kHeadGroup; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
     for (int st = 0; st < kNumStages; ++st) {
       const int slot = st % kHeadStages;
-      head_bar_wait(&s_bar[slot], (uint32_t)((st / kHeadStages) & 1));
-      const float* w = s_w + slot * kHeadKStage * kHeadWPitch + tc;
-#pragma unroll 8
-      for (int kk = 0; kk < kHeadKStage; ++kk) {
-        const float wv = w[kk * kHeadWPitch];
-        const float4 f0 = *reinterpret_cast<const float4*>(&s_feat[st * kHeadKStage + kk][i0]);
-        const float4 f1 = *reinterpret_cast<const float4*>(&s_feat[st * kHeadKStage + kk][i0 + 4]);
-        acc[0] = fmaf(f0.x, wv, acc[0]); acc[1] = fmaf(f0.y, wv, acc[1]);
-        acc[2] = fmaf(f0.z, wv, acc[2]); acc[3] = fmaf(f0.w, wv, acc[3]);
-        acc[4] = fmaf(f1.x, wv, acc[4]); acc[5] = fmaf(f1.y, wv, acc[5]);
-        acc[6] = fmaf(f1.z, wv, acc[6]); acc[7] = fmaf(f1.w, wv, acc[7]);
+      if (worker) {
+        head_bar_wait(&s_bar[slot], (uint32_t)((st / kHeadStages) & 1));
+        const float* w = s_w + slot * kHeadKStage * kHeadWPitch + 4 * cg;
+#pragma unroll 4
+        for (int kk = 0; kk < kHeadKStage; ++kk) {
+          const float4 wv = *reinterpret_cast<const float4*>(w + kk * kHeadWPitch);
+          const float* f = &s_feat[st * kHeadKStage + kk][i0];       // i0 * 4 bytes is a multiple of 8
+          const float2 f0 = *reinterpret_cast<const float2*>(f), f1 = *reinterpret_cast<const float2*>(f + 2),
+                       f2 = *reinterpret_cast<const float2*>(f + 4);
+          const float fv[kHeadGroup] = {f0.x, f0.y, f1.x, f1.y, f2.x, f2.y};
+#pragma unroll
+          for (int i = 0; i < kHeadGroup; ++i) {
+            acc[i][0] = fmaf(fv[i], wv.x, acc[i][0]); acc[i][1] = fmaf(fv[i], wv.y, acc[i][1]);
+            acc[i][2] = fmaf(fv[i], wv.z, acc[i][2]); acc[i][3] = fmaf(fv[i], wv.w, acc[i][3]);
+          }
+        }
       }
       __syncthreads();                                               // everybody is done with this ring slot
       if (t == 0 && st + kHeadStages < kNumStages)
         head_bulk_load(s_w + slot * kHeadKStage * kHeadWPitch, wslice + (size_t)(st + kHeadStages) * kHeadKStage * kHeadWPitch,
                        kHeadStageBytes, &s_bar[slot]);
     }
-    if (tc < kHeadClasses) {
-      const int c = kHeadClasses * (int)rank + tc;
-      const float b = __ldg(fc_b + c);
+    if (worker) {
 #pragma unroll
-      for (int i = 0; i < kHeadGroup; ++i) {
-        const int im = i0 + i;
-        if (im < kHeadImgs)
-          head_st_remote(head_mapa(&s_logit[im / kHeadCluster][c], (uint32_t)(im % kHeadCluster)), acc[i] + b);
+      for (int j = 0; j < 4; ++j) {
+        const int cl = 4 * cg + j;
+        if (cl < kHeadClasses) {
+          const int c = kHeadClasses * (int)rank + cl;
+          const float b = __ldg(fc_b + c);
+#pragma unroll
+          for (int i = 0; i < kHeadGroup; ++i) {
+            const int im = i0 + i;
+            if (im < kHeadImgs)
+              head_st_remote(head_mapa(&s_logit[im / kHeadCluster][c], (uint32_t)(im % kHeadCluster)), acc[i][j] + b);
+          }
+        }
       }
     }
   }

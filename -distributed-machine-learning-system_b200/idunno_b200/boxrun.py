@@ -31,7 +31,7 @@ from datetime import timedelta
 import numpy as np
 
 from .coordinator import BoxCoordinator
-from .dist import merge_idempotent
+from .dist import merge_chunks
 
 HEARTBEAT_S = 0.25
 LOSS_TIMEOUT_S = 2.0          # the reference's ping timeout (mp4_machinelearning.py:847)
@@ -190,7 +190,7 @@ class BoxRunner:
         indices ascending.  ``on_tick(runner)`` is called once per monitor iteration (the kill
         scenario uses it to shoot a worker at a chosen moment)."""
         todo = list(queries)
-        open_q = {}                                   # (model, qnum) -> merged {index: (top1, prob)}
+        open_q = {}                                   # (model, qnum) -> [(indices, top1, prob)] in arrival order
         done = {}
         local_results, errors = {}, []
         stop = threading.Event()
@@ -206,7 +206,7 @@ class BoxRunner:
                     if sum(1 for k in open_q if k[0] == model) >= max_in_flight:
                         continue
                     todo.remove(q)
-                    open_q[(model, qnum)] = {}
+                    open_q[(model, qnum)] = []
                     kw = {} if n_workers is None else {"n_workers": n_workers}
                     for (rank, ss, ee, _, _, _) in self.coord.assign(model, qnum, s, e, **kw):
                         self._dispatch(rank, model, qnum, ss, ee)
@@ -222,13 +222,10 @@ class BoxRunner:
                         elif self.store.check([_res_key(model, qnum, ss, ee)]):
                             got = _unpack(self.store.get(_res_key(model, qnum, ss, ee)))
                         if got is not None:
-                            merge_idempotent(open_q[key], *got)
+                            open_q[key].append(got)     # idempotent: a shard delivered twice merges to one
                             self.coord.mark_finished(model, qnum, ss, ee)
                     if self.coord.query_done(model, qnum):
-                        merged = open_q.pop(key)
-                        ind = np.asarray(sorted(merged), dtype=np.int64)
-                        done[key] = (ind, np.asarray([merged[i][0] for i in ind], dtype=np.int32),
-                                     np.asarray([merged[i][1] for i in ind], dtype=np.float32))
+                        done[key] = merge_chunks(open_q.pop(key))
                 # liveness
                 for r in self._dead_ranks():
                     t = time.monotonic()

@@ -58,3 +58,19 @@ def merge_idempotent(results: dict, indices, idx, prob):
     for i, k, p in zip(indices, idx, prob):
         results[int(i)] = (int(k), float(p))
     return results
+
+
+def merge_chunks(chunks):
+    """The same idempotent merge on whole arrays (the box runner's hot path: a per-image Python dict cost
+    more than classifying the images): ``chunks`` = [(indices, idx, prob)] in arrival order -> (indices,
+    idx, prob) sorted by image index, the LAST report of an image winning."""
+    if not chunks:
+        return (np.zeros(0, np.int64), np.zeros(0, np.int32), np.zeros(0, np.float32))
+    ind = np.concatenate([np.asarray(c[0], dtype=np.int64) for c in chunks])
+    idx = np.concatenate([np.asarray(c[1], dtype=np.int32) for c in chunks])
+    prob = np.concatenate([np.asarray(c[2], dtype=np.float32) for c in chunks])
+    order = np.argsort(ind, kind="stable")                 # stable: equal indices stay in arrival order
+    ind, idx, prob = ind[order], idx[order], prob[order]
+    last = np.ones(len(ind), dtype=bool)
+    last[:-1] = ind[1:] != ind[:-1]                        # keep the last of every run of equal indices
+    return ind[last], idx[last], prob[last]

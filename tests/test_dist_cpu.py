@@ -62,3 +62,20 @@ def test_shard_for_rank_and_merge():
     idist.merge_idempotent(res, [1, 2], [5, 6], [0.5, 0.25])
     idist.merge_idempotent(res, [2, 3], [6, 7], [0.25, 0.125])     # shard 2.. re-run elsewhere
     assert res == {1: (5, 0.5), 2: (6, 0.25), 3: (7, 0.125)}
+
+
+def test_merge_chunks_is_the_idempotent_merge():
+    from idunno_b200.dist import merge_chunks, merge_idempotent
+    rng = np.random.default_rng(3)
+    chunks = []
+    for s, e in ((10, 19), (0, 9), (10, 19), (25, 29)):          # one shard delivered twice, a gap
+        ind = np.arange(s, e + 1)
+        chunks.append((ind, rng.integers(0, 1000, len(ind)).astype(np.int32), rng.random(len(ind)).astype(np.float32)))
+    want = {}
+    for c in chunks:
+        merge_idempotent(want, *c)
+    ind, idx, prob = merge_chunks(chunks)
+    assert list(ind) == sorted(want)
+    assert [int(k) for k in idx] == [want[i][0] for i in ind]
+    assert np.array_equal(prob, np.asarray([want[i][1] for i in ind], dtype=np.float32))
+    assert merge_chunks([])[0].shape == (0,)

@@ -282,11 +282,9 @@ def bench_model(model, rank, world, device, args, peaks, dist):
     copies(40)
     dt_copy = time.perf_counter() - t0
     barrier()
-    h2d_gbs = 40 * BATCH * IMG_BYTES / dt_copy / 1e9          # this rank's rate while every rank copies
-    if world > 1:
-        t = torch.tensor([h2d_gbs], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        h2d_gbs = float(t.item())
+    # aggregate rate while every rank copies: all bytes over the SLOWEST rank's time (summing per-rank rates would
+    # credit a rank that finishes early with bandwidth the others then inherit)
+    h2d_gbs = world * 40 * BATCH * IMG_BYTES / max_over_ranks(dt_copy) / 1e9
     ceiling = h2d_gbs * 1e9 / IMG_BYTES
     e2e = {"value": round(e2e_value, 1), "unit": "images/s", "h2d_bytes_per_step": BATCH * IMG_BYTES + BATCH * 24,
            "d2h_bytes_per_step": BATCH * 8, "single_call_value": round(single, 1),

@@ -20,27 +20,32 @@ suite)
   echo "suite rc=$? $(tail -1 gpurun_out/suite.log)" ;;
 bench)
   timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err
-  echo "bench rc=$?"; cat gpurun_out/bench.json | cut -c1-1500 ;;
+  echo "bench rc=$?"; cat gpurun_out/bench.json | cut -c1-1500
+  for m in alexnet resnet18; do python tools/kms.py gpurun_out/bench_detail.json $m; done ;;
 benchref)
   timeout 900 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
   echo "benchref rc=$?"; cut -c1-600 gpurun_out/bench_ref.json ;;
 ncu)
   for m in alexnet resnet18; do
-    # one pass = 14 launches (alexnet) / 26 (resnet18); skip the 3 warm-up passes, list 2 passes
-    if [ $m = alexnet ]; then SK=42; CN=28; else SK=78; CN=52; fi
-    timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_$m.log 2>&1 &&
+    # one pass = 15 launches (alexnet) / 20 (resnet18) incl. the record copy; skip the 3 warm-up passes, list 2 passes
+    if [ $m = alexnet ]; then SK=45; CN=30; else SK=60; CN=40; fi
+    B="--steps 2 --warmup 3 --sustain 0 --range-images 0 --no-cpu --models $m"
+    timeout 600 python bench.py $B > gpurun_out/ncu_plain_$m.log 2>&1 &&
     timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s $SK -c $CN --csv \
-        --log-file gpurun_out/launches_$m.csv python bench.py --steps 2 --warmup 3 --models $m \
+        --log-file gpurun_out/launches_$m.csv python bench.py $B \
         > gpurun_out/ncu_launch_$m.log 2>&1
     echo "ncu launches $m rc=$?"
   done ;;
 ncufull)
   m=${NCU_MODEL:-resnet18}
-  timeout 600 python bench.py --steps 2 --warmup 3 --models $m > gpurun_out/ncu_plain_full.log 2>&1 &&
-  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:${NCU_REGEX:-conv_tc_kernel} \
-      -s ${NCU_SKIP:-60} -c ${NCU_COUNT:-20} -o gpurun_out/prof_${NCU_TAG:-$m} -f python bench.py --steps 2 --warmup 3 --models $m \
+  B="--steps 2 --warmup 3 --sustain 0 --range-images 0 --no-cpu --models $m"
+  timeout 600 python bench.py $B > gpurun_out/ncu_plain_full.log 2>&1 &&
+  timeout 1500 ncu --set full --clock-control none --import-source on -k regex:${NCU_REGEX:-kernel} \
+      -s ${NCU_SKIP:-60} -c ${NCU_COUNT:-20} -o gpurun_out/prof_${NCU_TAG:-$m} -f python bench.py $B \
       > gpurun_out/ncu_full_$m.log 2>&1
   echo "ncu full $m rc=$?" ;;
+smoke)
+  timeout 900 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; grep "^smoke" gpurun_out/smoke.log ;;
 scen)
   timeout 1500 python tools/box_scenarios.py --gpus ${SCEN_GPUS:-2} --scenario ${SCEN_WHAT:-all} \
       --batches ${SCEN_BATCHES:-64,128,256,512,1024,2048,4096} --per-rank ${SCEN_PER_RANK:-10000} \

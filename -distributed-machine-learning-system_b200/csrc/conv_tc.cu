@@ -341,7 +341,10 @@ struct TcCfg {
   static constexpr int B_BYTES = BLOCK_N * kBlockK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int kStages = BLOCK_N <= 64 ? 8 : BLOCK_N <= 128 ? 6 : BLOCK_N <= 192 ? 5 : 4;
-  static constexpr int TMEM_COLS = 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
+  // Four accumulator stages where they fit: with a second problem per tile (a 4-MMA downsample behind a
+  // 36-MMA convolution) two stages make the issuer wait for the long tile's epilogue on every tile.
+  static constexpr int kAcc = BLOCK_N <= 128 ? 4 : 2;
+  static constexpr int TMEM_COLS = kAcc * BLOCK_N <= 128 ? 128 : kAcc * BLOCK_N <= 256 ? 256 : 512;
   static constexpr int BAR_BYTES = 256;
   static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + 1024;  // + align slack
 };
@@ -416,6 +419,55 @@ struct ChunkAffine {
   }
 };
 
+// One 16-column chunk of one accumulator row.  The residual (if any) arrives in rr: the caller loads it, either
+// right here (epilogue_tile) or ahead of the accumulator (conv_halo_kernel, whose residual addresses do not
+// depend on the MMAs, so their latency hides behind the wait for the accumulator).
+template <int BLOCK_N>
+__device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const RowInfo& ri, const uint32_t (&v)[16],
+                                               int col, const float4* s4, const float4* b4,
+                                               const uint32_t (&rr)[8], bool has_res) {
+  if (ri.valid) {
+    float y[16];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4[j].x, b4[j].x);
+      y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4[j].y, b4[j].y);
+      y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4[j].z, b4[j].z);
+      y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4[j].w, b4[j].w);
+    }
+    if (has_res) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        y[2 * e + 0] += __uint_as_float(rr[e] << 16);
+        y[2 * e + 1] += __uint_as_float(rr[e] & 0xffff0000u);
+      }
+    }
+    if (p.out_f32) {
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) y[j] = fmaxf(y[j], 0.0f);
+      }
+      float* op = reinterpret_cast<float*>(p.out) + ri.dst_row * p.ldc + col;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        uint32_t w[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) w[e] = __float_as_uint(y[8 * j + e]);
+        ptx::st_global_256(op + 8 * j, w);
+      }
+    } else {
+      uint32_t w[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) w[e] = pack_bf16x2(y[2 * e], y[2 * e + 1]);
+      if (p.relu) {                // max(round(x), 0) == round(max(x, 0)): two channels per instruction
+#pragma unroll
+        for (int e = 0; e < 8; ++e) w[e] = relu_bf16x2(w[e]);
+      }
+      ptx::st_global_256(reinterpret_cast<bf16*>(p.out) + ri.dst_row * p.ldc + col, w);
+    }
+  }
+}
+
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
                                               int col0, int chunk0, const ChunkAffine* hoisted = nullptr) {
@@ -432,46 +484,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo
     uint32_t rr[8];
     if (has_res) ptx::ld_global_256(p.residual + ri.res_row * p.ldc + col, rr);
     ptx::tmem_ld_wait();
-    if (ri.valid) {
-      float y[16];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        y[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), s4[j].x, b4[j].x);
-        y[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), s4[j].y, b4[j].y);
-        y[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), s4[j].z, b4[j].z);
-        y[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), s4[j].w, b4[j].w);
-      }
-      if (has_res) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          y[2 * e + 0] += __uint_as_float(rr[e] << 16);
-          y[2 * e + 1] += __uint_as_float(rr[e] & 0xffff0000u);
-        }
-      }
-      if (p.out_f32) {
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) y[j] = fmaxf(y[j], 0.0f);
-        }
-        float* op = reinterpret_cast<float*>(p.out) + ri.dst_row * p.ldc + col;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          uint32_t w[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) w[e] = __float_as_uint(y[8 * j + e]);
-          ptx::st_global_256(op + 8 * j, w);
-        }
-      } else {
-        uint32_t w[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) w[e] = pack_bf16x2(y[2 * e], y[2 * e + 1]);
-        if (p.relu) {                // max(round(x), 0) == round(max(x, 0)): two channels per instruction
-#pragma unroll
-          for (int e = 0; e < 8; ++e) w[e] = relu_bf16x2(w[e]);
-        }
-        ptx::st_global_256(reinterpret_cast<bf16*>(p.out) + ri.dst_row * p.ldc + col, w);
-      }
-    }
+    epilogue_chunk<BLOCK_N>(p, ri, v, col, s4, b4, rr, has_res);
   }
 }
 
@@ -487,17 +500,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // in behind the long ones instead of paying a launch, a pipeline fill and a tail of their own.
   const int nprob = p2.num_m_tiles != 0 ? 2 : 1;
   using Cfg = TcCfg<BLOCK_N>;
-  constexpr int kStages = Cfg::kStages;
+  constexpr int kAcc = Cfg::kAcc;              // accumulator stages in TMEM
   extern __shared__ uint8_t smem_raw[];
 
   const uint32_t raw_u32 = ptx::smem_u32(smem_raw);
   const uint32_t base = (raw_u32 + 1023u) & ~1023u;   // SWIZZLE_128B tiles need 1024-byte alignment
+  constexpr int kStages = Cfg::kStages;
+  constexpr uint32_t kStageBytes = Cfg::STAGE_BYTES;
   const uint32_t bar_base = base + kStages * Cfg::STAGE_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + kAcc + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 2 * kAcc);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw_u32));
 
@@ -515,7 +530,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < kAcc; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
       ptx::mbar_init(tempty_bar(a), kEpiWarps);   // one arrive per epilogue warp
     }
@@ -546,9 +561,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           int tap = 0, cb = 0;
           for (int kb = 0; kb < k_blocks; ++kb) {
             if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
-            const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
+            const uint32_t a_dst = base + s * kStageBytes;
             const uint32_t b_dst = a_dst + Cfg::A_BYTES;
-            ptx::mbar_expect_tx(full_bar(s), Cfg::STAGE_BYTES);
+            ptx::mbar_expect_tx(full_bar(s), kStageBytes);
             ptx::tma_load_2d(a_dst, ta, full_bar(s), cb * kBlockK, m_tile * kBlockM + q.tap_off[tap]);
             ptx::tma_load_2d(b_dst, tb, full_bar(s), kb * kBlockK, n_tile * BLOCK_N);
             if (++cb == q.c_blocks) { cb = 0; ++tap; }
@@ -575,7 +590,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (!mbar_wait(full_bar(s), ph, 2, kb, p.profile)) { alive = false; break; }   // TMA bytes landed
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint32_t a_addr = base + s * Cfg::STAGE_BYTES;
+          const uint32_t a_addr = base + s * kStageBytes;
           const uint64_t da = make_sw128_desc(a_addr);
           const uint64_t db = make_sw128_desc(a_addr + Cfg::A_BYTES);
 #pragma unroll
@@ -590,7 +605,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         __syncwarp();
         if (++s == kStages) { s = 0; ph ^= 1u; }
       }
-      if (++as == 2) { as = 0; aph ^= 1u; }
+      if (++as == kAcc) { as = 0; aph ^= 1u; }
     }
   } else if (warp >= 4) {
     // ================================ epilogue ====================================
@@ -613,7 +628,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
-      if (++as == 2) { as = 0; aph ^= 1u; }
+      if (++as == kAcc) { as = 0; aph ^= 1u; }
     }
   }
 
@@ -997,14 +1012,48 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
       const int m_item = item / p.num_n_tiles;
       const int n_tile = item - m_item * p.num_n_tiles;
-      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
-      ptx::tc_fence_after();
+      if (p.residual == nullptr) {
+        if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+        ptx::tc_fence_after();
 #pragma unroll 1
-      for (int sub = 0; sub < MSUB; ++sub) {
-        const RowInfo ri = decode_row(p, m_item * MSUB + sub, ew * 32 + lane);
-        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) +
-                               (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
-        epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0, BLOCK_N == 64 ? &aff : nullptr);
+        for (int sub = 0; sub < MSUB; ++sub) {
+          const RowInfo ri = decode_row(p, m_item * MSUB + sub, ew * 32 + lane);
+          const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) +
+                                 (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
+          epilogue_tile<BLOCK_N>(p, ri, taddr, n_tile * BLOCK_N, chunk0, BLOCK_N == 64 ? &aff : nullptr);
+        }
+      } else {
+        // residual layers: this warp's residual rows of the item do not depend on the accumulator -- the first
+        // kPf chunks are requested before waiting for it, the rest kPf chunks ahead of their use
+        constexpr int kCh = BLOCK_N / 64;                 // 16-column chunks per warp and sub-tile
+        constexpr int kSteps = MSUB * kCh;
+        constexpr int kPf = kSteps < 2 ? kSteps : 2;
+        RowInfo ri[MSUB];
+#pragma unroll
+        for (int sub = 0; sub < MSUB; ++sub) ri[sub] = decode_row(p, m_item * MSUB + sub, ew * 32 + lane);
+        uint32_t rr[kPf][8];
+        auto request = [&](int step, uint32_t (&dst)[8]) {
+          const int sub = step / kCh, col = n_tile * BLOCK_N + (chunk0 + 4 * (step % kCh)) * 16;
+          if (ri[sub].valid) ptx::ld_global_256(p.residual + ri[sub].res_row * p.ldc + col, dst);
+        };
+#pragma unroll
+        for (int k = 0; k < kPf; ++k) request(k, rr[k]);
+        if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int step = 0; step < kSteps; ++step) {
+          const int sub = step / kCh, c0 = (chunk0 + 4 * (step % kCh)) * 16, col = n_tile * BLOCK_N + c0;
+          const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) +
+                                 (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
+          uint32_t v[16];
+          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)c0, v);
+          ChunkAffine loc;
+          if (BLOCK_N > 64) loc.load(p, col);
+          ptx::tmem_ld_wait();
+          epilogue_chunk<BLOCK_N>(p, ri[sub], v, col, BLOCK_N > 64 ? loc.s4 : aff.s4, BLOCK_N > 64 ? loc.b4 : aff.b4,
+                                  rr[step % kPf], ri[sub].valid);
+          if (step + kPf < kSteps) request(step + kPf, rr[step % kPf]);
+        }
       }
       ptx::tc_fence_before();
       __syncwarp();

@@ -40,7 +40,7 @@ for _p in (ROOT, PKG):
 
 import numpy as np  # noqa: E402
 
-BATCH = 400
+BATCH = int(os.environ.get("IDN_BENCH_BATCH", "400"))   # experiments only: the contract workload is 400
 IMG_BYTES = 224 * 224 * 3
 FLOP_PER_IMG = {"alexnet": 1428376960, "resnet18": 3628146688}
 PRE_BYTES_PER_IMG = 451584                                            # 224x224 source, bf16 out

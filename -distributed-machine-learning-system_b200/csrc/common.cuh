@@ -167,6 +167,11 @@ struct ConvParams {
   // output is not stored, stem_pool_kernel writes the pooled pixels to pool_out with plain stores.
   bf16* pool_out;             // nullptr: plain stem
   int pool_img_rows, pool_wp, pool_oh, pool_ow;
+  // conv_tc_pair_kernel, FC layers: split-K.  A function of the LAYER's shape only, never of the batch, so
+  // that an image's result does not depend on the engine's capacity or on the tensor batch it falls in.
+  int split_k;                // 0 / 1: off
+  float* splitk_ws;           // fp32 partial tiles [tile half][split][128][N tile]
+  unsigned int* splitk_cnt;   // per tile half: {arrivals, slices reduced}; zero between launches
 };
 
 // launchers (conv_tc.cu / conv_simt.cu)

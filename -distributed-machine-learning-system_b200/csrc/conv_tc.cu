@@ -248,6 +248,19 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
       : "memory");
 }
 
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.b32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 }  // namespace ptx
 
 // Diagnostics of a pipeline stall: [0] = 1 when a wait timed out, [1] = role (0 producer, 1 MMA
@@ -405,6 +418,9 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // issued before the first wait; a thread's 32 output bytes are one full sector (256-bit store).
 constexpr int kEpiWarps = 16;
 constexpr int kThreads = 128 + 32 * kEpiWarps;
+__device__ __forceinline__ void epi_bar_sync() {            // the 16 epilogue warps only
+  asm volatile("bar.sync 1, %0;" :: "n"(32 * kEpiWarps) : "memory");
+}
 
 // Per-channel scale/shift of one 16-column chunk.  With a 64-wide N tile and one N tile per layer a warp
 // always handles the same chunk, so these 32 values are loaded once per kernel (their L2 latency used to
@@ -684,7 +700,15 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const bool leader = rank == 0;
   const int pair = (int)(blockIdx.x >> 1), num_pairs = (int)(gridDim.x >> 1);
   const int m_pairs = (p.num_m_tiles + 1) >> 1;
-  const int total_items = m_pairs * p.num_n_tiles;
+  // Split-K (p.split_k = S > 1, single problem; narrow FC layers): S work items per output tile, item `mn * S + ks`
+  // covers k-blocks [ks * kbs, (ks + 1) * kbs).  Each writes its fp32 partial tile to p.splitk_ws, books itself on
+  // the tile's counter and waits for the other S - 1 (neighbouring pairs of the same persistent grid); then every
+  // split reduces its own 128 / S rows, adding the S partials in split order -- the sum does not depend on timing
+  // -- and runs the normal epilogue on them.
+  const int S = p.split_k > 1 ? p.split_k : 1;
+  const int total_items = m_pairs * p.num_n_tiles * S;
+  const int kbs = (p.num_taps * p.c_blocks + S - 1) / S;
+  const uint32_t split_flag = bar_base + 8u * (2 * kStages + 5);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -712,16 +736,18 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t ph = 0;
       bool alive = true;
       for (int item = pair; item < total_items && alive; item += num_pairs) {
-        const int m_pair = item / p.num_n_tiles;
-        const int n_tile = item - m_pair * p.num_n_tiles;
+        const int mn = item / S, ks = item - mn * S;
+        const int m_pair = mn / p.num_n_tiles;
+        const int n_tile = mn - m_pair * p.num_n_tiles;
         const int m_tile = 2 * m_pair + (int)rank;
         for (int pr = 0; pr < nprob && alive; ++pr) {
           const ConvParams& q = pr ? p2 : p;
           const CUtensorMap* ta = pr ? &tmA2 : &tmA;
           const CUtensorMap* tb = pr ? &tmB2 : &tmB;
           const int k_blocks = q.num_taps * q.c_blocks;
-          int tap = 0, cb = 0;
-          for (int kb = 0; kb < k_blocks; ++kb) {
+          const int kb0 = S > 1 ? ks * kbs : 0, kb1 = S > 1 ? min(k_blocks, kb0 + kbs) : k_blocks;
+          int tap = kb0 / q.c_blocks, cb = kb0 - tap * q.c_blocks;
+          for (int kb = kb0; kb < kb1; ++kb) {
             if (!mbar_wait(empty_bar(s), ph ^ 1u, 0, kb, p.profile)) { alive = false; break; }
             const uint32_t a_dst = base + s * Cfg::STAGE_BYTES;
             const uint32_t lead_bar = ptx::mapa(full_bar(s), 0);
@@ -745,10 +771,11 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int item = pair; item < total_items && alive; item += num_pairs)
     for (int pr = 0; pr < nprob && alive; ++pr) {
       const int k_blocks = pr ? p2.num_taps * p2.c_blocks : p.num_taps * p.c_blocks;
+      const int kb0 = S > 1 ? (item % S) * kbs : 0, kb1 = S > 1 ? min(k_blocks, kb0 + kbs) : k_blocks;
       if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) { alive = false; break; }
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
-      for (int kb = 0; kb < k_blocks; ++kb) {
+      for (int kb = kb0; kb < kb1; ++kb) {
         if (!mbar_wait(full_bar(s), ph, 2, kb, p.profile)) { alive = false; break; }
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
@@ -757,9 +784,9 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint64_t db = make_sw128_desc(a_addr + Cfg::A_BYTES);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)
-            ptx::umma_bf16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_bf16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb != kb0 || k != 0) ? 1u : 0u);
           ptx::umma_commit_pair(empty_bar(s));
-          if (kb == k_blocks - 1) ptx::umma_commit_pair(tfull_bar(as));
+          if (kb == kb1 - 1) ptx::umma_commit_pair(tfull_bar(as));
         }
         __syncwarp();
         if (++s == kStages) { s = 0; ph ^= 1u; }
@@ -776,16 +803,107 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int item = pair; item < total_items && alive; item += num_pairs)
     for (int pr = 0; pr < nprob; ++pr) {
       const ConvParams& q = pr ? p2 : p;
-      const int m_pair = item / p.num_n_tiles;
-      const int n_tile = item - m_pair * p.num_n_tiles;
+      const int mn = item / S, ks = item - mn * S;
+      const int m_pair = mn / p.num_n_tiles;
+      const int n_tile = mn - m_pair * p.num_n_tiles;
       const RowInfo ri = decode_row(q, 2 * m_pair + (int)rank, ew * 32 + lane);
       if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) { alive = false; break; }
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-      epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+      if (S == 1) {
+        epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0);
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+      } else {
+        // this CTA's 128 x BLOCK_N fp32 partials of the tile: [tile half][split][row][column]
+        float* tile_ws = p.splitk_ws + (size_t)(mn * 2 + (int)rank) * S * (kBlockM * BLOCK_N);
+        float* mine = tile_ws + (size_t)ks * (kBlockM * BLOCK_N) + (ew * 32 + lane) * BLOCK_N;
+#pragma unroll 1
+        for (int c0 = chunk0 * 16; c0 < BLOCK_N; c0 += 64) {
+          uint32_t v[16];
+          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)c0, v);
+          ptx::tmem_ld_wait();
+          uint32_t lo[8], hi[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { lo[e] = v[e]; hi[e] = v[8 + e]; }
+          ptx::st_global_256(mine + c0, lo);
+          ptx::st_global_256(mine + c0 + 8, hi);
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+        __threadfence();
+        epi_bar_sync();                                  // every partial of this CTA is written and fenced
+        unsigned int* cnt = p.splitk_cnt + 2 * (mn * 2 + (int)rank);   // [0] arrivals, [1] slices reduced
+        if (threadIdx.x == 128) {
+          atomicAdd(cnt, 1u);
+          // The S items of a tile sit in neighbouring pairs of one persistent grid (or in this pair's next
+          // round, which only ever waits for items further down the list): the others do arrive.
+          const unsigned long long t0 = ptx::globaltimer();
+          unsigned int spins = 0;
+          bool ok = true;
+          while (ptx::ld_acquire_gpu(cnt) < (unsigned int)S) {
+            if ((++spins & 0xffu) == 0 && ptx::globaltimer() - t0 > 2000000000ull) {
+              if (atomicCAS(&g_tc_watchdog[0], 0u, 1u) == 0u) {
+                g_tc_watchdog[1] = 7u; g_tc_watchdog[2] = blockIdx.x; g_tc_watchdog[3] = (unsigned)item;
+              }
+              ok = false;
+              break;
+            }
+          }
+          ptx::sts32(split_flag, ok ? 1u : 0u);
+        }
+        epi_bar_sync();
+        if (ptx::lds32(split_flag) == 0u) { alive = false; break; }
+        // every split reduces its own 128 / S rows of the tile half: partials added in split order
+        {
+          constexpr int kF4PerRow = BLOCK_N / 4;
+          const int per_split = kBlockM * kF4PerRow / S;                  // float4 elements of this slice
+          const float4* ws4 = reinterpret_cast<const float4*>(tile_ws);
+          const int et = (int)threadIdx.x - 128;
+          for (int e0 = et; e0 < per_split; e0 += 4 * 32 * kEpiWarps) {
+            float4 acc[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int sp = 0; sp < S; ++sp) {
+              float4 t[4];
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * 32 * kEpiWarps;
+                t[u] = e < per_split ? __ldcg(ws4 + (size_t)sp * (kBlockM * kF4PerRow) + ks * per_split + e)
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+              }
+#pragma unroll
+              for (int u = 0; u < 4; ++u) { acc[u].x += t[u].x; acc[u].y += t[u].y; acc[u].z += t[u].z; acc[u].w += t[u].w; }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = ks * per_split + e0 + u * 32 * kEpiWarps;
+              if (e0 + u * 32 * kEpiWarps >= per_split) continue;
+              const int row = e / kF4PerRow, col = n_tile * BLOCK_N + (e - row * kF4PerRow) * 4;
+              const RowInfo r2 = decode_row(q, 2 * m_pair + (int)rank, row);
+              if (!r2.valid) continue;
+              const float4 sc = __ldg(reinterpret_cast<const float4*>(q.scale + col));
+              const float4 sh = __ldg(reinterpret_cast<const float4*>(q.shift + col));
+              float4 y = make_float4(fmaf(acc[u].x, sc.x, sh.x), fmaf(acc[u].y, sc.y, sh.y),
+                                     fmaf(acc[u].z, sc.z, sh.z), fmaf(acc[u].w, sc.w, sh.w));
+              if (q.relu) { y.x = fmaxf(y.x, 0.f); y.y = fmaxf(y.y, 0.f); y.z = fmaxf(y.z, 0.f); y.w = fmaxf(y.w, 0.f); }
+              if (q.out_f32) {
+                *reinterpret_cast<float4*>(reinterpret_cast<float*>(q.out) + r2.dst_row * q.ldc + col) = y;
+              } else {
+                uint2 w;
+                w.x = pack_bf16x2(y.x, y.y); w.y = pack_bf16x2(y.z, y.w);
+                *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(q.out) + r2.dst_row * q.ldc + col) = w;
+              }
+            }
+          }
+        }
+        epi_bar_sync();                                  // this CTA's reads of the partials are done
+        if (threadIdx.x == 128) {
+          if (atomicAdd(cnt + 1, 1u) == (unsigned int)(S - 1)) { cnt[0] = 0u; cnt[1] = 0u; }   // last slice: reset
+        }
+      }
       if (++as == 2) { as = 0; aph ^= 1u; }
     }
   }
@@ -1614,9 +1732,6 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
   return v;
 }
-__device__ __forceinline__ void epi_bar_sync() {            // the 16 epilogue warps only
-  asm volatile("bar.sync 1, %0;" :: "n"(32 * kEpiWarps) : "memory");
-}
 // address of 16-byte chunk `c16` (0..7) of pixel `pix` in a [pixels][128 B] buffer, chunks swizzled by pixel
 __device__ __forceinline__ uint32_t sp_chunk(uint32_t buf, int pix, int c16) {
   return buf + (uint32_t)pix * 128u + (uint32_t)((c16 ^ (pix & 7)) << 4);
@@ -1977,8 +2092,13 @@ bool plan_tc_pair(int num_taps, int n_total, long long m_tiles_cap, int num_sms,
 template <int BLOCK_N>
 static int launch_tc_pair_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvParams& p,
                               const ConvSecond* second, int num_sms, cudaStream_t st) {
-  const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles;
+  const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles * (p.split_k > 1 ? p.split_k : 1);
   if (total <= 0) return IDN_OK;
+  if (p.split_k > 1 && (second || p.splitk_ws == nullptr || p.splitk_cnt == nullptr || p.residual != nullptr ||
+                        (p.split_k - 1) * ((p.num_taps * p.c_blocks + p.split_k - 1) / p.split_k) >= p.num_taps * p.c_blocks)) {
+    set_error("launch_conv_tc: bad split-K setup");
+    return IDN_EINVAL;
+  }
   static int configured[64] = {0};
   int dev = 0;
   cudaGetDevice(&dev);

@@ -128,6 +128,9 @@ struct idn_engine {
   int pool_img_rows = 0, pool_wp = 0;
   bool no_pool_fusion = false;
   int last_n = 0;
+  // split-K scratch of the FC layers, shared by all of them (they run one after the other)
+  float* splitk_ws = nullptr; size_t splitk_ws_floats = 0;
+  unsigned int* splitk_cnt = nullptr; size_t splitk_cnt_n = 0;
 };
 
 namespace idn {
@@ -308,6 +311,33 @@ static int add_conv(idn_engine* e, const std::string& name, const Act& src, cons
   }
   st.block_n = pick_block_n(cw.n_total, m_tiles_cap, e->num_sms);
   cp.tc_pair = plan_tc_pair(cp.num_taps, cw.n_total, m_tiles_cap, e->num_sms, &st.block_n) ? 1 : 0;
+  // Narrow FC layers (one row per image, long K, N <= 1024: AlexNet's FC8 is 4 x 2 tile pairs of 64 k-blocks for
+  // 74 CTA pairs): 256-wide pair tiles with split-K.  The split is a function of the layer's shape alone (never
+  // of the capacity or the batch), so every engine adds the same partial sums in the same order.  Wider FC
+  // layers fill the machine without it and lost a little to the extra pass (FC7 27 -> 31 us).
+  static const bool no_split = [] { const char* v = std::getenv("IDN_NO_FC_SPLIT"); return v && v[0] == '1'; }();
+  const int k_blocks = cp.num_taps * cp.c_blocks;
+  if (!no_split && cp.num_taps == 1 && tg.img_rows() == 1 && residual == nullptr && k_blocks >= 32 &&
+      cw.n_total % 256 == 0 && cw.n_total <= 1024 && e->num_sms % 2 == 0) {
+    int split = 1;
+    while (split < 8 && split * 2 * (cw.n_total / 256) <= 32 && k_blocks / (split * 2) >= 8 &&
+           k_blocks % (split * 2) == 0) split *= 2;
+    if (split > 1) {
+      cp.tc_pair = 1;
+      st.block_n = 256;
+      cp.split_k = split;
+      const size_t halves = (size_t)((m_tiles_cap + 1) / 2) * 2 * (cw.n_total / 256);
+      const size_t ws_floats = halves * split * kBlockM * 256;
+      if (ws_floats > e->splitk_ws_floats) {
+        IDN_TRY(dev_alloc(e, &e->splitk_ws, ws_floats, false));      // earlier, smaller one stays in dev_allocs
+        e->splitk_ws_floats = ws_floats;
+      }
+      if (halves > e->splitk_cnt_n) {
+        IDN_TRY(dev_alloc(e, &e->splitk_cnt, 2 * halves));
+        e->splitk_cnt_n = halves;
+      }
+    }
+  }
   cp.num_n_tiles = cw.n_total / st.block_n;
   IDN_TRY(make_tmap_2d(&st.tmA, src.ptr, (uint64_t)src.C, (uint64_t)src.rows(),
                        (uint64_t)src.C * 2, kBlockK, kBlockM));
@@ -682,6 +712,7 @@ static int launch_conv_step(idn_engine* e, Step& s, int n, int impl, cudaStream_
     cp.num_m_tiles = (int)((rows + item_rows - 1) / item_rows);
     return launch_conv_halo(s.tmA, s.tmA2, s.tmB, cp, s.block_n, s.b_resident, e->num_sms, st);
   }
+  if (cp.split_k > 1) { cp.splitk_ws = e->splitk_ws; cp.splitk_cnt = e->splitk_cnt; }
   if (s.second >= 0 && ds_fusion_active(e, impl)) {
     Step& t = e->steps[s.second];
     prepare_conv_params(e, t.cp, n);

@@ -348,6 +348,9 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
          ((uint32_t)(m >> 4) << 24);
 }
 
+constexpr int kAffMax = 512;                 // see stage_affine()
+constexpr int kAffBytes = 2 * kAffMax * 4;
+
 template <int BLOCK_N>
 struct TcCfg {
   static constexpr int A_BYTES = kBlockM * kBlockK * 2;          // 16 KiB
@@ -359,7 +362,7 @@ struct TcCfg {
   static constexpr int kAcc = BLOCK_N <= 128 ? 4 : 2;
   static constexpr int TMEM_COLS = kAcc * BLOCK_N <= 128 ? 128 : kAcc * BLOCK_N <= 256 ? 256 : 512;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + 1024;  // + align slack
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + 2 * kAffBytes + 1024;  // + align slack
 };
 
 struct RowInfo {
@@ -433,7 +436,33 @@ struct ChunkAffine {
 #pragma unroll
     for (int j = 0; j < 4; ++j) { s4[j] = __ldg(sc + j); b4[j] = __ldg(sh + j); }
   }
+  // from the copy stage_affine() made in shared memory: scale[kAffMax] then shift[kAffMax]
+  __device__ __forceinline__ void load_smem(uint32_t saff, int col);
 };
+
+// Scale/shift of layers with up to kAffMax output channels are copied to shared memory once per kernel.  Read from
+// global memory per chunk (wide tiles cannot keep them in registers) their latency was most of the epilogue's time:
+// the few KB of L1 beside 200+ KB of shared memory do not hold them (ncu: the FFMA behind the load carried the
+// epilogue warps' stall samples), and ResNet18's stride-2 layers were bound by the epilogue.
+__device__ __forceinline__ void ChunkAffine::load_smem(uint32_t saff, int col) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(s4[j].x), "=f"(s4[j].y), "=f"(s4[j].z), "=f"(s4[j].w) : "r"(saff + (uint32_t)(col + 4 * j) * 4u));
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(b4[j].x), "=f"(b4[j].y), "=f"(b4[j].z), "=f"(b4[j].w)
+                 : "r"(saff + (uint32_t)(kAffMax + col + 4 * j) * 4u));
+  }
+}
+// all threads of the CTA, before a __syncthreads(); returns the address to hand to the epilogue (0: not staged)
+__device__ __forceinline__ uint32_t stage_affine(uint32_t saff, const ConvParams& p) {
+  if (p.n_total > kAffMax) return 0u;
+  for (int i = threadIdx.x; i < p.n_total; i += blockDim.x) {
+    asm volatile("st.shared.f32 [%0], %1;" :: "r"(saff + (uint32_t)i * 4u), "f"(__ldg(p.scale + i)) : "memory");
+    asm volatile("st.shared.f32 [%0], %1;" :: "r"(saff + (uint32_t)(kAffMax + i) * 4u), "f"(__ldg(p.shift + i)) : "memory");
+  }
+  return saff;
+}
 
 // One 16-column chunk of one accumulator row.  The residual (if any) arrives in rr: the caller loads it, either
 // right here (epilogue_tile) or ahead of the accumulator (conv_halo_kernel, whose residual addresses do not
@@ -486,14 +515,17 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const RowInf
 
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
-                                              int col0, int chunk0, const ChunkAffine* hoisted = nullptr) {
+                                              int col0, int chunk0, const ChunkAffine* hoisted = nullptr,
+                                              uint32_t saff = 0u) {
 #pragma unroll 1
   for (int c0 = chunk0 * 16; c0 < BLOCK_N; c0 += 64) {
     uint32_t v[16];
     ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)c0, v);
     const int col = col0 + c0;
     ChunkAffine loc;
-    if (BLOCK_N > 64 || hoisted == nullptr) loc.load(p, col);
+    if (BLOCK_N > 64 || hoisted == nullptr) {
+      if (saff != 0u) loc.load_smem(saff, col); else loc.load(p, col);
+    }
     const float4* s4 = (BLOCK_N > 64 || hoisted == nullptr) ? loc.s4 : hoisted->s4;
     const float4* b4 = (BLOCK_N > 64 || hoisted == nullptr) ? loc.b4 : hoisted->b4;
     const bool has_res = p.residual != nullptr && ri.valid;
@@ -553,6 +585,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  const uint32_t saff1 = stage_affine(bar_base + Cfg::BAR_BYTES, p);
+  const uint32_t saff2 = nprob == 2 ? stage_affine(bar_base + Cfg::BAR_BYTES + kAffBytes, p2) : 0u;
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -631,20 +665,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int as = 0;
     uint32_t aph = 0;
     bool alive = true;
-    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x)
-    for (int pr = 0; pr < nprob; ++pr) {
-      const ConvParams& q = pr ? p2 : p;
+    // one problem's tile; expanded once per problem so that each copy reads ITS kernel parameters at fixed
+    // offsets (selecting p / p2 by index made every field an indexed constant load with its latency exposed)
+    auto one = [&](const ConvParams& q, uint32_t saff, int tile) -> bool {
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
       const RowInfo ri = decode_row(q, m_tile, row_in_tile);
-      if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) { alive = false; break; }
+      if (!mbar_wait(tfull_bar(as), aph, 3, tile, p.profile)) return false;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
-      epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0);
+      epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0, nullptr, saff);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
       if (++as == kAcc) { as = 0; aph ^= 1u; }
+      return true;
+    };
+    for (int tile = blockIdx.x; tile < total_tiles && alive; tile += gridDim.x) {
+      alive = one(p, saff1, tile);
+      if (alive && nprob == 2) alive = one(p2, saff2, tile);
     }
   }
 
@@ -673,7 +712,7 @@ struct TcPairCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int kStages = (220 * 1024 / STAGE_BYTES) < 8 ? (220 * 1024 / STAGE_BYTES) : 8;
   static constexpr int TMEM_COLS = 2 * BLOCK_N <= 128 ? 128 : 2 * BLOCK_N <= 256 ? 256 : 512;
-  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 256 + 1024;
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 256 + 2 * kAffBytes + 1024;
 };
 
 template <int BLOCK_N>
@@ -721,6 +760,8 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair<Cfg::TMEM_COLS>(tmem_slot);
+  const uint32_t saff1 = stage_affine(bar_base + 256u, p);
+  const uint32_t saff2 = nprob == 2 ? stage_affine(bar_base + 256u + kAffBytes, p2) : 0u;
   ptx::tc_fence_before();
   __syncthreads();
   ptx::cluster_sync();
@@ -800,18 +841,17 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int as = 0;
     uint32_t aph = 0;
     bool alive = true;
-    for (int item = pair; item < total_items && alive; item += num_pairs)
-    for (int pr = 0; pr < nprob; ++pr) {
-      const ConvParams& q = pr ? p2 : p;
+    // one problem's item; expanded once per problem so that each copy reads ITS parameters at fixed offsets
+    auto one = [&](const ConvParams& q, uint32_t saff, int item) -> bool {
       const int mn = item / S, ks = item - mn * S;
       const int m_pair = mn / p.num_n_tiles;
       const int n_tile = mn - m_pair * p.num_n_tiles;
       const RowInfo ri = decode_row(q, 2 * m_pair + (int)rank, ew * 32 + lane);
-      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) { alive = false; break; }
+      if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) return false;
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
       if (S == 1) {
-        epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0);
+        epilogue_tile<BLOCK_N>(q, ri, taddr, n_tile * BLOCK_N, chunk0, nullptr, saff);
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
@@ -855,7 +895,7 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           ptx::sts32(split_flag, ok ? 1u : 0u);
         }
         epi_bar_sync();
-        if (ptx::lds32(split_flag) == 0u) { alive = false; break; }
+        if (ptx::lds32(split_flag) == 0u) return false;
         // every split reduces its own 128 / S rows of the tile half: partials added in split order
         {
           constexpr int kF4PerRow = BLOCK_N / 4;
@@ -905,6 +945,11 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
       if (++as == 2) { as = 0; aph ^= 1u; }
+      return true;
+    };
+    for (int item = pair; item < total_items && alive; item += num_pairs) {
+      alive = one(p, saff1, item);
+      if (alive && nprob == 2) alive = one(p2, saff2, item);
     }
   }
 

@@ -169,6 +169,8 @@ struct ConvParams {
   int pool_img_rows, pool_wp, pool_oh, pool_ow;
   // conv_tc_pair_kernel, FC layers: split-K.  A function of the LAYER's shape only, never of the batch, so
   // that an image's result does not depend on the engine's capacity or on the tensor batch it falls in.
+  int k_steps;                // conv_halo_kernel, resident weights: MMA steps (16 channels) issued per channel block;
+                              // the steps left out have all-zero weights (0 is read as 4)
   int split_k;                // 0 / 1: off
   float* splitk_ws;           // fp32 partial tiles [tile half][split][128][N tile]
   unsigned int* splitk_cnt;   // per tile half: {arrivals, slices reduced}; zero between launches

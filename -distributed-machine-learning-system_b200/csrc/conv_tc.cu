@@ -1108,6 +1108,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           // the channel block in a single straight-line burst (TAPS > 0: fully unrolled, descriptor
           // arithmetic hoisted ahead of the back-pressured MMA issue)
           if (ptx::elect_one()) {
+            const int ksteps = (p.k_steps > 0 && p.k_steps < 4) ? p.k_steps : 4;   // trailing all-zero channels skipped
             const long long t_burst0 = p.profile ? clock64() : 0ll;
 #pragma unroll
             for (int tap = 0; tap < (TAPS > 0 ? TAPS : p.num_taps); ++tap) {
@@ -1118,8 +1119,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
                 const uint64_t da = make_sw128_desc(a_tap + (uint32_t)(sub * kBlockM) * 128u);
 #pragma unroll
                 for (int k = 0; k < kBlockK / 16; ++k)
-                  ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
-                                 db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
+                  if (k < ksteps)
+                    ptx::umma_bf16(d_tmem + (uint32_t)(sub * BLOCK_N), da + (uint64_t)(2 * k),
+                                   db + (uint64_t)(2 * k), idesc, (cb | tap | k) != 0 ? 1u : 0u);
               }
             }
             if (p.profile) atomicAdd(&g_tc_wait_cycles[7], (unsigned long long)(clock64() - t_burst0));   // burst issue

@@ -41,6 +41,7 @@ struct ConvWeights {     // device, kernel layout
   float* scale = nullptr;
   float* shift = nullptr;
   int n_total = 0, ktot = 0, taps = 0, c_blocks = 0;
+  int k_steps = 4;       // 16-channel MMA steps of a channel block that carry non-zero weights (single-block layers)
   bf16* stem_flat = nullptr;   // ResNet stem only: weights in stem_toeplitz_kernel's smem order
 };
 
@@ -177,6 +178,13 @@ static int upload_conv_weights(idn_engine* e, ConvWeights* cw, const float* w, i
         for (int s = 0; s < S; ++s)
           h[(size_t)n * cw->ktot + (size_t)(r * S + s) * cpad + c] =
               f32_to_bf16_bits(w[(((size_t)n * cin + c) * R + r) * S + s]);
+  if (cw->c_blocks == 1) {
+    // trailing all-zero channels (AlexNet's space-to-depth stem fills 48 of its 64): their MMA steps add nothing
+    int top = 0;
+    for (size_t i = 0; i < h.size(); ++i)
+      if ((h[i] & 0x7fffu) != 0) top = std::max(top, (int)(i % 64));
+    cw->k_steps = top / 16 + 1;
+  }
   IDN_TRY(dev_alloc(e, &cw->wt, h.size(), false));
   IDN_CUDA_TRY(cudaMemcpy(cw->wt, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
   std::vector<float> sc(cw->n_total, 0.0f), sh(cw->n_total, 0.0f);
@@ -292,6 +300,7 @@ static int add_conv(idn_engine* e, const std::string& name, const Act& src, cons
   }
   fill_dest(&st, dst, spec.out_f32, dst.C);
   if (dst.C != cw.n_total) { set_error(name + ": dst channels != padded Cout"); return IDN_EINVAL; }
+  cp.k_steps = cw.k_steps;
   cp.a_ptr = src.ptr; cp.b_ptr = cw.wt;
   cp.a_rows = src.rows(); cp.a_ld = src.C; cp.ktot = cw.ktot;
   if (src.C != cw.c_blocks * 64) { set_error(name + ": src channels != weight channels"); return IDN_EINVAL; }

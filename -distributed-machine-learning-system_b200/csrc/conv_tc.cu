@@ -261,6 +261,14 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ void sts128_(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128_(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 }  // namespace ptx
 
 // Diagnostics of a pipeline stall: [0] = 1 when a wait timed out, [1] = role (0 producer, 1 MMA
@@ -404,6 +412,12 @@ __device__ __forceinline__ RowInfo decode_row(const ConvParams& p, int m_tile, i
 __device__ __forceinline__ uint32_t relu_bf16x2(uint32_t v) {
   __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&v);
   x = __hmax2(x, __float2bfloat162_rn(0.0f));
+  return *reinterpret_cast<uint32_t*>(&x);
+}
+
+__device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
+  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a), y = *reinterpret_cast<__nv_bfloat162*>(&b);
+  x = __hmax2(x, y);
   return *reinterpret_cast<uint32_t*>(&x);
 }
 
@@ -981,7 +995,16 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 constexpr int kMaxAStages = 4;
 constexpr int kMaxBStages = 16;
 
-template <int BLOCK_N, int MSUB, bool BRES, int TAPS>
+// POOL (AlexNet features.0 -> features.2; <64, 2, true, 9> only): the 3x3 / stride-2 max-pool that follows the
+// convolution is done here and the convolution's own output is never stored.  A CTA owns a contiguous run of
+// "units" (image, pooled row) and walks the flat rows under it in 256-row items, so the three conv rows of every
+// pooling window it meets come from items it has just finished: the epilogue writes the biased, ReLU'd bf16 rows
+// into a 448-row ring in shared memory (16-byte chunks XOR-swizzled by row), and after each item all 16 warps
+// reduce the pooled rows that have become complete (a thread takes 8 channels of one pooled pixel: nine 16-byte
+// loads, packed bf16 max, one 16-byte store; eight threads write a pixel's 128 bytes).  The one conv row a run
+// shares with its predecessor is recomputed (57 of ~4200 rows).  Bit-identical to conv + maxpool3x3s2_kernel.
+constexpr int kPoolRing = 448;                 // rows of 128 bytes: a 256-row item + the two conv rows (and a bit) carried over
+template <int BLOCK_N, int MSUB, bool BRES, int TAPS, bool POOL = false>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
@@ -1015,7 +1038,16 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_items = p.num_m_tiles * p.num_n_tiles;     // num_m_tiles counts 128*MSUB-row items
+  // POOL: this CTA's units [u0, u1), the flat rows [row_lo, row_hi) under them, items of 128*MSUB rows from row_lo
+  const int units = POOL ? p.nimg * p.pool_oh : 0;
+  const int u0 = POOL ? (int)(((long long)blockIdx.x * units) / gridDim.x) : 0;
+  const int u1 = POOL ? (int)(((long long)(blockIdx.x + 1) * units) / gridDim.x) : 0;
+  const int row_lo = POOL ? (u0 / p.pool_oh) * p.img_rows + 2 * (u0 % p.pool_oh) * p.wp : 0;
+  const int row_hi = POOL && u1 > u0 ? ((u1 - 1) / p.pool_oh) * p.img_rows + (2 * ((u1 - 1) % p.pool_oh) + 2) * p.wp + p.W : 0;
+  const int item_first = POOL ? 0 : (int)blockIdx.x;
+  const int item_step = POOL ? 1 : (int)gridDim.x;
+  const int total_items = POOL ? (row_hi - row_lo + kBlockM * MSUB - 1) / (kBlockM * MSUB)
+                               : p.num_m_tiles * p.num_n_tiles;     // num_m_tiles counts 128*MSUB-row items
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA1);
@@ -1044,9 +1076,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       uint32_t pha = 0;
       bool alive = true;
       const uint32_t a_bytes = (uint32_t)(p.halo_r1 + p.halo_r2) * 128u;
-      for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
+      for (int item = item_first; item < total_items && alive; item += item_step) {
         const int m_item = item / p.num_n_tiles;
-        const int row0 = m_item * (kBlockM * MSUB) + p.halo_lo;
+        const int row0 = (POOL ? row_lo : 0) + m_item * (kBlockM * MSUB) + p.halo_lo;
         for (int cb = 0; cb < p.c_blocks; ++cb) {
           if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb, p.profile)) { alive = false; break; }
           const uint32_t dst = a_base + (uint32_t)(sa * p.a_stage_bytes);
@@ -1071,7 +1103,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         int sb = 0;
         uint32_t phb = 0;
         bool alive = true;
-        for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
+        for (int item = item_first; item < total_items && alive; item += item_step) {
           const int n_tile = item % p.num_n_tiles;
           for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
             for (int tap = 0; tap < p.num_taps; tap += G) {
@@ -1095,7 +1127,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     uint32_t pha = 0, phb = 0, aph = 0;
     bool alive = true;
     if (BRES) alive = mbar_wait(bres_bar, 0u, 5, 0, p.profile);
-    for (int item = blockIdx.x; item < total_items && alive; item += gridDim.x) {
+    for (int item = item_first; item < total_items && alive; item += item_step) {
       if (!mbar_wait(tempty_bar(as), aph ^ 1u, 1, item, p.profile)) break;
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * ACC_COLS);
@@ -1174,9 +1206,75 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     if (BLOCK_N == 64) aff.load(p, chunk0 * 16);       // n_total == 64: the same 16 channels every tile
     int as = 0;
     uint32_t aph = 0;
-    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+    int next_unit = u0;                                  // POOL: first unit not yet written out
+    for (int item = item_first; item < total_items; item += item_step) {
       const int m_item = item / p.num_n_tiles;
       const int n_tile = item - m_item * p.num_n_tiles;
+      if constexpr (POOL) {
+        const uint32_t ring = bar_base + 1024u;
+        if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+        ptx::tc_fence_after();
+        // ---- a: accumulator -> bias / ReLU -> bf16 -> ring row (rows are relative to row_lo)
+#pragma unroll
+        for (int sub = 0; sub < MSUB; ++sub) {
+          const int rel = item * (kBlockM * MSUB) + sub * kBlockM + ew * 32 + lane;
+          const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * ACC_COLS + sub * BLOCK_N);
+          uint32_t v[16];
+          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(chunk0 * 16), v);
+          ptx::tmem_ld_wait();
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float y0 = fmaf(__uint_as_float(v[4 * j + 0]), aff.s4[j].x, aff.b4[j].x);
+            const float y1 = fmaf(__uint_as_float(v[4 * j + 1]), aff.s4[j].y, aff.b4[j].y);
+            const float y2 = fmaf(__uint_as_float(v[4 * j + 2]), aff.s4[j].z, aff.b4[j].z);
+            const float y3 = fmaf(__uint_as_float(v[4 * j + 3]), aff.s4[j].w, aff.b4[j].w);
+            w[2 * j] = pack_bf16x2(y0, y1);
+            w[2 * j + 1] = pack_bf16x2(y2, y3);
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) w[e] = relu_bf16x2(w[e]);
+          }
+          const uint32_t slot = (uint32_t)rel % (uint32_t)kPoolRing;
+          const uint32_t rowaddr = ring + slot * 128u;
+          ptx::sts128_(rowaddr + ((((uint32_t)(2 * chunk0)) ^ (slot & 7u)) << 4), w[0], w[1], w[2], w[3]);
+          ptx::sts128_(rowaddr + ((((uint32_t)(2 * chunk0 + 1)) ^ (slot & 7u)) << 4), w[4], w[5], w[6], w[7]);
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(tempty_bar(as));
+        if (++as == ACC_STAGES) { as = 0; aph ^= 1u; }
+        epi_bar_sync();                                   // the item's rows are in the ring
+        // ---- b: the pooled rows this item completed, two per round (threads 0..255 / 256..511)
+        const int written = (item + 1) * (kBlockM * MSUB);
+        const int et = (int)threadIdx.x - 128, half = et >> 8, t = et & 255;
+        auto last_rel = [&](int u) { return (u / p.pool_oh) * p.img_rows + (2 * (u % p.pool_oh) + 2) * p.wp + (p.W - 1) - row_lo; };
+        for (;;) {
+          const bool ca = next_unit < u1 && last_rel(next_unit) < written;
+          if (!ca) break;
+          const bool cb = next_unit + 1 < u1 && last_rel(next_unit + 1) < written;
+          if ((half == 0 || cb) && t < p.pool_ow * 8) {
+            const int u = next_unit + half, img = u / p.pool_oh, P = u - img * p.pool_oh, Q = t >> 3, c16 = t & 7;
+            const int rel0 = img * p.img_rows + 2 * P * p.wp + 2 * Q - row_lo;
+            uint4 m = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int aa = 0; aa < 3; ++aa)
+#pragma unroll
+              for (int bb = 0; bb < 3; ++bb) {
+                const uint32_t slot = (uint32_t)(rel0 + aa * p.wp + bb) % (uint32_t)kPoolRing;
+                const uint4 x = ptx::lds128_(ring + slot * 128u + ((((uint32_t)c16) ^ (slot & 7u)) << 4));
+                if (aa == 0 && bb == 0) m = x;
+                else { m.x = max_bf16x2(m.x, x.x); m.y = max_bf16x2(m.y, x.y); m.z = max_bf16x2(m.z, x.z); m.w = max_bf16x2(m.w, x.w); }
+              }
+            bf16* dst = p.pool_out + ((long long)img * p.pool_img_rows + (long long)P * p.pool_wp + Q) * 64 + c16 * 8;
+            *reinterpret_cast<uint4*>(dst) = m;
+          }
+          next_unit += cb ? 2 : 1;
+        }
+        epi_bar_sync();                                   // the next item may overwrite ring rows read above
+        continue;
+      }
       if (p.residual == nullptr) {
         if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
         ptx::tc_fence_after();
@@ -1604,11 +1702,6 @@ __device__ __forceinline__ uint64_t make_nosw_desc(uint32_t smem_addr, uint32_t 
   d |= (uint64_t)(sbo_bytes >> 4) << 32;
   d |= (uint64_t)1 << 46;
   return d;                                                     // layout type 0 = no swizzle
-}
-
-__device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
-  __nv_bfloat162 x = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
-  return *reinterpret_cast<uint32_t*>(&x);
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -2428,6 +2521,32 @@ bool plan_conv_halo(ConvParams* p, int n_total, long long m_rows_cap, int num_sm
   return true;
 }
 
+// AlexNet features.0 with features.2's max-pool in its epilogue (conv_halo_kernel<64, 2, true, 9, true>)
+static int launch_halo_pool(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                            const ConvParams& p, int num_sms, cudaStream_t st) {
+  const int units = p.nimg * p.pool_oh;
+  if (units <= 0) return IDN_OK;
+  if (p.a_stages < 2 || p.c_blocks != 1 || p.num_n_tiles != 1 || p.halo_lo != 0 || p.residual != nullptr || p.out_f32 ||
+      2 * (p.pool_oh - 1) + 2 > p.H - 1 || 2 * (p.pool_ow - 1) + 2 > p.W - 1 || 2 * p.wp + p.W + kBlockM * 2 > kPoolRing) {
+    set_error("launch_conv_halo: layer does not fit the pooled epilogue");
+    return IDN_EINVAL;
+  }
+  const int k_total = p.num_taps * p.c_blocks;
+  const int smem = 2 * p.a_stage_bytes + k_total * 64 * 128 + 1024 + 1024 + kPoolRing * 128;
+  static int configured_smem[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_smem[dev & 63] < smem) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(conv_halo_kernel<64, 2, true, 9, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured_smem[dev & 63] = smem;
+  }
+  ConvParams q = p;
+  q.a_stages = 2;                                       // the ring takes the third stage's room
+  const int grid = units < num_sms ? units : num_sms;
+  IDN_CUDA_TRY(launch_pdl(conv_halo_kernel<64, 2, true, 9, true>, dim3(grid), dim3(kThreads), (size_t)smem, st, tmA1, tmA2, tmB, q));
+  return IDN_OK;
+}
+
 template <int BLOCK_N, int MSUB, bool BRES, int TAPS>
 static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                            const ConvParams& p, int num_sms, cudaStream_t st) {
@@ -2495,6 +2614,7 @@ int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUt
     return launch_pair_res_one<2, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   }
   if (block_n == 64 && b_resident && p.msub == 2) {
+    if (p.num_taps == 9 && p.pool_out != nullptr) return launch_halo_pool(tmA1, tmA2, tmB, p, num_sms, st);
     if (p.num_taps == 9) return launch_halo_one<64, 2, true, 9>(tmA1, tmA2, tmB, p, num_sms, st);
     return launch_halo_one<64, 2, true, 0>(tmA1, tmA2, tmB, p, num_sms, st);
   }

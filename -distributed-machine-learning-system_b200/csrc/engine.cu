@@ -126,7 +126,7 @@ struct idn_engine {
   // pooling windows are resolved in shared memory, pooled pixels leave with plain stores).
   int fuse_stem_step = -1, fuse_pool_step = -1, pool_last_reader = -1;
   bf16* pool_buf = nullptr; size_t pool_img_bytes = 0;
-  int pool_img_rows = 0, pool_wp = 0;
+  int pool_img_rows = 0, pool_wp = 0, pool_oh = 0, pool_ow = 0;
   bool no_pool_fusion = false;
   int last_n = 0;
   // split-K scratch of the FC layers, shared by all of them (they run one after the other)
@@ -562,6 +562,11 @@ static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
     IDN_TRY(add_conv(e, "features.0+relu", xs, w0, s0, c1, nullptr, cap)); }
   Act p1; IDN_TRY(alloc_act(e, &p1, make_geom(27, 27, 2), 64, cap));
   add_pool(e, "features.2 maxpool", c1, p1, 0);
+  // features.2 runs in features.0's epilogue (conv_halo_kernel<64, 2, true, 9, true>); the stand-alone pool is the
+  // cross-check (IDN_NO_POOL_FUSION=1) and serves activation taps of features.0
+  e->fuse_stem_step = (int)e->steps.size() - 2; e->fuse_pool_step = (int)e->steps.size() - 1;
+  e->pool_buf = p1.ptr; e->pool_img_rows = p1.g.img_rows(); e->pool_wp = p1.g.Wp;
+  e->pool_oh = 27; e->pool_ow = 27;
   // features.3: 5x5 p2, 64 -> 192
   ConvWeights w3;
   IDN_TRY(take2((size_t)192 * 64 * 25, 192, &w, &b));
@@ -755,7 +760,8 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
   cudaStream_t st = e->stream;
   e->last_n = n;
   const bool fuse = e->fuse_stem_step >= 0 && e->impl == IDN_IMPL_TC && !e->stem_simt && !e->no_pool_fusion &&
-                    e->stop_after != e->fuse_stem_step;      // a tap of conv1 itself needs the plain stem
+                    e->stop_after != e->fuse_stem_step &&    // a tap of the convolution itself needs its own output
+                    (e->steps[e->fuse_stem_step].cp.mode == MODE_STEM || e->steps[e->fuse_stem_step].use_halo);
   int step_no = 0;
   for (Step& s : e->steps) {
     if (e->stop_after >= 0 && step_no > e->stop_after) break;
@@ -774,6 +780,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
         if (step_idx == e->fuse_stem_step) {
           s.cp.pool_out = fuse ? e->pool_buf : nullptr;
           s.cp.pool_img_rows = e->pool_img_rows; s.cp.pool_wp = e->pool_wp;
+          if (e->pool_oh > 0) { s.cp.pool_oh = e->pool_oh; s.cp.pool_ow = e->pool_ow; }
         }
         if (s.merged_into >= 0 && ds_fusion_active(e, e->impl)) { e->launches -= 1; break; }   // rode in that step's launch
         IDN_TRY(launch_conv_step(e, s, n, e->impl, st));
@@ -1194,7 +1201,7 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
   const bool fuse = h->fuse_stem_step == step && !h->no_pool_fusion && !h->stem_simt;
   switch (s.kind) {
     case STEP_PRE: k = "preprocess_kernel<" + N(h->pre_mode) + ">"; break;
-    case STEP_POOL: k = (h->fuse_pool_step == step && !h->no_pool_fusion && !h->stem_simt) ? "(folded into stem_pool_kernel)" : "maxpool3x3s2_kernel"; break;
+    case STEP_POOL: k = (h->fuse_pool_step == step && !h->no_pool_fusion && !h->stem_simt) ? (h->steps[h->fuse_stem_step].cp.mode == MODE_STEM ? "(folded into stem_pool_kernel)" : "(folded into the convolution before it)") : "maxpool3x3s2_kernel"; break;
     case STEP_RHEAD: k = h->no_head_fusion ? "avgpool_kernel + fc_fp32_kernel + softmax_top1_kernel" : "resnet_head_kernel"; break;
     case STEP_SOFTMAX: k = "softmax_top1_kernel"; break;
     case STEP_CONV:
@@ -1204,7 +1211,7 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
       else if (s.use_halo && cp.pair && s.b_resident) k = "conv_pair_res_kernel<" + N(cp.msub) + ", " + N(cp.num_taps == 9 ? 9 : 0) + ">";
       else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + ">";
       else if (s.use_halo) k = "conv_halo_kernel<" + N(s.block_n) + ", " + N(cp.msub) + ", " + N(s.b_resident ? 1 : 0) + ", " +
-                               N(s.b_resident ? (cp.num_taps == 9 ? 9 : 0) : (cp.b_group == 3 ? 3 : 0)) + ">";
+                               N(s.b_resident ? (cp.num_taps == 9 ? 9 : 0) : (cp.b_group == 3 ? 3 : 0)) + (fuse ? ", 1>" : ">");
       else if (cp.tc_pair) k = "conv_tc_pair_kernel<" + N(s.block_n) + ">";
       else k = "conv_tc_kernel<" + N(s.block_n) + ">";
       break;

@@ -287,6 +287,45 @@ def test_resnet_stem_pool_fusion_is_bit_identical(built_library, monkeypatch):
     assert np.array_equal(l3, l1) and np.array_equal(l2, l1[:7])
 
 
+def test_alexnet_first_pool_in_the_conv_epilogue_is_bit_identical(built_library, monkeypatch):
+    """AlexNet's features.2 max-pool runs in the epilogue of features.0 (conv rows kept in a shared-memory ring by
+    the CTA that owns a contiguous run of pooled rows); IDN_NO_POOL_FUSION=1 keeps conv + maxpool3x3s2_kernel.
+    max over the same nine bf16 values is exact, so the pooled activation and everything after it must be
+    identical bit for bit: 16 images (432 pooled rows over 148 CTAs: runs start and end inside images), a ragged
+    second batch, a single image, and repeated passes; one launch fewer per pass."""
+    sd = make_state_dict("alexnet", 0, "stress")
+    imgs = [synth_image(i, mixed=True) for i in range(21)]
+    with Engine("alexnet", sd, max_batch=16) as eng:
+        names = [n for n, _ in eng.steps()]
+        pool_step = names.index("features.2 maxpool")
+        assert dict(eng.step_kernels())["features.2 maxpool"].startswith("(folded")
+        i1, p1, l1 = eng.infer(imgs, want_logits=True)          # two tensor batches: 16 + 5
+        i2, p2, l2 = eng.infer(imgs[:1], want_logits=True)
+        i3, p3, l3 = eng.infer(imgs, want_logits=True)
+        eng.infer(imgs[:16])
+        k0 = eng.kernel_launches
+        eng.infer(imgs[:16])
+        fused_launches = eng.kernel_launches - k0
+        eng.stop_after(pool_step)
+        eng.infer(imgs[:16])
+        a1 = eng.read_activation(pool_step, 16)
+    monkeypatch.setenv("IDN_NO_POOL_FUSION", "1")
+    with Engine("alexnet", sd, max_batch=16) as eng:
+        assert dict(eng.step_kernels())["features.2 maxpool"] == "maxpool3x3s2_kernel"
+        j1, q1, m1 = eng.infer(imgs, want_logits=True)
+        eng.infer(imgs[:16])
+        k0 = eng.kernel_launches
+        eng.infer(imgs[:16])
+        plain_launches = eng.kernel_launches - k0
+        eng.stop_after(pool_step)
+        eng.infer(imgs[:16])
+        b1 = eng.read_activation(pool_step, 16)
+    assert np.array_equal(a1, b1), f"pooled activation differs in {int((a1 != b1).sum())} of {a1.size} values"
+    assert np.array_equal(l1, m1) and np.array_equal(i1, j1) and np.array_equal(p1, q1)
+    assert np.array_equal(l3, l1) and np.array_equal(l2, l1[:1])
+    assert fused_launches == plain_launches - 1, (fused_launches, plain_launches)
+
+
 def test_resnet_head_fusion_is_bit_identical(built_library, monkeypatch):
     """avgpool + fp32 FC + softmax/top-1 as ONE kernel (clusters of 4 CTAs, 11 images each) against the three
     separate kernels (IDN_NO_HEAD_FUSION=1): the fused kernel keeps their arithmetic and its order (pixels h, w

@@ -84,6 +84,17 @@ void build_axis_table(int in_size, int out_size, int crop_off, std::string* out)
       xcnt[i] = n;
     }
   }
+  // Pillow sizes its coefficient rows for the filter's support (3 for any upscale) but a row only uses xcnt of them
+  // (2 when upscaling): keep the widest row actually used, so that the kernel's register window is no wider.
+  int kuse = 1;
+  for (int i = 0; i < IDN_CROP; ++i) kuse = std::max(kuse, xcnt[i]);
+  if (kuse < ksize) {
+    std::vector<int> k2((size_t)IDN_CROP * kuse, 0);
+    for (int i = 0; i < IDN_CROP; ++i)
+      for (int x = 0; x < xcnt[i]; ++x) k2[(size_t)i * kuse + x] = kk[(size_t)i * ksize + x];
+    kk.swap(k2);
+    ksize = kuse;
+  }
   std::vector<int> flat;
   flat.push_back(ksize);
   flat.insert(flat.end(), xmin.begin(), xmin.end());
@@ -199,7 +210,7 @@ __device__ __forceinline__ void pre_fast_band(const uint8_t* __restrict__ src, c
   }
   const long long rowstep = (long long)m.W * 3;
   const uint8_t* colp = src + (long long)x0 * 3;
-  constexpr int NW = NT == 3 ? 3 : 4;                     // aligned words under 3 NT bytes at any alignment
+  constexpr int NW = NT <= 3 ? 3 : 4;                     // aligned words under 3 NT bytes at any alignment
   uint32_t pw[NW];
   int psh;
   auto fetch = [&](int r) {                               // words of source row r (clamped: the last rows are
@@ -220,13 +231,13 @@ __device__ __forceinline__ void pre_fast_band(const uint8_t* __restrict__ src, c
     for (int f = 0; f < v.nnew; ++f) {
       // ---- horizontal pass of source row nr -> packed uint8 RGB, into the youngest window slot
       const uint32_t p0 = __funnelshift_r(pw[0], pw[1], psh), p1 = __funnelshift_r(pw[1], pw[2], psh);
-      const uint32_t p2 = __funnelshift_r(pw[2], NT == 4 ? pw[3] : 0u, psh);
+      const uint32_t p2 = NT >= 3 ? __funnelshift_r(pw[2], NT == 4 ? pw[3] : 0u, psh) : 0u;
       ++nr;
       fetch(nr);
       int h0 = 1 << 21, h1 = 1 << 21, h2 = 1 << 21;
       h0 += bsel(p0, 0) * kk[0]; h1 += bsel(p0, 1) * kk[0]; h2 += bsel(p0, 2) * kk[0];
       h0 += bsel(p0, 3) * kk[1]; h1 += bsel(p1, 0) * kk[1]; h2 += bsel(p1, 1) * kk[1];
-      h0 += bsel(p1, 2) * kk[2]; h1 += bsel(p1, 3) * kk[2]; h2 += bsel(p2, 0) * kk[2];
+      if (NT >= 3) { h0 += bsel(p1, 2) * kk[NT >= 3 ? 2 : 0]; h1 += bsel(p1, 3) * kk[NT >= 3 ? 2 : 0]; h2 += bsel(p2, 0) * kk[NT >= 3 ? 2 : 0]; }
       if (NT == 4) { h0 += bsel(p2, 1) * kk[3]; h1 += bsel(p2, 2) * kk[3]; h2 += bsel(p2, 3) * kk[3]; }
       // coefficients are >= 0 and sum to 2^22 (+- rounding), so the result is already in [0, 255]
 #pragma unroll
@@ -287,7 +298,7 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
   const int ylo = kPreBand * (int)blockIdx.x;
   const int yhi = min(ylo + kPreBand, IDN_CROP);
   const int hks = ht[0], vks = vt[0];
-  const int nt = (hks <= 3 && vks <= 3) ? 3 : (hks <= 4 && vks <= 4) ? 4 : 0;
+  const int nt = (hks <= 2 && vks <= 2) ? 2 : (hks <= 3 && vks <= 3) ? 3 : (hks <= 4 && vks <= 4) ? 4 : 0;
   const bool fast = nt != 0 && m.W >= nt;
   const int first_row = vt[1 + ylo];
   if (fast && tid < yhi - ylo) {
@@ -309,7 +320,8 @@ preprocess_kernel(const uint8_t* __restrict__ imgs, const PreMeta* __restrict__ 
   }
   __syncthreads();
   if (fast) {
-    if (nt == 3) pre_fast_band<OUT_MODE, 3>(src, m, ht, s_v, s_lut, out, n, ylo, yhi, first_row, left_pad, ws);
+    if (nt == 2) pre_fast_band<OUT_MODE, 2>(src, m, ht, s_v, s_lut, out, n, ylo, yhi, first_row, left_pad, ws);
+    else if (nt == 3) pre_fast_band<OUT_MODE, 3>(src, m, ht, s_v, s_lut, out, n, ylo, yhi, first_row, left_pad, ws);
     else pre_fast_band<OUT_MODE, 4>(src, m, ht, s_v, s_lut, out, n, ylo, yhi, first_row, left_pad, ws);
   } else {                                              // huge downscales, images narrower than the window
     for (int y = ylo; y < yhi; ++y) {

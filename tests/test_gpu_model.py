@@ -167,6 +167,22 @@ def test_full_query_of_400_is_consistent_with_small_batches(built_library, model
     _compare(f"{model}/batch400-tail", i1[380:], p1[380:], l1[380:], want)
 
 
+def test_alexnet_tensor_batch_of_1200_matches_the_batch_400_engine(built_library):
+    """A tensor batch larger than one wave of work items: with max_batch = 1200 FC8's split-K has 160 items for 74
+    CTA pairs (a pair runs several rounds and waits, inside a round, for splits its neighbours are still computing)
+    and features.0's pooled runs are 219 rows long.  The partial sums are added in split order whoever arrives last,
+    so the results must equal the batch-400 engine's bit for bit -- and the call must come back at all."""
+    sd = make_state_dict("alexnet", 0, "default")
+    imgs = list(noise_images(1190, seed=23)) + [synth_image(i, mixed=True) for i in range(10)]
+    with Engine("alexnet", sd, max_batch=1200) as big:
+        i1, p1, l1 = big.infer(imgs, want_logits=True)
+        i1b, _, l1b = big.infer(imgs, want_logits=True)
+    with Engine("alexnet", sd, max_batch=400) as ref:
+        i2, p2, l2 = ref.infer(imgs, want_logits=True)           # 400 + 400 + 400
+    assert np.array_equal(l1, l1b) and np.array_equal(i1, i1b)
+    assert np.array_equal(l1, l2) and np.array_equal(i1, i2) and np.array_equal(p1, p2)
+
+
 @pytest.mark.parametrize("model", ["alexnet", "resnet18"])
 def test_baseline_query_top1_against_reference(built_library, golden_dir, model):
     """BASELINE.json configs[0] at full size: images 0-399 in ONE 400-image tensor batch against the

@@ -167,6 +167,7 @@ struct ConvParams {
   // output is not stored, stem_pool_kernel writes the pooled pixels to pool_out with plain stores.
   bf16* pool_out;             // nullptr: plain stem
   int pool_img_rows, pool_wp, pool_oh, pool_ow;
+  bf16* pool_ring;            // conv_pair_kernel<.., POOL>: [pairs][1024 rows][n_total] scratch for conv rows (L2-resident)
   // conv_tc_pair_kernel, FC layers: split-K.  A function of the LAYER's shape only, never of the batch, so
   // that an image's result does not depend on the engine's capacity or on the tensor batch it falls in.
   int k_steps;                // conv_halo_kernel, resident weights: MMA steps (16 channels) issued per channel block;

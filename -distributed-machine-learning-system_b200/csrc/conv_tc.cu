@@ -484,7 +484,7 @@ __device__ __forceinline__ uint32_t stage_affine(uint32_t saff, const ConvParams
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const RowInfo& ri, const uint32_t (&v)[16],
                                                int col, const float4* s4, const float4* b4,
-                                               const uint32_t (&rr)[8], bool has_res) {
+                                               const uint32_t (&rr)[8], bool has_res, bf16* out_override = nullptr) {
   if (ri.valid) {
     float y[16];
 #pragma unroll
@@ -522,7 +522,7 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const RowInf
 #pragma unroll
         for (int e = 0; e < 8; ++e) w[e] = relu_bf16x2(w[e]);
       }
-      ptx::st_global_256(reinterpret_cast<bf16*>(p.out) + ri.dst_row * p.ldc + col, w);
+      ptx::st_global_256((out_override ? out_override : reinterpret_cast<bf16*>(p.out)) + ri.dst_row * p.ldc + col, w);
     }
   }
 }
@@ -530,7 +530,7 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const RowInf
 template <int BLOCK_N>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo& ri, uint32_t taddr,
                                               int col0, int chunk0, const ChunkAffine* hoisted = nullptr,
-                                              uint32_t saff = 0u) {
+                                              uint32_t saff = 0u, bf16* out_override = nullptr) {
 #pragma unroll 1
   for (int c0 = chunk0 * 16; c0 < BLOCK_N; c0 += 64) {
     uint32_t v[16];
@@ -546,7 +546,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const RowInfo
     uint32_t rr[8];
     if (has_res) ptx::ld_global_256(p.residual + ri.res_row * p.ldc + col, rr);
     ptx::tmem_ld_wait();
-    epilogue_chunk<BLOCK_N>(p, ri, v, col, s4, b4, rr, has_res);
+    epilogue_chunk<BLOCK_N>(p, ri, v, col, s4, b4, rr, has_res, out_override);
   }
 }
 
@@ -1348,7 +1348,16 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 //               barriers at the same offset in both CTAs; the peer's epilogue warps arrive remotely on
 //               the leader's "accumulator drained" barrier.
 // =============================================================================================
-template <int BLOCK_N, int G>      // G = filter taps per weight stage (one barrier round-trip each)
+// POOL (AlexNet features.3 -> features.5, features.10 -> features.12): the 3x3 / stride-2 max-pool that follows runs
+// in this kernel and the convolution's own output is never written to its buffer.  A pair owns a contiguous run of
+// (image, pooled row) units and walks the flat rows under it in 256-row items; both CTAs write their biased, ReLU'd
+// bf16 rows into the pair's 1024-row ring in GLOBAL memory (a few hundred KB per pair: it lives in L2; the windows
+// of N = 192 / 256 layers do not fit in shared memory next to the operand stages), tell each other through an
+// mbarrier per item, and then pool the units that item completed -- even units on CTA 0, odd ones on CTA 1, a
+// thread taking 8 channels of one pooled pixel (nine 16-byte L2 loads, packed bf16 max, one 16-byte store).
+// The one conv row a run shares with its predecessor is recomputed.  Bit-identical to conv + maxpool3x3s2_kernel.
+constexpr int kPairRing = 1024;
+template <int BLOCK_N, int G, bool POOL = false>      // G = filter taps per weight stage (one barrier round-trip each)
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ ConvParams p) {
@@ -1376,7 +1385,16 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   const bool leader = rank == 0;
   const int pair = (int)(blockIdx.x >> 1), num_pairs = (int)(gridDim.x >> 1);
   const int m_pairs = (p.num_m_tiles + 1) >> 1;                  // num_m_tiles counts 128-row tiles
-  const int total_items = m_pairs * p.num_n_tiles;
+  // POOL: this pair's units [u0, u1), the flat rows [row_lo, row_hi) under them, 256-row items from row_lo
+  const int units = POOL ? p.nimg * p.pool_oh : 0;
+  const int u0 = POOL ? (int)(((long long)pair * units) / num_pairs) : 0;
+  const int u1 = POOL ? (int)(((long long)(pair + 1) * units) / num_pairs) : 0;
+  const int row_lo = POOL ? (u0 / p.pool_oh) * p.img_rows + 2 * (u0 % p.pool_oh) * p.wp : 0;
+  const int row_hi = POOL && u1 > u0 ? ((u1 - 1) / p.pool_oh) * p.img_rows + (2 * ((u1 - 1) % p.pool_oh) + 2) * p.wp + p.W : 0;
+  const int item_first = POOL ? 0 : pair;
+  const int item_step = POOL ? 1 : num_pairs;
+  const int total_items = POOL ? (row_hi - row_lo + 2 * kBlockM - 1) / (2 * kBlockM) : m_pairs * p.num_n_tiles;
+  const uint32_t peer_bar = bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 6);   // POOL: the partner's rows are in the ring
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA1);
@@ -1387,6 +1405,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     for (int s = 0; s < kMaxAStages; ++s) { ptx::mbar_init(a_full(s), 1); ptx::mbar_init(a_empty(s), 1); }
     for (int s = 0; s < kMaxBStages; ++s) { ptx::mbar_init(b_full(s), 1); ptx::mbar_init(b_empty(s), 1); }
     for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 2 * kEpiWarps); }
+    ptx::mbar_init(peer_bar, 1);
+    ptx::sts32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7), 0u);       // POOL: "handshake timed out" flag
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair<TMEM_COLS>(tmem_slot);
@@ -1405,9 +1425,9 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       uint32_t pha = 0;
       bool alive = true;
       const uint32_t a_bytes = (uint32_t)(p.halo_r1 + p.halo_r2) * 128u;
-      for (int item = pair; item < total_items && alive; item += num_pairs) {
+      for (int item = item_first; item < total_items && alive; item += item_step) {
         const int m_tile = 2 * (item / p.num_n_tiles) + (int)rank;
-        const int row0 = m_tile * kBlockM + p.halo_lo;
+        const int row0 = (POOL ? row_lo + (2 * item + (int)rank) * kBlockM : m_tile * kBlockM) + p.halo_lo;
         for (int cb = 0; cb < p.c_blocks; ++cb) {
           if (!mbar_wait(a_empty(sa), pha ^ 1u, 0, cb, p.profile)) { alive = false; break; }
           const uint32_t dst = a_base + (uint32_t)(sa * p.a_stage_bytes);
@@ -1427,7 +1447,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
       int sb = 0;
       uint32_t phb = 0;
       bool alive = true;
-      for (int item = pair; item < total_items && alive; item += num_pairs) {
+      for (int item = item_first; item < total_items && alive; item += item_step) {
         const int n_tile = item % p.num_n_tiles;
         for (int cb = 0; cb < p.c_blocks && alive; ++cb) {
           for (int tap = 0; tap < p.num_taps; tap += G) {
@@ -1450,7 +1470,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     int sa = 0, sb = 0, as = 0;
     uint32_t pha = 0, phb = 0, aph = 0;
     bool alive = true;
-    for (int item = pair; item < total_items && alive; item += num_pairs) {
+    for (int item = item_first; item < total_items && alive; item += item_step) {
       if (!mbar_wait_cluster(tempty_bar(as), aph ^ 1u, 1, item)) break;      // both CTAs' epilogues drained
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(as * BLOCK_N);
@@ -1492,7 +1512,60 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     const int chunk0 = (warp - 4) >> 2;
     int as = 0;
     uint32_t aph = 0;
-    for (int item = pair; item < total_items; item += num_pairs) {
+    int next_unit = u0;                                  // POOL: first unit not yet written out
+    for (int item = item_first; item < total_items; item += item_step) {
+      if constexpr (POOL) {
+        bf16* ring = p.pool_ring + (size_t)pair * kPairRing * p.n_total;
+        if (!mbar_wait(tfull_bar(as), aph, 3, item, p.profile)) break;
+        ptx::tc_fence_after();
+        // ---- a: this CTA's 128 rows of the item -> bias / ReLU -> bf16 -> ring (rows relative to row_lo)
+        RowInfo rr;
+        rr.valid = true;
+        rr.dst_row = ((2 * item + (int)rank) * kBlockM + ew * 32 + lane) % kPairRing;
+        rr.res_row = 0;
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(as * BLOCK_N);
+        epilogue_tile<BLOCK_N>(p, rr, taddr, 0, chunk0, nullptr, 0u, ring);
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+        if (++as == 2) { as = 0; aph ^= 1u; }
+        __threadfence();
+        epi_bar_sync();                                   // this CTA's rows of the item are written and fenced
+        if (threadIdx.x == 128) {
+          ptx::mbar_arrive_cluster(ptx::mapa(peer_bar, rank ^ 1u));
+          if (!mbar_wait_cluster(peer_bar, (uint32_t)(item & 1), 7, item)) ptx::sts32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7), 1u);
+        }
+        epi_bar_sync();                                   // ... and so are the partner's
+        if (ptx::lds32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7)) != 0u) break;
+        // ---- b: the units this item completed: even ones here on CTA 0, odd ones on CTA 1
+        const int written = (item + 1) * (2 * kBlockM);
+        const int et = (int)threadIdx.x - 128;
+        const int cvec = p.n_total >> 3, tasks = p.pool_ow * cvec;
+        for (;;) {
+          if (next_unit >= u1) break;
+          const int u = next_unit, img = u / p.pool_oh, P = u - img * p.pool_oh;
+          const int rel_row0 = img * p.img_rows + 2 * P * p.wp - row_lo;
+          if (rel_row0 + 2 * p.wp + p.W - 1 >= written) break;
+          if ((u & 1) == (int)rank) {
+            for (int t = et; t < tasks; t += 32 * kEpiWarps) {
+              const int Q = t / cvec, cv = t - Q * cvec;
+              uint4 m = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+              for (int aa = 0; aa < 3; ++aa)
+#pragma unroll
+                for (int bb = 0; bb < 3; ++bb) {
+                  const int slot = (rel_row0 + aa * p.wp + 2 * Q + bb) % kPairRing;
+                  const uint4 x = __ldcg(reinterpret_cast<const uint4*>(ring + (size_t)slot * p.n_total) + cv);
+                  if (aa == 0 && bb == 0) m = x;
+                  else { m.x = max_bf16x2(m.x, x.x); m.y = max_bf16x2(m.y, x.y); m.z = max_bf16x2(m.z, x.z); m.w = max_bf16x2(m.w, x.w); }
+                }
+              reinterpret_cast<uint4*>(p.pool_out + ((long long)img * p.pool_img_rows + (long long)P * p.pool_wp + Q) * p.n_total)[cv] = m;
+            }
+          }
+          ++next_unit;
+        }
+        continue;
+      }
       const int m_pair = item / p.num_n_tiles;
       const int n_tile = item - m_pair * p.num_n_tiles;
       const RowInfo ri = decode_row(p, 2 * m_pair + (int)rank, ew * 32 + lane);
@@ -2569,6 +2642,31 @@ static int launch_halo_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, con
 }
 
 template <int BLOCK_N, int G>
+static int launch_pair_pool(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
+                            const ConvParams& p, int num_sms, cudaStream_t st) {
+  const int units = p.nimg * p.pool_oh;
+  if (units <= 0) return IDN_OK;
+  if (p.num_n_tiles != 1 || p.halo_lo > 0 || p.residual != nullptr || p.out_f32 || p.pool_ring == nullptr ||
+      2 * (p.pool_oh - 1) + 2 > p.H - 1 || 2 * (p.pool_ow - 1) + 2 > p.W - 1 || 2 * p.wp + p.W + 3 * 2 * kBlockM > kPairRing ||
+      p.n_total % 8 != 0) {
+    set_error("launch_conv_halo: layer does not fit the pooled pair epilogue");
+    return IDN_EINVAL;
+  }
+  const int smem = p.a_stages * p.a_stage_bytes + p.b_stages * G * (BLOCK_N / 2) * 128 + 1024 + 1024;
+  static int configured_smem[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_smem[dev & 63] < smem) {
+    IDN_CUDA_TRY(cudaFuncSetAttribute(conv_pair_kernel<BLOCK_N, G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured_smem[dev & 63] = smem;
+  }
+  const int pairs = std::min(units, num_sms / 2);
+  IDN_CUDA_TRY(launch_pdl(conv_pair_kernel<BLOCK_N, G, true>, dim3(2 * pairs), dim3(kThreads), (size_t)smem, st,
+                          tmA1, tmA2, tmB, p));
+  return IDN_OK;
+}
+
+template <int BLOCK_N, int G>
 static int launch_pair_one(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUtensorMap& tmB,
                            const ConvParams& p, int num_sms, cudaStream_t st) {
   const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles;           // 256-row pair items
@@ -2626,6 +2724,12 @@ int launch_conv_halo(const CUtensorMap& tmA1, const CUtensorMap& tmA2, const CUt
     if (!b_resident && p.msub == 1) {
 #define IDN_PAIR_CASE(N, GG) \
       if (block_n == N && p.b_group == GG) return launch_pair_one<N, GG>(tmA1, tmA2, tmB, p, num_sms, st);
+      if (p.pool_out != nullptr) {
+        if (block_n == 192 && p.b_group == 5) return launch_pair_pool<192, 5>(tmA1, tmA2, tmB, p, num_sms, st);
+        if (block_n == 256 && p.b_group == 3) return launch_pair_pool<256, 3>(tmA1, tmA2, tmB, p, num_sms, st);
+        set_error("launch_conv_halo: no pooled pair kernel for this tile");
+        return IDN_EINVAL;
+      }
       IDN_PAIR_CASE(256, 1) IDN_PAIR_CASE(256, 3)
       IDN_PAIR_CASE(192, 1) IDN_PAIR_CASE(192, 3) IDN_PAIR_CASE(192, 5)
       IDN_PAIR_CASE(128, 1) IDN_PAIR_CASE(128, 3) IDN_PAIR_CASE(128, 9)

@@ -127,6 +127,10 @@ struct idn_engine {
   int fuse_stem_step = -1, fuse_pool_step = -1, pool_last_reader = -1;
   bf16* pool_buf = nullptr; size_t pool_img_bytes = 0;
   int pool_img_rows = 0, pool_wp = 0, pool_oh = 0, pool_ow = 0;
+  // further conv -> max-pool pairs fused on the CTA-pair kernel (AlexNet features.3/5, features.10/12)
+  struct FusePair { int conv_step, pool_step; bf16* buf; int img_rows, wp, oh, ow; };
+  std::vector<FusePair> fuse_pairs;
+  bf16* pool_ring = nullptr;           // [num_sms / 2][1024 rows][256] bf16: the pairs' conv-row rings
   bool no_pool_fusion = false;
   int last_n = 0;
   // split-K scratch of the FC layers, shared by all of them (they run one after the other)
@@ -576,6 +580,11 @@ static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
   IDN_TRY(add_conv(e, "features.3+relu", p1, w3, s5, c2, nullptr, cap));
   Act p2; IDN_TRY(alloc_act(e, &p2, make_geom(13, 13, 1), 192, cap));
   add_pool(e, "features.5 maxpool", c2, p2, 0);
+  // (features.5 inside features.3 is correct but does not pay: the 192-wide layer's epilogue has no slack for the
+  //  hand-over and the pooling, 0.1538 ms fused against 0.1235 + 0.0313 -- it stays behind IDN_FUSE_FEATURES5=1)
+  { const char* v = std::getenv("IDN_FUSE_FEATURES5");
+    if (v && v[0] == '1')
+      e->fuse_pairs.push_back({(int)e->steps.size() - 2, (int)e->steps.size() - 1, p2.ptr, p2.g.img_rows(), p2.g.Wp, p2.g.H, p2.g.W}); }
   ConvSpec s3; s3.R = 3; s3.S = 3; s3.pad = 1; s3.relu = true;
   ConvWeights w6, w8, w10;
   IDN_TRY(take2((size_t)384 * 192 * 9, 384, &w, &b));
@@ -592,6 +601,8 @@ static int build_alexnet(idn_engine* e, const float* blob, size_t count) {
   IDN_TRY(add_conv(e, "features.10+relu", c4, w10, s3, c5, nullptr, cap));
   Act p3; IDN_TRY(alloc_act(e, &p3, make_geom(6, 6, 0), 256, cap));
   add_pool(e, "features.12 maxpool", c5, p3, 0);
+  e->fuse_pairs.push_back({(int)e->steps.size() - 2, (int)e->steps.size() - 1, p3.ptr, p3.g.img_rows(), p3.g.Wp, p3.g.H, p3.g.W});
+  IDN_TRY(dev_alloc(e, &e->pool_ring, (size_t)(e->num_sms / 2 + 1) * 1024 * 256, false));
   // classifier: the flatten order of torch.flatten(x, 1) on [B,256,6,6] is (c, h, w)
   // (tv:models/alexnet.py:50); activations here are (h, w, c), so FC6's columns are permuted once.
   IDN_TRY(take2((size_t)4096 * 9216, 4096, &w, &b));
@@ -762,6 +773,12 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
   const bool fuse = e->fuse_stem_step >= 0 && e->impl == IDN_IMPL_TC && !e->stem_simt && !e->no_pool_fusion &&
                     e->stop_after != e->fuse_stem_step &&    // a tap of the convolution itself needs its own output
                     (e->steps[e->fuse_stem_step].cp.mode == MODE_STEM || e->steps[e->fuse_stem_step].use_halo);
+  // the conv -> pool pairs of the CTA-pair kernel that run fused in this pass
+  auto pair_fused = [&](const idn_engine::FusePair& fp) {
+    const Step& c = e->steps[fp.conv_step];
+    return e->impl == IDN_IMPL_TC && !e->no_pool_fusion && e->stop_after != fp.conv_step && c.use_halo && c.cp.pair &&
+           !c.b_resident && c.cp.num_n_tiles == 1 && ((c.block_n == 192 && c.cp.b_group == 5) || (c.block_n == 256 && c.cp.b_group == 3));
+  };
   int step_no = 0;
   for (Step& s : e->steps) {
     if (e->stop_after >= 0 && step_no > e->stop_after) break;
@@ -782,11 +799,23 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
           s.cp.pool_img_rows = e->pool_img_rows; s.cp.pool_wp = e->pool_wp;
           if (e->pool_oh > 0) { s.cp.pool_oh = e->pool_oh; s.cp.pool_ow = e->pool_ow; }
         }
+        for (const auto& fp : e->fuse_pairs)
+          if (fp.conv_step == step_idx) {
+            const bool on = pair_fused(fp);
+            s.cp.pool_out = on ? fp.buf : nullptr;
+            s.cp.pool_img_rows = fp.img_rows; s.cp.pool_wp = fp.wp; s.cp.pool_oh = fp.oh; s.cp.pool_ow = fp.ow;
+            s.cp.pool_ring = e->pool_ring;
+          }
         if (s.merged_into >= 0 && ds_fusion_active(e, e->impl)) { e->launches -= 1; break; }   // rode in that step's launch
         IDN_TRY(launch_conv_step(e, s, n, e->impl, st));
         break;
       case STEP_POOL:
         if (fuse && step_idx == e->fuse_pool_step) { e->launches -= 1; break; }   // done by the stem's epilogue
+        {
+          bool done = false;
+          for (const auto& fp : e->fuse_pairs) done = done || (fp.pool_step == step_idx && pair_fused(fp));
+          if (done) { e->launches -= 1; break; }                                  // done by the convolution before it
+        }
         s.pp.nimg = n;
         IDN_TRY(launch_maxpool(s.pp, st));
         break;
@@ -1199,9 +1228,19 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
   std::string k;
   auto N = [](int v) { return std::to_string(v); };
   const bool fuse = h->fuse_stem_step == step && !h->no_pool_fusion && !h->stem_simt;
+  auto pair_fused = [&](const idn_engine::FusePair& fp) {
+    const Step& c = h->steps[fp.conv_step];
+    return h->impl == IDN_IMPL_TC && !h->no_pool_fusion && c.use_halo && c.cp.pair && !c.b_resident && c.cp.num_n_tiles == 1 &&
+           ((c.block_n == 192 && c.cp.b_group == 5) || (c.block_n == 256 && c.cp.b_group == 3));
+  };
+  bool pair_conv = false, pair_pool = false;
+  for (const auto& fp : h->fuse_pairs) {
+    pair_conv = pair_conv || (fp.conv_step == step && pair_fused(fp));
+    pair_pool = pair_pool || (fp.pool_step == step && pair_fused(fp));
+  }
   switch (s.kind) {
     case STEP_PRE: k = "preprocess_kernel<" + N(h->pre_mode) + ">"; break;
-    case STEP_POOL: k = (h->fuse_pool_step == step && !h->no_pool_fusion && !h->stem_simt) ? (h->steps[h->fuse_stem_step].cp.mode == MODE_STEM ? "(folded into stem_pool_kernel)" : "(folded into the convolution before it)") : "maxpool3x3s2_kernel"; break;
+    case STEP_POOL: k = pair_pool ? "(folded into the convolution before it)" : (h->fuse_pool_step == step && !h->no_pool_fusion && !h->stem_simt) ? (h->steps[h->fuse_stem_step].cp.mode == MODE_STEM ? "(folded into stem_pool_kernel)" : "(folded into the convolution before it)") : "maxpool3x3s2_kernel"; break;
     case STEP_RHEAD: k = h->no_head_fusion ? "avgpool_kernel + fc_fp32_kernel + softmax_top1_kernel" : "resnet_head_kernel"; break;
     case STEP_SOFTMAX: k = "softmax_top1_kernel"; break;
     case STEP_CONV:
@@ -1209,7 +1248,7 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
       else if (h->impl != IDN_IMPL_TC || (cp.mode == MODE_STEM && h->stem_simt)) k = "conv_simt_kernel";
       else if (cp.mode == MODE_STEM) k = fuse ? "stem_pool_kernel" : "stem_kernel";
       else if (s.use_halo && cp.pair && s.b_resident) k = "conv_pair_res_kernel<" + N(cp.msub) + ", " + N(cp.num_taps == 9 ? 9 : 0) + ">";
-      else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + ">";
+      else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + (pair_conv ? ", 1>" : ">");
       else if (s.use_halo) k = "conv_halo_kernel<" + N(s.block_n) + ", " + N(cp.msub) + ", " + N(s.b_resident ? 1 : 0) + ", " +
                                N(s.b_resident ? (cp.num_taps == 9 ? 9 : 0) : (cp.b_group == 3 ? 3 : 0)) + (fuse ? ", 1>" : ">");
       else if (cp.tc_pair) k = "conv_tc_pair_kernel<" + N(s.block_n) + ">";

@@ -1394,7 +1394,9 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
   const int item_first = POOL ? 0 : pair;
   const int item_step = POOL ? 1 : num_pairs;
   const int total_items = POOL ? (row_hi - row_lo + 2 * kBlockM - 1) / (2 * kBlockM) : m_pairs * p.num_n_tiles;
-  const uint32_t peer_bar = bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 6);   // POOL: the partner's rows are in the ring
+  // POOL: "the partner's rows of item j are in the ring", barrier j & 1 (two, alternating, so that a parity wait can
+  // never fall two phases behind however the two CTAs drift)
+  auto peer_bar = [&](int j) { return bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 8 + (j & 1)); };
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA1);
@@ -1405,7 +1407,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
     for (int s = 0; s < kMaxAStages; ++s) { ptx::mbar_init(a_full(s), 1); ptx::mbar_init(a_empty(s), 1); }
     for (int s = 0; s < kMaxBStages; ++s) { ptx::mbar_init(b_full(s), 1); ptx::mbar_init(b_empty(s), 1); }
     for (int a = 0; a < 2; ++a) { ptx::mbar_init(tfull_bar(a), 1); ptx::mbar_init(tempty_bar(a), 2 * kEpiWarps); }
-    ptx::mbar_init(peer_bar, 1);
+    ptx::mbar_init(peer_bar(0), 1);
+    ptx::mbar_init(peer_bar(1), 1);
     ptx::sts32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7), 0u);       // POOL: "handshake timed out" flag
     ptx::fence_barrier_init();
   }
@@ -1532,8 +1535,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
         __threadfence();
         epi_bar_sync();                                   // this CTA's rows of the item are written and fenced
         if (threadIdx.x == 128) {
-          ptx::mbar_arrive_cluster(ptx::mapa(peer_bar, rank ^ 1u));
-          if (!mbar_wait_cluster(peer_bar, (uint32_t)(item & 1), 7, item)) ptx::sts32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7), 1u);
+          ptx::mbar_arrive_cluster(ptx::mapa(peer_bar(item), rank ^ 1u));
+          if (!mbar_wait_cluster(peer_bar(item), (uint32_t)((item >> 1) & 1), 7, item)) ptx::sts32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7), 1u);
         }
         epi_bar_sync();                                   // ... and so are the partner's
         if (ptx::lds32(bar_base + 8u * (2 * kMaxAStages + 2 * kMaxBStages + 7)) != 0u) break;

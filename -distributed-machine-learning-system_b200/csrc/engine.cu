@@ -1248,9 +1248,9 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
       else if (h->impl != IDN_IMPL_TC || (cp.mode == MODE_STEM && h->stem_simt)) k = "conv_simt_kernel";
       else if (cp.mode == MODE_STEM) k = fuse ? "stem_pool_kernel" : "stem_kernel";
       else if (s.use_halo && cp.pair && s.b_resident) k = "conv_pair_res_kernel<" + N(cp.msub) + ", " + N(cp.num_taps == 9 ? 9 : 0) + ">";
-      else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + (pair_conv ? ", 1>" : ">");
+      else if (s.use_halo && cp.pair) k = "conv_pair_kernel<" + N(s.block_n) + ", " + N(cp.b_group) + (pair_conv ? ", 1>" : ", 0>");
       else if (s.use_halo) k = "conv_halo_kernel<" + N(s.block_n) + ", " + N(cp.msub) + ", " + N(s.b_resident ? 1 : 0) + ", " +
-                               N(s.b_resident ? (cp.num_taps == 9 ? 9 : 0) : (cp.b_group == 3 ? 3 : 0)) + (fuse ? ", 1>" : ">");
+                               N(s.b_resident ? (cp.num_taps == 9 ? 9 : 0) : (cp.b_group == 3 ? 3 : 0)) + (fuse ? ", 1>" : ", 0>");
       else if (cp.tc_pair) k = "conv_tc_pair_kernel<" + N(s.block_n) + ">";
       else k = "conv_tc_kernel<" + N(s.block_n) + ">";
       break;

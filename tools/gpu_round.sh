@@ -27,8 +27,8 @@ benchref)
   echo "benchref rc=$?"; cut -c1-600 gpurun_out/bench_ref.json ;;
 ncu)
   for m in alexnet resnet18; do
-    # one pass = 13 launches (alexnet) / 20 (resnet18) incl. the record copy; skip the 3 warm-up passes, list 2 passes
-    if [ $m = alexnet ]; then SK=39; CN=26; else SK=60; CN=40; fi
+    # one pass = 12 launches (alexnet) / 20 (resnet18) incl. the record copy; skip the 3 warm-up passes, list 2 passes
+    if [ $m = alexnet ]; then SK=36; CN=24; else SK=60; CN=40; fi
     B="--steps 2 --warmup 3 --sustain 0 --range-images 0 --no-cpu --models $m"
     timeout 600 python bench.py $B > gpurun_out/ncu_plain_$m.log 2>&1 &&
     timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s $SK -c $CN --csv \

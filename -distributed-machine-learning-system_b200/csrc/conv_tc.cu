@@ -261,12 +261,12 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void sts128_(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
-__device__ __forceinline__ uint4 lds128_(uint32_t addr) {
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
 }  // namespace ptx
@@ -1238,8 +1238,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
           }
           const uint32_t slot = (uint32_t)rel % (uint32_t)kPoolRing;
           const uint32_t rowaddr = ring + slot * 128u;
-          ptx::sts128_(rowaddr + ((((uint32_t)(2 * chunk0)) ^ (slot & 7u)) << 4), w[0], w[1], w[2], w[3]);
-          ptx::sts128_(rowaddr + ((((uint32_t)(2 * chunk0 + 1)) ^ (slot & 7u)) << 4), w[4], w[5], w[6], w[7]);
+          ptx::sts128(rowaddr + ((((uint32_t)(2 * chunk0)) ^ (slot & 7u)) << 4), w[0], w[1], w[2], w[3]);
+          ptx::sts128(rowaddr + ((((uint32_t)(2 * chunk0 + 1)) ^ (slot & 7u)) << 4), w[4], w[5], w[6], w[7]);
         }
         ptx::tc_fence_before();
         __syncwarp();
@@ -1263,7 +1263,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant
 #pragma unroll
               for (int bb = 0; bb < 3; ++bb) {
                 const uint32_t slot = (uint32_t)(rel0 + aa * p.wp + bb) % (uint32_t)kPoolRing;
-                const uint4 x = ptx::lds128_(ring + slot * 128u + ((((uint32_t)c16) ^ (slot & 7u)) << 4));
+                const uint4 x = ptx::lds128(ring + slot * 128u + ((((uint32_t)c16) ^ (slot & 7u)) << 4));
                 if (aa == 0 && bb == 0) m = x;
                 else { m.x = max_bf16x2(m.x, x.x); m.y = max_bf16x2(m.y, x.y); m.z = max_bf16x2(m.z, x.z); m.w = max_bf16x2(m.w, x.w); }
               }
@@ -1935,14 +1935,8 @@ constexpr int kSpTilesW = 14, kSpTilesH = 7;
 constexpr int kSpBandRows = 2 * kStemTH + 5;                // input rows under a 16-row tile: 2*16 + 7 - 2 = 37
 constexpr int kSpSmemBytes = kSpStages * kStemStageBytes + kStemWBytes + 3 * kSpEBytes + 2 * kSpPRBytes + 512 + 1024;
 
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ uint4 lds128(uint32_t addr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-  return v;
-}
+using ptx::sts128;
+using ptx::lds128;
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   uint2 v;
   asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));

@@ -239,6 +239,7 @@ int launch_preprocess(const uint8_t* d_imgs, const PreMeta* d_meta, const int* d
 void build_axis_table(int in_size, int out_size, int crop_off, std::string* ints /* int32 bytes */);
 void resized_size(int h, int w, int* nh, int* nw);
 int crop_offset(int resized);
+void needed_source_range(int in_size, int out_size, int crop_off, int* first, int* last);
 void build_norm_lut(uint16_t* lut768);
 
 }  // namespace idn

@@ -132,6 +132,8 @@ struct idn_engine {
   std::vector<FusePair> fuse_pairs;
   bf16* pool_ring = nullptr;           // [num_sms / 2][1024 rows][256] bf16: the pairs' conv-row rings
   bool no_pool_fusion = false;
+  bool full_h2d = false;               // IDN_FULL_H2D=1: always copy whole images
+  int64_t h2d_bytes = 0;               // image bytes queued host-to-device so far (idn_h2d_bytes)
   int last_n = 0;
   // split-K scratch of the FC layers, shared by all of them (they run one after the other)
   float* splitk_ws = nullptr; size_t splitk_ws_floats = 0;
@@ -946,6 +948,7 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   e->device = device; e->model = model_id; e->cap = max_batch;
   { const char* v = std::getenv("IDN_STEM_SIMT"); e->stem_simt = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_POOL_FUSION"); e->no_pool_fusion = v && v[0] == '1'; }
+  { const char* v = std::getenv("IDN_FULL_H2D"); e->full_h2d = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_HEAD_FUSION"); e->no_head_fusion = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_DS_FUSION"); e->no_ds_fusion = v && v[0] == '1'; }
   int rc = IDN_OK;
@@ -1065,7 +1068,31 @@ int idn_submit_u8hwc(idn_handle h, const uint8_t* imgs, const int64_t* offsets, 
   // copy stream: the image bytes; the handle's stream: everything else, after the copy has landed
   // ... and the per-image records, so that nothing of this batch is left to fetch from the host when
   // the kernels of the previous batch finish
-  IDN_CUDA_TRY(cudaMemcpyAsync(sl.d_stage, imgs + lo, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+  // A batch of equally sized images at a constant stride (the usual case: one dataset, one packed buffer) is copied
+  // as ONE pitched copy of the source rows the centre crop reads -- Resize(256) + CenterCrop(224) never looks at
+  // the outer (1 - 224/256) / 2 of the shorter side: 198 of 224 rows for a 224 x 224 image, 11.6 % fewer bytes on a
+  // host link that bounds the whole end-to-end rate.  The rows keep their place in the staging buffer, so nothing
+  // else changes (the kernel reads at most one row past the last one it needs, inside the buffer).
+  bool rows_only = !h->full_h2d && n > 1;
+  const int H0 = hw[0], W0 = hw[1];
+  const int64_t stride = n > 1 ? offsets[1] - offsets[0] : 0;
+  for (int i = 0; i < n && rows_only; ++i)
+    rows_only = hw[2 * i] == H0 && hw[2 * i + 1] == W0 && offsets[i] == offsets[0] + (int64_t)i * stride;
+  rows_only = rows_only && stride >= (int64_t)H0 * W0 * 3 && H0 > 0 && W0 > 0;
+  size_t copied = bytes;
+  if (rows_only) {
+    int nh, nw, r0, r1;
+    resized_size(H0, W0, &nh, &nw);
+    needed_source_range(H0, nh, crop_offset(nh), &r0, &r1);
+    r1 = std::min(H0, r1 + 1);                                  // the kernel fetches one row ahead
+    const size_t row_bytes = (size_t)W0 * 3, first = (size_t)r0 * row_bytes, width = (size_t)(r1 - r0) * row_bytes;
+    IDN_CUDA_TRY(cudaMemcpy2DAsync(sl.d_stage + (offsets[0] - lo) + first, (size_t)stride, imgs + offsets[0] + first, (size_t)stride,
+                                   width, (size_t)n, cudaMemcpyHostToDevice, h->copy_stream));
+    copied = width * (size_t)n;
+  } else {
+    IDN_CUDA_TRY(cudaMemcpyAsync(sl.d_stage, imgs + lo, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+  }
+  h->h2d_bytes += (int64_t)copied;
   IDN_TRY(fill_meta(h, offsets, hw, n, lo, sl.h_meta, sl.d_meta, h->copy_stream));
   IDN_CUDA_TRY(cudaEventRecord(sl.ev_copied, h->copy_stream));
   IDN_CUDA_TRY(cudaStreamWaitEvent(h->stream, sl.ev_copied, 0));
@@ -1298,6 +1325,7 @@ int idn_debug_stop_after(idn_handle h, int step) {
 }
 
 int64_t idn_kernel_launches(idn_handle h) { return h ? h->launches : -1; }
+int64_t idn_h2d_bytes(idn_handle h) { return h ? h->h2d_bytes : -1; }
 
 int idn_set_timing(idn_handle h, int on) {
   if (!h) return IDN_EINVAL;

@@ -42,6 +42,20 @@ int crop_offset(int resized) {
 }
 
 // Table layout (int32): [ksize][xmin[224]][xcnt[224]][k[224][ksize]]
+// Source rows (or columns) [*first, *last) that crop positions 0..IDN_CROP-1 of an axis read: the bounds
+// build_axis_table computes for the first and the last crop position (same arithmetic).
+void needed_source_range(int in_size, int out_size, int crop_off, int* first, int* last) {
+  if (in_size == out_size) { *first = crop_off; *last = crop_off + IDN_CROP; return; }
+  const double scale = (double)in_size / (double)out_size;
+  const double support = scale < 1.0 ? 1.0 : scale;
+  const double c0 = (crop_off + 0.5) * scale, c1 = (IDN_CROP - 1 + crop_off + 0.5) * scale;
+  int x0 = (int)(c0 - support + 0.5);
+  if (x0 < 0) x0 = 0;
+  int x1 = (int)(c1 + support + 0.5);
+  if (x1 > in_size) x1 = in_size;
+  *first = x0; *last = x1;
+}
+
 void build_axis_table(int in_size, int out_size, int crop_off, std::string* out) {
   const int prec = 22;
   std::vector<int> xmin(IDN_CROP), xcnt(IDN_CROP);

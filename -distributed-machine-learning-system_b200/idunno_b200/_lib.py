@@ -41,6 +41,7 @@ SIGNATURES = {
     "idn_step_kernel": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_int]),
     "idn_debug_stop_after": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_kernel_launches": (C.c_int64, [C.c_void_p]),
+    "idn_h2d_bytes": (C.c_int64, [C.c_void_p]),
     "idn_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_step_wait_cycles": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "idn_step_time_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),

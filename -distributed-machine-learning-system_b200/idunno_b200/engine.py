@@ -190,6 +190,11 @@ class Engine:
     def kernel_launches(self) -> int:
         return int(self._lib.idn_kernel_launches(self._h))
 
+    @property
+    def h2d_bytes(self) -> int:
+        """Image bytes queued host-to-device so far (only the source rows the centre crop reads are copied)."""
+        return int(self._lib.idn_h2d_bytes(self._h))
+
 
 def preprocess(images, device: int = 0) -> np.ndarray:
     """uint8 HWC images -> bf16 bit patterns (uint16) NCHW [n, 3, 224, 224] via the CUDA kernel."""

@@ -145,6 +145,10 @@ int idn_debug_stop_after(idn_handle h, int step);
  * (idn_set_timing(h, 1) records CUDA events around every step; 2 additionally books the pipeline
  * waits idn_step_wait_cycles reports, which slows the kernels a little). */
 int64_t idn_kernel_launches(idn_handle h);
+/* Image bytes this handle has queued host-to-device since creation (idn_submit_u8hwc / idn_infer_u8hwc).  A batch
+ * of equally sized images at a constant stride is copied as one pitched copy of the source rows that
+ * Resize(256) + CenterCrop(224) reads (198 of 224 rows for a 224 x 224 image; IDN_FULL_H2D=1 copies whole images). */
+int64_t idn_h2d_bytes(idn_handle h);
 int idn_set_timing(idn_handle h, int on);
 int idn_step_time_ms(idn_handle h, int step, float* ms);
 /* With timing on: SM cycles the tensor-core kernel of plan step `step` spent blocked in each kind of

@@ -167,6 +167,38 @@ def test_full_query_of_400_is_consistent_with_small_batches(built_library, model
     _compare(f"{model}/batch400-tail", i1[380:], p1[380:], l1[380:], want)
 
 
+@pytest.mark.parametrize("shape", [(224, 224), (300, 260), (231, 517), (900, 640)])
+def test_only_the_rows_the_crop_reads_are_copied(built_library, monkeypatch, shape):
+    """A batch of equally sized images at a constant stride goes to the GPU as one pitched copy of the source rows
+    Resize(256) + CenterCrop(224) reads.  The staging buffers are reused, so the rows that are skipped hold the
+    previous batch's pixels: results must still equal an engine that copies whole images (IDN_FULL_H2D=1) bit for
+    bit, for upscaled, downscaled, portrait and landscape sources, and fewer bytes must have been queued."""
+    h, w = shape
+    rng = np.random.default_rng(h * 1000 + w)
+    a = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(6)]
+    b = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for _ in range(6)]
+    sd = make_state_dict("resnet18", 0, "default")
+    with Engine("resnet18", sd, max_batch=6) as eng:
+        for _ in range(3):                                   # every slot's staging buffer has held batch a
+            eng.infer(a)
+        k0 = eng.h2d_bytes
+        i1, p1, l1 = eng.infer(b, want_logits=True)
+        copied = eng.h2d_bytes - k0
+    monkeypatch.setenv("IDN_FULL_H2D", "1")
+    with Engine("resnet18", sd, max_batch=6) as eng:
+        k0 = eng.h2d_bytes
+        i2, p2, l2 = eng.infer(b, want_logits=True)
+        full = eng.h2d_bytes - k0
+    assert np.array_equal(l1, l2) and np.array_equal(i1, i2) and np.array_equal(p1, p2)
+    short = min(h, w)
+    print(f"\n[{h}x{w}] copied {copied} of {full} bytes ({copied / full:.3f})")
+    assert full >= 6 * h * w * 3
+    if h <= w:                                               # the rows are the shorter side: 224/256 of them (+ filter support)
+        assert copied < 0.93 * full, (copied, full)
+    else:
+        assert copied <= full
+
+
 def test_alexnet_tensor_batch_of_1200_matches_the_batch_400_engine(built_library):
     """A tensor batch larger than one wave of work items: with max_batch = 1200 FC8's split-K has 160 items for 74
     CTA pairs (a pair runs several rounds and waits, inside a round, for splits its neighbours are still computing)

@@ -1,3 +1,4 @@
+"""Experiment helper: the stride-2 / downsample step times of ResNet18 from a bench_detail.json."""
 import json,sys
 d=json.load(open(sys.argv[1]))['models']['resnet18']
 k=d['kernel_ms']

@@ -1327,6 +1327,14 @@ int idn_debug_stop_after(idn_handle h, int step) {
 int64_t idn_kernel_launches(idn_handle h) { return h ? h->launches : -1; }
 int64_t idn_h2d_bytes(idn_handle h) { return h ? h->h2d_bytes : -1; }
 
+int idn_debug_needed_rows(int H, int W, int* first_row, int* end_row) {
+  if (H <= 0 || W <= 0 || !first_row || !end_row) { set_error("idn_debug_needed_rows: bad argument"); return IDN_EINVAL; }
+  int nh, nw;
+  resized_size(H, W, &nh, &nw);
+  needed_source_range(H, nh, crop_offset(nh), first_row, end_row);
+  return IDN_OK;
+}
+
 int idn_set_timing(idn_handle h, int on) {
   if (!h) return IDN_EINVAL;
   h->timing = on != 0;

@@ -42,6 +42,7 @@ SIGNATURES = {
     "idn_debug_stop_after": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_kernel_launches": (C.c_int64, [C.c_void_p]),
     "idn_h2d_bytes": (C.c_int64, [C.c_void_p]),
+    "idn_debug_needed_rows": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "idn_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "idn_step_wait_cycles": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "idn_step_time_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),

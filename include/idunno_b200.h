@@ -149,6 +149,10 @@ int64_t idn_kernel_launches(idn_handle h);
  * of equally sized images at a constant stride is copied as one pitched copy of the source rows that
  * Resize(256) + CenterCrop(224) reads (198 of 224 rows for a 224 x 224 image; IDN_FULL_H2D=1 copies whole images). */
 int64_t idn_h2d_bytes(idn_handle h);
+/* Host-only: the source rows [*first_row, *end_row) of an H x W image that Resize(256) + CenterCrop(224) reads --
+ * what the pitched copy sends (plus the one row the kernel fetches ahead).  Needs no GPU; tests/test_host.py checks
+ * it against the oracle's Pillow coefficient bounds over a sweep of sizes. */
+int idn_debug_needed_rows(int H, int W, int* first_row, int* end_row);
 int idn_set_timing(idn_handle h, int on);
 int idn_step_time_ms(idn_handle h, int step, float* ms);
 /* With timing on: SM cycles the tensor-core kernel of plan step `step` spent blocked in each kind of

@@ -91,6 +91,32 @@ def test_library_exports_every_declared_symbol():
     assert b"sm_100a" in _lib.load_library().idn_version()
 
 
+def test_rows_sent_to_the_gpu_are_exactly_the_rows_the_crop_reads():
+    """The host-buffer path copies only source rows [first, end) of equally sized images (idn_debug_needed_rows, host
+    arithmetic, no GPU).  Against the oracle's restatement of Pillow's coefficient bounds: the union of the rows the 224
+    crop rows read must be exactly that range -- one row less would classify stale pixels -- over upscaled, downscaled,
+    square, portrait and landscape sources, including the smallest and some odd sizes."""
+    from oracle import pil_resize
+    lib = _lib.load_library()
+    sizes = [(224, 224), (225, 224), (1, 1), (2, 3), (3, 700), (37, 41), (255, 255), (256, 256), (257, 300), (300, 260),
+             (231, 517), (517, 231), (375, 500), (500, 375), (480, 640), (900, 640), (640, 900), (1000, 225), (1200, 1600)]
+    rng = np.random.default_rng(5)
+    sizes += [(int(a), int(b)) for a, b in rng.integers(1, 1500, (40, 2))]
+    for h, w in sizes:
+        nh, nw = pil_resize.resized_size(h, w)
+        top, _ = pil_resize.crop_offsets(nh, nw)
+        if nh == h:
+            lo, hi = top, top + 224                               # Pillow skips the vertical pass
+        else:
+            xmin, xcnt, _ = pil_resize.precompute_coeffs(h, nh)
+            lo = int(min(xmin[top + y] for y in range(224)))
+            hi = int(max(xmin[top + y] + xcnt[top + y] for y in range(224)))
+        a, b = ctypes.c_int(), ctypes.c_int()
+        assert lib.idn_debug_needed_rows(h, w, ctypes.byref(a), ctypes.byref(b)) == 0
+        assert (a.value, b.value) == (lo, hi), (h, w, a.value, b.value, lo, hi)
+        assert 0 <= a.value < b.value <= h
+
+
 def test_no_cpu_fallback_without_a_device():
     import torch
     if torch.cuda.is_available():

@@ -250,7 +250,7 @@ def bench_model(model, rank, world, device, args, peaks, dist):
         while pending:
             eng.collect(pending.pop(0))
     run_e2e(3)
-    e2e_steps = max(steps, 100)     # ~0.1-0.2 s: filling/draining the 3-deep pipeline is < 2 %, host jitter averages out
+    e2e_steps = max(steps, 200)     # ~0.2-0.4 s: filling/draining the 3-deep pipeline is < 1 %, host jitter averages out
     barrier()
     h2d0 = eng.h2d_bytes
     t0 = time.perf_counter()

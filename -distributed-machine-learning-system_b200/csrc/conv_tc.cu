@@ -2,8 +2,9 @@
 //
 //   D[128 pixels x BLOCK_N channels] (fp32, TMEM) += A[128 x 64] (bf16, smem) * B[BLOCK_N x 64]^T
 //
-// * one persistent CTA per SM, 8 warps: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer,
-//   warp 2 = TMEM allocator, warps 4..7 = epilogue (one thread per TMEM lane / output pixel);
+// * one persistent CTA per SM, 20 warps: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer,
+//   warp 2 = TMEM allocator, warp 3 = second producer where weights have their own ring, warps 4..19 =
+//   epilogue (a warp owns one TMEM lane quarter and every fourth 16-column chunk);
 // * operands arrive by TMA (cp.async.bulk.tensor) into a kStages-deep ring of 128B-swizzled,
 //   K-major tiles; mbarriers full[s]/empty[s] pair the producer with the MMA warp;
 // * the accumulator is double buffered in TMEM (tmem_full[a]/tmem_empty[a]) so the epilogue of
@@ -11,14 +12,18 @@
 // * a filter tap is a row offset into the flat padded NHWC activation matrix (common.cuh), so the
 //   k-loop is (taps x 64-channel blocks) and the A box of every k-block is a plain 2-D TMA box;
 // * epilogue: tcgen05.ld -> per-channel fp32 scale/shift (folded BatchNorm or bias) -> optional
-//   residual add -> optional ReLU -> bf16 (or fp32 logits) with 128-bit stores, written either in
+//   residual add -> optional ReLU -> bf16 (or fp32 logits) with 256-bit stores, written either in
 //   the tile's own geometry or scattered to the parity planes a following stride-2 layer reads.
 //
 // Kernels in this file, all sharing the epilogue and the barrier/watchdog helpers:
-//   conv_tc_kernel        one TMA box per (tap, 64-channel block): FC layers, stride-2 and 1x1 layers
+//   conv_tc_kernel        one TMA box per (tap, 64-channel block): stride-2 and 1x1 layers (a second problem may
+//                         ride in the launch: ResNet18's downsamples)
+//   conv_tc_pair_kernel   the same ring on CTA pairs: FC layers (FC8 with a deterministic split-K), 256-wide stride-2
 //   conv_halo_kernel      stride-1 multi-tap layers: one staged activation tile per channel block, taps
-//                         are descriptor offsets into it; weights resident (64-wide) or streamed
-//   conv_pair_kernel      the same on CTA pairs (tcgen05 cta_group::2): 192- and 256-wide layers
+//                         are descriptor offsets into it; weights resident (64-wide) or streamed; POOL: the
+//                         following 3x3/s2 max-pool in the epilogue (AlexNet features.0 + features.2)
+//   conv_pair_kernel      the same on CTA pairs (tcgen05 cta_group::2): 192- and 256-wide layers; POOL: the
+//                         following max-pool through an L2-resident ring (AlexNet features.10 + features.12)
 //   conv_pair_res_kernel  64-wide layers on CTA pairs (experiment, off by default)
 //   stem_kernel           ResNet18's 7x7 s2 p3 stem (C = 3), conv1 + bn1 + relu (tests, activation taps)
 //   stem_pool_kernel      the product path: the same plus the following max-pool, pooled pixels stored directly

@@ -53,7 +53,12 @@ typedef struct idn_engine* idn_handle;
  * INTEGRATION.md; idunno_b200.weights.pack_state_dict builds it).  BatchNorm is folded to a
  * per-channel fp32 scale/shift, weights are converted to bf16 and re-laid-out for the kernels.
  * max_batch = largest tensor batch one pass processes (activation buffers are sized for it; longer
- * inputs are processed in chunks of max_batch). */
+ * inputs are processed in chunks of max_batch).
+ * One handle's work is ordered on its stream.  Handles of DIFFERENT models may run at the same time on one GPU
+ * (the concurrent AlexNet + ResNet18 jobs of the reference).  Two handles of the SAME model running at the same
+ * time on one GPU are not supported with the default kernels: AlexNet's last FC layer splits K over CTAs that wait
+ * for one another inside the launch, and two such launches, each holding part of the GPU, could wait for ever
+ * (the pipeline watchdog turns that into an error after two seconds).  Set IDN_NO_FC_SPLIT=1 for such a set-up. */
 int idn_create(int device, int model_id, const void* weights_blob, size_t n_bytes, int max_batch,
                idn_handle* out);
 

@@ -172,6 +172,8 @@ struct ConvParams {
   // that an image's result does not depend on the engine's capacity or on the tensor batch it falls in.
   int k_steps;                // conv_halo_kernel, resident weights: MMA steps (16 channels) issued per channel block;
                               // the steps left out have all-zero weights (0 is read as 4)
+  int split_defer;            // split-K only: 1 = write the partial tiles and stop; the kernel after this one adds them
+                              // (AlexNet's FC8: softmax_top1_splitk_kernel) -- no CTA waits for another
   int split_k;                // 0 / 1: off
   float* splitk_ws;           // fp32 partial tiles [tile half][split][128][N tile]
   unsigned int* splitk_cnt;   // per tile half: {arrivals, slices reduced}; zero between launches
@@ -218,6 +220,8 @@ int launch_resnet_head(const bf16* act, int nimg, int img_rows, int wp, int H, i
 int launch_resnet_head_fused(const bf16* act, int nimg, int img_rows, int wp, int H, int W, int C,
                              const float* fc_wt, const float* fc_b, float* feats, float* logits_out_or_null,
                              int32_t* idx, float* prob, cudaStream_t st);
+int launch_softmax_top1_splitk(const float* ws, int splits, int num_n_tiles, const float* scale, const float* shift, int nimg,
+                               float* logits_out_or_null, int32_t* idx, float* prob, cudaStream_t st);
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out_or_null,
                         int32_t* idx, float* prob, cudaStream_t st);
 // Copies n_words 32-bit words with SM loads/stores.  Used for the few KB of per-batch records that come

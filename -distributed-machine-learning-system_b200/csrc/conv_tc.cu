@@ -892,6 +892,10 @@ conv_tc_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive_cluster(ptx::mapa(tempty_bar(as), 0));
+        if (p.split_defer) {                             // the next kernel adds the partials: nothing to wait for
+          if (++as == 2) { as = 0; aph ^= 1u; }
+          return true;
+        }
         __threadfence();
         epi_bar_sync();                                  // every partial of this CTA is written and fenced
         unsigned int* cnt = p.splitk_cnt + 2 * (mn * 2 + (int)rank);   // [0] arrivals, [1] slices reduced

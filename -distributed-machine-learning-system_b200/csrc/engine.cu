@@ -133,6 +133,7 @@ struct idn_engine {
   bf16* pool_ring = nullptr;           // [num_sms / 2][1024 rows][256] bf16: the pairs' conv-row rings
   bool no_pool_fusion = false;
   bool full_h2d = false;               // IDN_FULL_H2D=1: always copy whole images
+  bool no_split_defer = false;         // IDN_NO_SPLIT_DEFER=1: FC8's splits are added inside its own kernel (CTAs wait)
   int64_t h2d_bytes = 0;               // image bytes queued host-to-device so far (idn_h2d_bytes)
   int last_n = 0;
   // split-K scratch of the FC layers, shared by all of them (they run one after the other)
@@ -781,6 +782,7 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
     return e->impl == IDN_IMPL_TC && !e->no_pool_fusion && e->stop_after != fp.conv_step && c.use_halo && c.cp.pair &&
            !c.b_resident && c.cp.num_n_tiles == 1 && ((c.block_n == 192 && c.cp.b_group == 5) || (c.block_n == 256 && c.cp.b_group == 3));
   };
+  const Step* deferred_fc = nullptr;
   int step_no = 0;
   for (Step& s : e->steps) {
     if (e->stop_after >= 0 && step_no > e->stop_after) break;
@@ -808,6 +810,14 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
             s.cp.pool_img_rows = fp.img_rows; s.cp.pool_wp = fp.wp; s.cp.pool_oh = fp.oh; s.cp.pool_ow = fp.ow;
             s.cp.pool_ring = e->pool_ring;
           }
+        // AlexNet's FC8 (split-K, straight before the softmax step): its partial tiles are added by the softmax kernel
+        // instead of by waiting CTAs -- unless this very step's output is wanted (activation tap) or IDN_NO_SPLIT_DEFER=1
+        s.cp.split_defer = 0;
+        if (s.cp.split_k > 1 && e->impl == IDN_IMPL_TC && step_idx + 1 < (int)e->steps.size() &&
+            e->steps[step_idx + 1].kind == STEP_SOFTMAX && e->stop_after != step_idx && !e->no_split_defer) {
+          s.cp.split_defer = 1;
+          deferred_fc = &s;
+        }
         if (s.merged_into >= 0 && ds_fusion_active(e, e->impl)) { e->launches -= 1; break; }   // rode in that step's launch
         IDN_TRY(launch_conv_step(e, s, n, e->impl, st));
         break;
@@ -833,6 +843,11 @@ static int run_plan(idn_engine* e, const uint8_t* d_imgs, int n, int32_t* d_idx,
         e->launches += 2;                       // avgpool, fc, softmax/top-1
         break;
       case STEP_SOFTMAX:
+        if (deferred_fc != nullptr) {
+          const ConvParams& f = deferred_fc->cp;
+          IDN_TRY(launch_softmax_top1_splitk(e->splitk_ws, f.split_k, f.num_n_tiles, f.scale, f.shift, n, d_logits, d_idx, d_prob, st));
+          break;
+        }
         IDN_TRY(launch_softmax_top1(e->logits_pad, 1024, n, d_logits, d_idx, d_prob, st));
         break;
     }
@@ -949,6 +964,7 @@ int idn_create(int device, int model_id, const void* weights_blob, size_t n_byte
   { const char* v = std::getenv("IDN_STEM_SIMT"); e->stem_simt = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_POOL_FUSION"); e->no_pool_fusion = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_FULL_H2D"); e->full_h2d = v && v[0] == '1'; }
+  { const char* v = std::getenv("IDN_NO_SPLIT_DEFER"); e->no_split_defer = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_HEAD_FUSION"); e->no_head_fusion = v && v[0] == '1'; }
   { const char* v = std::getenv("IDN_NO_DS_FUSION"); e->no_ds_fusion = v && v[0] == '1'; }
   int rc = IDN_OK;
@@ -1269,7 +1285,10 @@ int idn_step_kernel(idn_handle h, int step, char* name, int name_len) {
     case STEP_PRE: k = "preprocess_kernel<" + N(h->pre_mode) + ">"; break;
     case STEP_POOL: k = pair_pool ? "(folded into the convolution before it)" : (h->fuse_pool_step == step && !h->no_pool_fusion && !h->stem_simt) ? (h->steps[h->fuse_stem_step].cp.mode == MODE_STEM ? "(folded into stem_pool_kernel)" : "(folded into the convolution before it)") : "maxpool3x3s2_kernel"; break;
     case STEP_RHEAD: k = h->no_head_fusion ? "avgpool_kernel + fc_fp32_kernel + softmax_top1_kernel" : "resnet_head_kernel"; break;
-    case STEP_SOFTMAX: k = "softmax_top1_kernel"; break;
+    case STEP_SOFTMAX:
+      k = (step > 0 && h->steps[step - 1].kind == STEP_CONV && h->steps[step - 1].cp.split_k > 1 && h->impl == IDN_IMPL_TC &&
+           !h->no_split_defer) ? "softmax_top1_splitk_kernel" : "softmax_top1_kernel";
+      break;
     case STEP_CONV:
       if (s.merged_into >= 0 && h->impl == IDN_IMPL_TC && !h->no_ds_fusion) k = "(rides in the launch of step " + N(s.merged_into) + ")";
       else if (h->impl != IDN_IMPL_TC || (cp.mode == MODE_STEM && h->stem_simt)) k = "conv_simt_kernel";

@@ -60,6 +60,8 @@ int launch_maxpool(const PoolParams& p, cudaStream_t st) {
 // Replaces softmax + topk(.,1) of alexnet_resnet.py:80-84; exact ties -> lowest class index.
 // The 1000 logits of an image sit in registers (8 float4 per lane, all loads issued before the first use),
 // so the row is read once and the two passes cost one memory latency instead of ~60.
+__device__ __forceinline__ void warp_softmax_top1_regs(float4 (&v)[8], int lane, int32_t* idx_out,
+                                                       float* prob_out, float* copy_out);
 __device__ __forceinline__ void warp_softmax_top1(const float* logits, int lane, int32_t* idx_out,
                                                   float* prob_out, float* copy_out) {
   constexpr int kVec = IDN_NUM_CLASSES / 4;          // 250 float4
@@ -70,6 +72,12 @@ __device__ __forceinline__ void warp_softmax_top1(const float* logits, int lane,
     v[i] = q < kVec ? *(reinterpret_cast<const float4*>(logits) + q)       // global or shared memory
                     : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
   }
+  warp_softmax_top1_regs(v, lane, idx_out, prob_out, copy_out);
+}
+// the row's 1000 logits in registers: lane l holds float4 groups l, l + 32, ... (-inf beyond 250)
+__device__ __forceinline__ void warp_softmax_top1_regs(float4 (&v)[8], int lane, int32_t* idx_out,
+                                                       float* prob_out, float* copy_out) {
+  constexpr int kVec = IDN_NUM_CLASSES / 4;
   float best = -INFINITY;
   int best_i = 0x7fffffff;
 #pragma unroll
@@ -119,6 +127,58 @@ __global__ void __launch_bounds__(128) softmax_top1_kernel(const float* __restri
   const float* l = logits + (long long)warp * ld;       // ld % 4 == 0: rows are float4-aligned
   warp_softmax_top1(l, lane, idx + warp, prob + warp,
                     logits_out != nullptr ? logits_out + (long long)warp * IDN_NUM_CLASSES : nullptr);
+}
+
+// AlexNet's FC8 with split-K leaves `splits` fp32 partial tiles per 128 x 256 tile half
+// ([tile half][split][128 rows][256 columns], tile half = (m_pair * num_n_tiles + n_tile) * 2 + CTA rank, see
+// conv_tc_pair_kernel); this kernel adds them in split order, applies scale/shift (the bias) -- the arithmetic and
+// order of the in-kernel reduction it replaces, so the logits are the same bits -- and goes on to softmax/top-1.
+// No CTA of the FC kernel has to wait for another one.
+__global__ void __launch_bounds__(128) softmax_top1_splitk_kernel(const float* __restrict__ ws, int splits, int num_n_tiles,
+                                                                  const float* __restrict__ scale, const float* __restrict__ shift,
+                                                                  int nimg, float* __restrict__ logits_out,
+                                                                  int32_t* __restrict__ idx, float* __restrict__ prob) {
+  pdl_wait();
+  pdl_launch_dependents();
+  const int img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (img >= nimg) return;
+  constexpr int kVec = IDN_NUM_CLASSES / 4, kTile = 128 * 256;
+  const int m_pair = img >> 8, rank = (img >> 7) & 1, row = img & 127;
+  float4 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int q = lane + 32 * i;
+    if (q < kVec) {
+      const int n_tile = q >> 6, col = (q & 63) * 4;
+      const float* src = ws + ((size_t)((m_pair * num_n_tiles + n_tile) * 2 + rank) * splits) * kTile + row * 256 + col;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int sp0 = 0; sp0 < splits; sp0 += 8) {        // eight partials in flight, added in split order
+        float4 t[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          t[j] = sp0 + j < splits ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)(sp0 + j) * kTile))
+                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (sp0 + j < splits) { acc.x += t[j].x; acc.y += t[j].y; acc.z += t[j].z; acc.w += t[j].w; }
+      }
+      const float4 sc = __ldg(reinterpret_cast<const float4*>(scale) + q), sh = __ldg(reinterpret_cast<const float4*>(shift) + q);
+      v[i] = make_float4(fmaf(acc.x, sc.x, sh.x), fmaf(acc.y, sc.y, sh.y), fmaf(acc.z, sc.z, sh.z), fmaf(acc.w, sc.w, sh.w));
+    } else {
+      v[i] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    }
+  }
+  warp_softmax_top1_regs(v, lane, idx + img, prob + img,
+                         logits_out != nullptr ? logits_out + (long long)img * IDN_NUM_CLASSES : nullptr);
+}
+
+int launch_softmax_top1_splitk(const float* ws, int splits, int num_n_tiles, const float* scale, const float* shift, int nimg,
+                               float* logits_out, int32_t* idx, float* prob, cudaStream_t st) {
+  if (nimg <= 0) return IDN_OK;
+  IDN_CUDA_TRY(launch_pdl(softmax_top1_splitk_kernel, dim3((nimg + 3) / 4), dim3(128), 0, st, ws, splits, num_n_tiles, scale, shift,
+                          nimg, logits_out, idx, prob));
+  return IDN_OK;
 }
 
 int launch_softmax_top1(const float* logits, int ld, int nimg, float* logits_out, int32_t* idx,

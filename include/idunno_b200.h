@@ -54,11 +54,11 @@ typedef struct idn_engine* idn_handle;
  * per-channel fp32 scale/shift, weights are converted to bf16 and re-laid-out for the kernels.
  * max_batch = largest tensor batch one pass processes (activation buffers are sized for it; longer
  * inputs are processed in chunks of max_batch).
- * One handle's work is ordered on its stream.  Handles of DIFFERENT models may run at the same time on one GPU
- * (the concurrent AlexNet + ResNet18 jobs of the reference).  Two handles of the SAME model running at the same
- * time on one GPU are not supported with the default kernels: AlexNet's last FC layer splits K over CTAs that wait
- * for one another inside the launch, and two such launches, each holding part of the GPU, could wait for ever
- * (the pipeline watchdog turns that into an error after two seconds).  Set IDN_NO_FC_SPLIT=1 for such a set-up. */
+ * One handle's work is ordered on its stream; several handles may run at the same time on one GPU (the concurrent
+ * AlexNet + ResNet18 jobs of the reference): no CTA of any kernel waits for a CTA outside its own cluster.  (The
+ * one kernel that could -- AlexNet's last FC layer with its K loop split over CTAs -- leaves the sum of its partial
+ * tiles to the softmax kernel behind it; only with IDN_NO_SPLIT_DEFER=1, or when that layer's own output is read back
+ * as an activation tap, do its CTAs wait for one another, and two such launches must then not share a GPU.) */
 int idn_create(int device, int model_id, const void* weights_blob, size_t n_bytes, int max_batch,
                idn_handle* out);
 

@@ -199,6 +199,29 @@ def test_only_the_rows_the_crop_reads_are_copied(built_library, monkeypatch, sha
         assert copied <= full
 
 
+def test_alexnet_fc8_partials_summed_by_the_softmax_kernel_are_bit_identical(built_library, monkeypatch):
+    """FC8 splits K eight ways.  In the product path it only writes its partial tiles and softmax_top1_splitk_kernel adds
+    them; with IDN_NO_SPLIT_DEFER=1 (and for activation taps of FC8) the FC kernel's own CTAs wait for one another and
+    add them.  Same split order, same fmaf with the bias: logits, classes and probabilities must be the same bits, for
+    a ragged batch (37 on an engine of 48: second 128-row half empty) and one of 300 (both row pairs)."""
+    sd = make_state_dict("alexnet", 0, "stress")
+    imgs = [synth_image(i, mixed=True) for i in range(37)]
+    big = list(noise_images(300, seed=3))
+    with Engine("alexnet", sd, max_batch=48) as eng:
+        assert dict(eng.step_kernels())["softmax+top1"] == "softmax_top1_splitk_kernel"
+        i1, p1, l1 = eng.infer(imgs, want_logits=True)
+    with Engine("alexnet", sd, max_batch=300) as eng:
+        i3, p3, l3 = eng.infer(big, want_logits=True)
+    monkeypatch.setenv("IDN_NO_SPLIT_DEFER", "1")
+    with Engine("alexnet", sd, max_batch=48) as eng:
+        assert dict(eng.step_kernels())["softmax+top1"] == "softmax_top1_kernel"
+        i2, p2, l2 = eng.infer(imgs, want_logits=True)
+    with Engine("alexnet", sd, max_batch=300) as eng:
+        i4, p4, l4 = eng.infer(big, want_logits=True)
+    assert np.array_equal(l1, l2) and np.array_equal(i1, i2) and np.array_equal(p1, p2)
+    assert np.array_equal(l3, l4) and np.array_equal(i3, i4) and np.array_equal(p3, p4)
+
+
 def test_alexnet_tensor_batch_of_1200_matches_the_batch_400_engine(built_library):
     """A tensor batch larger than one wave of work items: with max_batch = 1200 FC8's split-K has 160 items for 74
     CTA pairs (a pair runs several rounds and waits, inside a round, for splits its neighbours are still computing)

@@ -140,43 +140,40 @@ __global__ void __launch_bounds__(128) softmax_top1_splitk_kernel(const float* _
                                                                   int32_t* __restrict__ idx, float* __restrict__ prob) {
   pdl_wait();
   pdl_launch_dependents();
-  const int img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (img >= nimg) return;
+  // one image per block: 128 threads add the partials of two float4 groups each (16 loads in flight) into the image's
+  // logits in shared memory, then warp 0 runs the same warp-level softmax/top-1 as softmax_top1_kernel on them
+  __shared__ __align__(16) float s_logits[IDN_NUM_CLASSES];
+  const int img = blockIdx.x;
   constexpr int kVec = IDN_NUM_CLASSES / 4, kTile = 128 * 256;
   const int m_pair = img >> 8, rank = (img >> 7) & 1, row = img & 127;
-  float4 v[8];
+  for (int q = threadIdx.x; q < kVec; q += 128) {
+    const int n_tile = q >> 6, col = (q & 63) * 4;
+    const float* src = ws + ((size_t)((m_pair * num_n_tiles + n_tile) * 2 + rank) * splits) * kTile + row * 256 + col;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int sp0 = 0; sp0 < splits; sp0 += 8) {          // eight partials in flight, added in split order
+      float4 t[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int q = lane + 32 * i;
-    if (q < kVec) {
-      const int n_tile = q >> 6, col = (q & 63) * 4;
-      const float* src = ws + ((size_t)((m_pair * num_n_tiles + n_tile) * 2 + rank) * splits) * kTile + row * 256 + col;
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int sp0 = 0; sp0 < splits; sp0 += 8) {        // eight partials in flight, added in split order
-        float4 t[8];
+      for (int j = 0; j < 8; ++j)
+        t[j] = sp0 + j < splits ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)(sp0 + j) * kTile))
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          t[j] = sp0 + j < splits ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)(sp0 + j) * kTile))
-                                  : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (sp0 + j < splits) { acc.x += t[j].x; acc.y += t[j].y; acc.z += t[j].z; acc.w += t[j].w; }
-      }
-      const float4 sc = __ldg(reinterpret_cast<const float4*>(scale) + q), sh = __ldg(reinterpret_cast<const float4*>(shift) + q);
-      v[i] = make_float4(fmaf(acc.x, sc.x, sh.x), fmaf(acc.y, sc.y, sh.y), fmaf(acc.z, sc.z, sh.z), fmaf(acc.w, sc.w, sh.w));
-    } else {
-      v[i] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+      for (int j = 0; j < 8; ++j)
+        if (sp0 + j < splits) { acc.x += t[j].x; acc.y += t[j].y; acc.z += t[j].z; acc.w += t[j].w; }
     }
+    const float4 sc = __ldg(reinterpret_cast<const float4*>(scale) + q), sh = __ldg(reinterpret_cast<const float4*>(shift) + q);
+    reinterpret_cast<float4*>(s_logits)[q] =
+        make_float4(fmaf(acc.x, sc.x, sh.x), fmaf(acc.y, sc.y, sh.y), fmaf(acc.z, sc.z, sh.z), fmaf(acc.w, sc.w, sh.w));
   }
-  warp_softmax_top1_regs(v, lane, idx + img, prob + img,
-                         logits_out != nullptr ? logits_out + (long long)img * IDN_NUM_CLASSES : nullptr);
+  __syncthreads();
+  if (threadIdx.x < 32)
+    warp_softmax_top1(s_logits, (int)threadIdx.x, idx + img, prob + img,
+                      logits_out != nullptr ? logits_out + (long long)img * IDN_NUM_CLASSES : nullptr);
 }
 
 int launch_softmax_top1_splitk(const float* ws, int splits, int num_n_tiles, const float* scale, const float* shift, int nimg,
                                float* logits_out, int32_t* idx, float* prob, cudaStream_t st) {
   if (nimg <= 0) return IDN_OK;
-  IDN_CUDA_TRY(launch_pdl(softmax_top1_splitk_kernel, dim3((nimg + 3) / 4), dim3(128), 0, st, ws, splits, num_n_tiles, scale, shift,
+  IDN_CUDA_TRY(launch_pdl(softmax_top1_splitk_kernel, dim3(nimg), dim3(128), 0, st, ws, splits, num_n_tiles, scale, shift,
                           nimg, logits_out, idx, prob));
   return IDN_OK;
 }
